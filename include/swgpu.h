@@ -1,0 +1,120 @@
+/*
+ * swgpu.h -- C-ABI of the B200 Smith-Waterman database-search engine (libswgpu.so).
+ *
+ * Plain pointers and sizes only; no CUDA or torch types cross this boundary.
+ * This is the `extern "C"` device layer the C host code (alignment_cmdline.c in
+ * this repo) calls, and what a maintainer of the reference would bind instead of
+ * its OpenMP loop.  Each entry point names the reference interface it replaces
+ * (paths relative to the reference tree).
+ *
+ * Residue codes are the reference's: letters_to_index() of src/alignment_scoring.c:70-81
+ * (A..Z -> 1..26, '*' -> 31).  Code 0 is reserved by the engine as padding.
+ * The substitution table is the reference's scoring_t::swap_scores, int8 [32][32],
+ * indexed [query code][target code] (src/alignment_scoring.h:34, src/alignment.c:33,41).
+ * Gap penalties follow src/alignment_scoring.c:35-36: a gap of length N costs
+ * gap_open + N*gap_extend (both normally negative).
+ *
+ * All functions return 0 on success and a negative SWGPU_E* code on failure;
+ * swgpu_last_error() gives the message.  Nothing here ever falls back to the CPU:
+ * without a CUDA device every compute entry point fails with SWGPU_ENODEV.
+ */
+#ifndef SWGPU_H_SEEN
+#define SWGPU_H_SEEN
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SWGPU_OK        0
+#define SWGPU_ENODEV   -1   /* no CUDA device / driver */
+#define SWGPU_ECUDA    -2   /* a CUDA call failed */
+#define SWGPU_EINVAL   -3   /* bad argument */
+#define SWGPU_ENOMEM   -4
+
+typedef struct swgpu_db swgpu_db_t;   /* packed, HBM-resident database on one GPU */
+
+/* Packing knobs (0 = engine default). */
+typedef struct {
+    int32_t long_threshold;   /* targets longer than this go to the intra-sequence kernel */
+    int32_t reserved[7];
+} swgpu_pack_opts_t;
+
+/* Per-search statistics, all device-timed with CUDA events on the engine's stream. */
+typedef struct {
+    double  ms_total;         /* first kernel launch -> last result resident in HBM */
+    double  ms_inter;         /* inter-sequence packed 16-bit kernel (K1) */
+    double  ms_intra;         /* intra-sequence 32-bit kernel, long targets (K3) */
+    double  ms_rescore;       /* 32-bit rescoring of saturated targets (K2 = K3 code path) */
+    double  ms_h2d, ms_d2h;   /* query/table upload, score download (host API only) */
+    int64_t cells;            /* sum over targets of Lq * Lt, real residues */
+    int64_t cells_inter, cells_intra, cells_rescore;
+    int64_t n_rescored;       /* targets whose 16-bit result saturated */
+    int64_t n_long;           /* targets scored by the intra-sequence kernel */
+    int32_t kernel_launches;  /* engine kernels launched by this search */
+    int32_t tile_rows;        /* query rows per register tile chosen for K1 */
+} swgpu_stats_t;
+
+/* Top hit with coordinates (the reference has no counterpart). */
+typedef struct {
+    int32_t score;
+    int32_t q_start, q_end, t_start, t_end;   /* 0-based inclusive; -1 if score == 0 */
+    int64_t entry;                            /* file-order index of the target */
+} swgpu_hit_t;
+
+int         swgpu_device_count(void);
+const char *swgpu_last_error(void);
+const char *swgpu_version(void);
+
+/*
+ * Database packing.  Replaces the batch build of src/alignment_cmdline.c:422-457
+ * (encode, 16-lane interleave, '*' padding): here targets are sorted by length
+ * inside the engine (the reference demands a pre-sorted file, :431-439), grouped
+ * into 64-target chunks, column-interleaved and uploaded once.
+ *   codes    n_residues residue codes, targets back to back, file order
+ *   offsets  n_targets+1 prefix offsets into codes
+ *   entry_base  file-order index of target 0 of this shard (multi-GPU sharding)
+ */
+int  swgpu_db_create(swgpu_db_t **out, int device, const int8_t *codes, const int64_t *offsets,
+                     int64_t n_targets, int64_t entry_base, const swgpu_pack_opts_t *opts);
+void swgpu_db_destroy(swgpu_db_t *db);
+int64_t swgpu_db_num_targets(const swgpu_db_t *db);
+int64_t swgpu_db_num_residues(const swgpu_db_t *db);
+int64_t swgpu_db_device_bytes(const swgpu_db_t *db);
+
+/*
+ * One-to-many scoring: replaces the `omp parallel for` over alignment_fill_matrices
+ * (src/alignment_cmdline.c:504-507, src/alignment.c:47-187) for the whole database.
+ * scores[n_targets] are written in FILE order (the order Entry #N is printed in,
+ * src/tools/sw_cmdline.c:55-72) as int32: exact scores, including those above the
+ * reference's int16 range.  Query and table are host pointers; scores is a host pointer.
+ */
+int swgpu_search(swgpu_db_t *db, const int8_t *query, int64_t query_len,
+                 const int8_t *table /* [32*32] */, int gap_open, int gap_extend,
+                 int32_t *scores, swgpu_stats_t *stats);
+
+/* Same search, scores left resident on the device (no D2H); used for device-timed
+ * throughput.  swgpu_db_scores_d2h() copies the last result out. */
+int swgpu_search_resident(swgpu_db_t *db, const int8_t *query, int64_t query_len,
+                          const int8_t *table, int gap_open, int gap_extend, swgpu_stats_t *stats);
+int swgpu_db_scores_d2h(swgpu_db_t *db, int32_t *scores);
+
+/*
+ * Device-side top-k of the last search (score desc, file-order entry asc) with
+ * linear-space end/start coordinates recomputed on the GPU for the k hits.
+ */
+int swgpu_topk(swgpu_db_t *db, int k, swgpu_hit_t *hits, int *n_hits);
+
+/* Single-batch call with the reference's own batch layout: 16 lanes interleaved
+ * [pos][lane], pad 31 -- the GPU twin of alignment_fill_matrices(aligner_t*)
+ * (src/alignment.c:47).  Far too fine-grained to be fast; kept for API parity. */
+int swgpu_fill_batch16(int device, const int8_t *query, int64_t query_len,
+                       const int8_t *batch_interleaved, int64_t padded_len, int lanes,
+                       const int8_t *table, int gap_open, int gap_extend, int32_t *scores16);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SWGPU_H_SEEN */

@@ -1,0 +1,391 @@
+// swgpu.cu -- implementation of the C-ABI in include/swgpu.h (thin extern "C" layer over the
+// kernels in sw_kernels.cuh).  No CPU fallback: every compute entry point needs a CUDA device.
+#include "../../include/swgpu.h"
+#include "db_pack.h"
+#include "sw_kernels.cuh"
+
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <cstdarg>
+#include <vector>
+#include <algorithm>
+
+namespace {
+
+thread_local char g_err[512] = "";
+
+int fail(int code, const char* fmt, ...) {
+  va_list ap; va_start(ap, fmt); vsnprintf(g_err, sizeof(g_err), fmt, ap); va_end(ap);
+  return code;
+}
+
+#define CU(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) \
+  return fail(e_ == cudaErrorNoDevice || e_ == cudaErrorInsufficientDriver ? SWGPU_ENODEV : SWGPU_ECUDA, \
+              "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); } while (0)
+
+constexpr int kDefaultLongThreshold = 3072;
+constexpr int kTileChoices[] = {32, 28, 24, 20, 16};
+
+}  // namespace
+
+struct swgpu_db {
+  int device = 0;
+  int sm_count = 0;
+  int64_t n = 0, n_residues = 0, n_long = 0, n_chunks = 0, entry_base = 0;
+  int32_t max_len = 0, max_chunk_cols = 0;
+  // device arrays (database, resident)
+  int8_t*   d_plain = nullptr;
+  int64_t*  d_plain_off = nullptr;
+  int64_t*  d_order = nullptr;
+  uint2*    d_cols = nullptr;
+  int64_t*  d_chunk_off = nullptr;
+  int32_t*  d_chunk_cols = nullptr;
+  // device scratch (per search)
+  int32_t*  d_scores = nullptr;        // file order
+  unsigned* d_raw = nullptr;           // n_chunks*32
+  int*      d_rescore_list = nullptr;  // up to n
+  unsigned* d_counters = nullptr;      // [0]=k1 queue, [1]=k3 long queue, [2]=rescore count, [3]=k3 rescore queue
+  uint2*    d_bnd1 = nullptr;  long long bnd1_stride = 0;  int k1_grid = 0;
+  int2*     d_bnd3 = nullptr;  long long bnd3_stride = 0;  int k3_grid = 0;
+  int8_t*   d_query = nullptr; int64_t query_cap = 0;
+  int8_t*   d_table = nullptr;
+  unsigned* d_prof = nullptr;  size_t prof_cap = 0;
+  int64_t   device_bytes = 0;
+  // host copies needed after packing
+  std::vector<int64_t> h_order;
+  std::vector<int64_t> h_len_sorted_prefix;   // plain_off (sorted)
+  cudaStream_t s_main = nullptr, s_aux = nullptr;
+  cudaEvent_t ev[8] = {};
+  int64_t last_lq = 0;
+  bool have_scores = false;
+};
+
+namespace {
+
+template <typename T>
+int dalloc(swgpu_db* db, T** p, size_t count) {
+  const size_t bytes = std::max<size_t>(count, 1) * sizeof(T);
+  CU(cudaMalloc((void**)p, bytes));
+  db->device_bytes += (int64_t)bytes;
+  return SWGPU_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int swgpu_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return n;
+}
+
+const char* swgpu_last_error(void) { return g_err; }
+const char* swgpu_version(void) { return "swgpu 0.1 (sm_100a)"; }
+
+void swgpu_db_destroy(swgpu_db_t* db) {
+  if (!db) return;
+  cudaSetDevice(db->device);
+  cudaFree(db->d_plain); cudaFree(db->d_plain_off); cudaFree(db->d_order); cudaFree(db->d_cols);
+  cudaFree(db->d_chunk_off); cudaFree(db->d_chunk_cols); cudaFree(db->d_scores); cudaFree(db->d_raw);
+  cudaFree(db->d_rescore_list); cudaFree(db->d_counters); cudaFree(db->d_bnd1); cudaFree(db->d_bnd3);
+  cudaFree(db->d_query); cudaFree(db->d_table); cudaFree(db->d_prof);
+  for (auto& e : db->ev) if (e) cudaEventDestroy(e);
+  if (db->s_main) cudaStreamDestroy(db->s_main);
+  if (db->s_aux) cudaStreamDestroy(db->s_aux);
+  delete db;
+}
+
+int swgpu_db_create(swgpu_db_t** out, int device, const int8_t* codes, const int64_t* offsets,
+                    int64_t n_targets, int64_t entry_base, const swgpu_pack_opts_t* opts) {
+  if (!out || n_targets < 0 || (n_targets > 0 && (!codes || !offsets))) return fail(SWGPU_EINVAL, "swgpu_db_create: bad argument");
+  *out = nullptr;
+  int ndev = 0;
+  CU(cudaGetDeviceCount(&ndev));
+  if (ndev <= 0) return fail(SWGPU_ENODEV, "no CUDA device");
+  if (device < 0 || device >= ndev) return fail(SWGPU_EINVAL, "device %d out of range (%d devices)", device, ndev);
+  CU(cudaSetDevice(device));
+
+  const int long_thr = (opts && opts->long_threshold > 0) ? opts->long_threshold : kDefaultLongThreshold;
+  swpack_t pk;
+  static const int64_t zero_off[1] = {0};
+  if (swpack_build(&pk, codes, n_targets ? offsets : zero_off, n_targets, long_thr) != 0)
+    return fail(SWGPU_EINVAL, "database packing failed (residue code outside 0..31, negative length, or out of memory)");
+
+  swgpu_db* db = new swgpu_db();
+  db->device = device;
+  db->n = pk.n_targets; db->n_residues = pk.n_residues; db->n_long = pk.n_long; db->n_chunks = pk.n_chunks;
+  db->max_len = pk.max_len; db->max_chunk_cols = pk.max_chunk_cols; db->entry_base = entry_base;
+  db->h_order.assign(pk.order, pk.order + pk.n_targets);
+  db->h_len_sorted_prefix.assign(pk.plain_off, pk.plain_off + pk.n_targets + 1);
+
+  int rc = SWGPU_OK;
+  auto body = [&]() -> int {
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, device));
+    db->sm_count = prop.multiProcessorCount;
+    CU(cudaStreamCreateWithFlags(&db->s_main, cudaStreamNonBlocking));
+    CU(cudaStreamCreateWithFlags(&db->s_aux, cudaStreamNonBlocking));
+    for (auto& e : db->ev) CU(cudaEventCreate(&e));
+    int r;
+    if ((r = dalloc(db, &db->d_plain, (size_t)pk.n_residues))) return r;
+    if ((r = dalloc(db, &db->d_plain_off, (size_t)pk.n_targets + 1))) return r;
+    if ((r = dalloc(db, &db->d_order, (size_t)pk.n_targets))) return r;
+    if ((r = dalloc(db, &db->d_cols, (size_t)pk.cols_words))) return r;
+    if ((r = dalloc(db, &db->d_chunk_off, (size_t)pk.n_chunks + 1))) return r;
+    if ((r = dalloc(db, &db->d_chunk_cols, (size_t)pk.n_chunks))) return r;
+    if ((r = dalloc(db, &db->d_scores, (size_t)pk.n_targets))) return r;
+    if ((r = dalloc(db, &db->d_raw, (size_t)pk.n_chunks * 32))) return r;
+    if ((r = dalloc(db, &db->d_rescore_list, (size_t)pk.n_targets))) return r;
+    if ((r = dalloc(db, &db->d_counters, 8))) return r;
+    if ((r = dalloc(db, &db->d_table, 1024))) return r;
+    CU(cudaMemcpy(db->d_plain, pk.plain, (size_t)pk.n_residues, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(db->d_plain_off, pk.plain_off, sizeof(int64_t) * ((size_t)pk.n_targets + 1), cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(db->d_order, pk.order, sizeof(int64_t) * (size_t)pk.n_targets, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(db->d_cols, pk.cols, sizeof(uint64_t) * (size_t)pk.cols_words, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(db->d_chunk_off, pk.chunk_off, sizeof(int64_t) * ((size_t)pk.n_chunks + 1), cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(db->d_chunk_cols, pk.chunk_cols, sizeof(int32_t) * (size_t)pk.n_chunks, cudaMemcpyHostToDevice));
+
+    // persistent grids: K1 two CTAs of 8 warps per SM; K3 eight CTAs of 4 warps per SM at most
+    db->k1_grid = (int)std::min<int64_t>((int64_t)db->sm_count * 2, (pk.n_chunks + swk::K1_WARPS - 1) / swk::K1_WARPS);
+    db->k1_grid = std::max(db->k1_grid, 1);
+    db->bnd1_stride = (long long)std::max<int32_t>(pk.max_chunk_cols, 4) * 32;
+    if ((r = dalloc(db, &db->d_bnd1, (size_t)db->k1_grid * swk::K1_WARPS * (size_t)db->bnd1_stride))) return r;
+    db->k3_grid = db->sm_count * 4;
+    db->bnd3_stride = std::max<int32_t>(pk.max_len, 32);
+    if ((r = dalloc(db, &db->d_bnd3, (size_t)db->k3_grid * swk::K3_WARPS * (size_t)db->bnd3_stride))) return r;
+    return SWGPU_OK;
+  };
+  rc = body();
+  swpack_free(&pk);
+  if (rc != SWGPU_OK) { swgpu_db_destroy(db); return rc; }
+  *out = db;
+  return SWGPU_OK;
+}
+
+int64_t swgpu_db_num_targets(const swgpu_db_t* db) { return db ? db->n : 0; }
+int64_t swgpu_db_num_residues(const swgpu_db_t* db) { return db ? db->n_residues : 0; }
+int64_t swgpu_db_device_bytes(const swgpu_db_t* db) { return db ? db->device_bytes : 0; }
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------------------------
+// search
+// ------------------------------------------------------------------------------------------
+namespace {
+
+template <int R>
+int launch_k1(swgpu_db* db, const swk::K1Params& P) {
+  const size_t smem = (size_t)swk::K1_WARPS * swk::Tile<R>::WORDS * sizeof(unsigned);
+  swk::k1_inter<R><<<db->k1_grid, swk::K1_WARPS * 32, smem, db->s_main>>>(P);
+  CU(cudaGetLastError());
+  return SWGPU_OK;
+}
+
+int launch_k3(swgpu_db* db, cudaStream_t st, const swk::K3Params& P, int lq) {
+  if (lq <= 128) swk::k3_intra<4><<<db->k3_grid, swk::K3_WARPS * 32, 0, st>>>(P);
+  else           swk::k3_intra<8><<<db->k3_grid, swk::K3_WARPS * 32, 0, st>>>(P);
+  CU(cudaGetLastError());
+  return SWGPU_OK;
+}
+
+int pick_tile_rows(int64_t lq) {
+  int best_r = kTileChoices[0]; int64_t best_pad = -1;
+  for (int r : kTileChoices) {
+    const int64_t padded = (lq + r - 1) / r * r;
+    if (best_pad < 0 || padded < best_pad) { best_pad = padded; best_r = r; }
+  }
+  return best_r;
+}
+
+int run_search(swgpu_db* db, const int8_t* query, int64_t lq, const int8_t* table, int gap_open, int gap_extend,
+               swgpu_stats_t* stats) {
+  if (!db) return fail(SWGPU_EINVAL, "null database handle");
+  if (lq < 0 || (lq > 0 && !query) || !table) return fail(SWGPU_EINVAL, "bad query/table argument");
+  if (lq > 0x7fffffff) return fail(SWGPU_EINVAL, "query too long");
+  const int oe = gap_open + gap_extend, ge = gap_extend;
+  if (oe > 0 || ge > 0 || gap_open > 0)
+    return fail(SWGPU_EINVAL, "positive gap scores are outside the supported (and the reference-equivalent) range");
+  if (oe < -100000 || ge < -100000) return fail(SWGPU_EINVAL, "gap penalty out of range");
+  for (int64_t i = 0; i < lq; ++i) if (query[i] < 0 || query[i] > 31) return fail(SWGPU_EINVAL, "query code outside 0..31");
+  CU(cudaSetDevice(db->device));
+  swgpu_stats_t st; memset(&st, 0, sizeof(st));
+  db->have_scores = false;
+
+  // ---- uploads (query, table) ----
+  if (lq > db->query_cap) {
+    if (db->d_query) { cudaFree(db->d_query); db->d_query = nullptr; }
+    db->query_cap = std::max<int64_t>(lq, 1024);
+    CU(cudaMalloc((void**)&db->d_query, (size_t)db->query_cap));
+  }
+  cudaEvent_t *e = db->ev;
+  CU(cudaEventRecord(e[6], db->s_main));
+  if (lq > 0) CU(cudaMemcpyAsync(db->d_query, query, (size_t)lq, cudaMemcpyHostToDevice, db->s_main));
+  CU(cudaMemcpyAsync(db->d_table, table, 1024, cudaMemcpyHostToDevice, db->s_main));
+  CU(cudaEventRecord(e[7], db->s_main));
+
+  const unsigned B = 128u + (unsigned)(-oe) + (unsigned)(-ge);
+  const bool use16 = (B <= 16384u) && db->n_chunks > 0 && lq > 0;
+  const int R = pick_tile_rows(lq);
+  const int ntiles = lq > 0 ? (int)((lq + R - 1) / R) : 0;
+  st.tile_rows = use16 ? R : 0;
+  if (use16) {
+    const size_t need = (size_t)ntiles * 32 * (((R / 4) | 1) + ((R / 2) | 1));
+    if (need > db->prof_cap) {
+      if (db->d_prof) { cudaFree(db->d_prof); db->d_prof = nullptr; }
+      db->prof_cap = need + need / 2;
+      CU(cudaMalloc((void**)&db->d_prof, db->prof_cap * sizeof(unsigned)));
+    }
+  }
+
+  // ---- timed region: first kernel -> last result resident ----
+  CU(cudaEventRecord(e[0], db->s_main));
+  CU(cudaMemsetAsync(db->d_counters, 0, 8 * sizeof(unsigned), db->s_main));
+  if (lq == 0 || db->n == 0) {
+    if (db->n) CU(cudaMemsetAsync(db->d_scores, 0, sizeof(int32_t) * (size_t)db->n, db->s_main));
+    CU(cudaEventRecord(e[1], db->s_main));
+    CU(cudaEventRecord(e[2], db->s_main));
+  } else {
+    swk::K3Params P3; memset(&P3, 0, sizeof(P3));
+    P3.plain = db->d_plain; P3.plain_off = db->d_plain_off; P3.query = db->d_query; P3.lq = (int)lq;
+    P3.table = db->d_table; P3.oe = oe; P3.ge = ge; P3.bnd = db->d_bnd3; P3.bnd_stride = db->bnd3_stride;
+    P3.order = db->d_order; P3.scores_file = db->d_scores; P3.one = 1u;
+    if (use16) {
+      // long targets on the aux stream, concurrently with K1
+      CU(cudaEventRecord(e[3], db->s_main));
+      if (db->n_long > 0) {
+        CU(cudaStreamWaitEvent(db->s_aux, e[3], 0));
+        swk::K3Params PL = P3; PL.worklist = nullptr; PL.n_work = (int)db->n_long; PL.counter = db->d_counters + 1;
+        int r = launch_k3(db, db->s_aux, PL, (int)lq); if (r) return r;
+        st.kernel_launches++;
+        CU(cudaEventRecord(e[4], db->s_aux));
+      }
+      swk::build_profile<<<std::min(1024, (ntiles * 26 * 32 + 255) / 256 + 1), 256, 0, db->s_main>>>(
+          db->d_query, (int)lq, db->d_table, R, (R / 4) | 1, (R / 2) | 1, ntiles, db->d_prof);
+      CU(cudaGetLastError()); st.kernel_launches++;
+      swk::K1Params P1; memset(&P1, 0, sizeof(P1));
+      P1.cols = db->d_cols; P1.chunk_off = db->d_chunk_off; P1.chunk_cols = db->d_chunk_cols; P1.n_chunks = (int)db->n_chunks;
+      P1.prof = db->d_prof; P1.ntiles = ntiles; P1.bnd = db->d_bnd1; P1.bnd_stride = db->bnd1_stride;
+      P1.counter = db->d_counters + 0; P1.raw_out = db->d_raw;
+      P1.BB = B | (B << 16); P1.OE32 = (unsigned)(oe * 65537); P1.GE2 = ((unsigned)ge & 0xffffu) * 0x10001u; P1.one = 1u;
+      int r = SWGPU_OK;
+      switch (R) {
+        case 32: r = launch_k1<32>(db, P1); break;
+        case 28: r = launch_k1<28>(db, P1); break;
+        case 24: r = launch_k1<24>(db, P1); break;
+        case 20: r = launch_k1<20>(db, P1); break;
+        default: r = launch_k1<16>(db, P1); break;
+      }
+      if (r) return r;
+      st.kernel_launches++;
+      const long n_lanes = (long)db->n_chunks * 32;
+      swk::k1_finalize<<<(int)std::min<long>((n_lanes + 255) / 256, 2048), 256, 0, db->s_main>>>(
+          db->d_raw, n_lanes, (long)db->n_long, (long)db->n, B, 65535u - 129u, db->d_order, db->d_scores,
+          db->d_rescore_list, db->d_counters + 2);
+      CU(cudaGetLastError()); st.kernel_launches++;
+      CU(cudaEventRecord(e[1], db->s_main));
+      // 32-bit rescoring of saturated targets (count lives on the device)
+      swk::K3Params PR = P3; PR.worklist = db->d_rescore_list; PR.work_count = db->d_counters + 2; PR.counter = db->d_counters + 3;
+      r = launch_k3(db, db->s_main, PR, (int)lq); if (r) return r;
+      st.kernel_launches++;
+      if (db->n_long > 0) CU(cudaStreamWaitEvent(db->s_main, e[4], 0));
+      CU(cudaEventRecord(e[2], db->s_main));
+    } else {
+      swk::K3Params PA = P3; PA.worklist = nullptr; PA.n_work = (int)db->n; PA.counter = db->d_counters + 1;
+      int r = launch_k3(db, db->s_main, PA, (int)lq); if (r) return r;
+      st.kernel_launches++;
+      CU(cudaEventRecord(e[1], db->s_main));
+      CU(cudaEventRecord(e[2], db->s_main));
+    }
+  }
+  CU(cudaStreamSynchronize(db->s_main));
+  CU(cudaStreamSynchronize(db->s_aux));
+  db->have_scores = true;
+  db->last_lq = lq;
+
+  float ms = 0;
+  CU(cudaEventElapsedTime(&ms, e[0], e[2])); st.ms_total = ms;
+  CU(cudaEventElapsedTime(&ms, e[6], e[7])); st.ms_h2d = ms;
+  st.cells = lq * db->n_residues;
+  if (lq > 0 && db->n > 0) {
+    if (use16) {
+      CU(cudaEventElapsedTime(&ms, e[0], e[1])); st.ms_inter = ms;
+      CU(cudaEventElapsedTime(&ms, e[1], e[2])); st.ms_rescore = ms;
+      if (db->n_long > 0) { CU(cudaEventElapsedTime(&ms, e[3], e[4])); st.ms_intra = ms; }
+      st.n_long = db->n_long;
+      st.cells_intra = lq * db->h_len_sorted_prefix[db->n_long];
+      st.cells_inter = st.cells - st.cells_intra;
+      unsigned nres = 0;
+      CU(cudaMemcpy(&nres, db->d_counters + 2, sizeof(unsigned), cudaMemcpyDeviceToHost));
+      st.n_rescored = nres;
+      if (nres) {
+        std::vector<int> lst(nres);
+        CU(cudaMemcpy(lst.data(), db->d_rescore_list, sizeof(int) * nres, cudaMemcpyDeviceToHost));
+        int64_t res = 0;
+        for (int s : lst) res += db->h_len_sorted_prefix[s + 1] - db->h_len_sorted_prefix[s];
+        st.cells_rescore = lq * res;
+      }
+    } else {
+      st.ms_intra = st.ms_total; st.n_long = db->n; st.cells_intra = st.cells;
+    }
+  }
+  if (stats) *stats = st;
+  return SWGPU_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int swgpu_search_resident(swgpu_db_t* db, const int8_t* query, int64_t query_len, const int8_t* table,
+                          int gap_open, int gap_extend, swgpu_stats_t* stats) {
+  return run_search(db, query, query_len, table, gap_open, gap_extend, stats);
+}
+
+int swgpu_db_scores_d2h(swgpu_db_t* db, int32_t* scores) {
+  if (!db || !scores) return fail(SWGPU_EINVAL, "bad argument");
+  if (!db->have_scores) return fail(SWGPU_EINVAL, "no search result resident");
+  CU(cudaSetDevice(db->device));
+  if (db->n) CU(cudaMemcpy(scores, db->d_scores, sizeof(int32_t) * (size_t)db->n, cudaMemcpyDeviceToHost));
+  return SWGPU_OK;
+}
+
+int swgpu_search(swgpu_db_t* db, const int8_t* query, int64_t query_len, const int8_t* table,
+                 int gap_open, int gap_extend, int32_t* scores, swgpu_stats_t* stats) {
+  if (!scores && db && db->n) return fail(SWGPU_EINVAL, "null scores buffer");
+  swgpu_stats_t st;
+  int r = run_search(db, query, query_len, table, gap_open, gap_extend, &st);
+  if (r) return r;
+  CU(cudaEventRecord(db->ev[6], db->s_main));
+  if (db->n) CU(cudaMemcpyAsync(scores, db->d_scores, sizeof(int32_t) * (size_t)db->n, cudaMemcpyDeviceToHost, db->s_main));
+  CU(cudaEventRecord(db->ev[7], db->s_main));
+  CU(cudaStreamSynchronize(db->s_main));
+  float ms = 0; CU(cudaEventElapsedTime(&ms, db->ev[6], db->ev[7])); st.ms_d2h = ms;
+  if (stats) *stats = st;
+  return SWGPU_OK;
+}
+
+int swgpu_fill_batch16(int device, const int8_t* query, int64_t query_len, const int8_t* batch, int64_t padded_len,
+                       int lanes, const int8_t* table, int gap_open, int gap_extend, int32_t* scores16) {
+  if (lanes < 1 || lanes > 16 || padded_len < 0 || !batch || !scores16) return fail(SWGPU_EINVAL, "bad batch argument");
+  // The reference scores the '*' padding rows too (alignment.c:88 runs to the padded length),
+  // so every lane is handed over at its full padded length.
+  std::vector<int8_t> codes((size_t)lanes * (size_t)padded_len);
+  std::vector<int64_t> off(lanes + 1);
+  for (int l = 0; l < lanes; ++l) {
+    off[l] = (int64_t)l * padded_len;
+    for (int64_t j = 0; j < padded_len; ++j) codes[(size_t)off[l] + j] = batch[j * 16 + l];
+  }
+  off[lanes] = (int64_t)lanes * padded_len;
+  swgpu_db_t* db = nullptr;
+  int r = swgpu_db_create(&db, device, codes.data(), off.data(), lanes, 0, nullptr);
+  if (r) return r;
+  r = swgpu_search(db, query, query_len, table, gap_open, gap_extend, scores16, nullptr);
+  swgpu_db_destroy(db);
+  return r;
+}
+
+}  // extern "C"
+
+// top-k + coordinates live in swgpu_topk.cu

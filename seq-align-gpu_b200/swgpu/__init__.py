@@ -1,0 +1,156 @@
+"""swgpu -- ctypes binding of libswgpu.so (the C-ABI in include/swgpu.h).
+
+Python is only the test / bench harness language here; the product is the C-ABI
+library and the C host layer.  The binding refuses to work without the compiled
+CUDA library: there is no CPU fallback.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from dataclasses import dataclass
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(os.path.dirname(_HERE), "libswgpu.so")
+
+
+class SwgpuError(RuntimeError):
+    pass
+
+
+class Stats(C.Structure):
+    _fields_ = [
+        ("ms_total", C.c_double), ("ms_inter", C.c_double), ("ms_intra", C.c_double),
+        ("ms_rescore", C.c_double), ("ms_h2d", C.c_double), ("ms_d2h", C.c_double),
+        ("cells", C.c_int64), ("cells_inter", C.c_int64), ("cells_intra", C.c_int64),
+        ("cells_rescore", C.c_int64), ("n_rescored", C.c_int64), ("n_long", C.c_int64),
+        ("kernel_launches", C.c_int32), ("tile_rows", C.c_int32),
+    ]
+
+    def as_dict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+class Hit(C.Structure):
+    _fields_ = [("score", C.c_int32), ("q_start", C.c_int32), ("q_end", C.c_int32),
+                ("t_start", C.c_int32), ("t_end", C.c_int32), ("entry", C.c_int64)]
+
+
+class PackOpts(C.Structure):
+    _fields_ = [("long_threshold", C.c_int32), ("reserved", C.c_int32 * 7)]
+
+
+_lib = None
+
+
+def lib():
+    """Load libswgpu.so; raise loudly if the CUDA extension was not built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise SwgpuError(f"{LIB_PATH} missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                         "(there is no CPU fallback)")
+    L = C.CDLL(LIB_PATH)
+    P = C.POINTER
+    L.swgpu_device_count.restype = C.c_int
+    L.swgpu_last_error.restype = C.c_char_p
+    L.swgpu_version.restype = C.c_char_p
+    L.swgpu_db_create.restype = C.c_int
+    L.swgpu_db_create.argtypes = [P(C.c_void_p), C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p]
+    L.swgpu_db_destroy.argtypes = [C.c_void_p]
+    L.swgpu_db_destroy.restype = None
+    for f in ("swgpu_db_num_targets", "swgpu_db_num_residues", "swgpu_db_device_bytes"):
+        getattr(L, f).restype = C.c_int64
+        getattr(L, f).argtypes = [C.c_void_p]
+    L.swgpu_search.restype = C.c_int
+    L.swgpu_search.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int, C.c_int, C.c_void_p, P(Stats)]
+    L.swgpu_search_resident.restype = C.c_int
+    L.swgpu_search_resident.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int, C.c_int, P(Stats)]
+    L.swgpu_db_scores_d2h.restype = C.c_int
+    L.swgpu_db_scores_d2h.argtypes = [C.c_void_p, C.c_void_p]
+    L.swgpu_topk.restype = C.c_int
+    L.swgpu_topk.argtypes = [C.c_void_p, C.c_int, P(Hit), P(C.c_int)]
+    L.swgpu_fill_batch16.restype = C.c_int
+    L.swgpu_fill_batch16.argtypes = [C.c_int, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_int,
+                                     C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+    _lib = L
+    return L
+
+
+def _check(rc):
+    if rc != 0:
+        raise SwgpuError(f"swgpu error {rc}: {lib().swgpu_last_error().decode()}")
+
+
+def _i8(a):
+    a = np.ascontiguousarray(a, dtype=np.int8)
+    return a, a.ctypes.data_as(C.c_void_p)
+
+
+class Database:
+    """Packed, HBM-resident database on one GPU (swgpu_db_t)."""
+
+    def __init__(self, codes, offsets, device=0, entry_base=0, long_threshold=0):
+        L = lib()
+        self._codes, pc = _i8(codes)
+        self._off = np.ascontiguousarray(offsets, dtype=np.int64)
+        self.n = len(self._off) - 1
+        h = C.c_void_p()
+        opts = PackOpts(long_threshold=long_threshold)
+        _check(L.swgpu_db_create(C.byref(h), device, pc, self._off.ctypes.data_as(C.c_void_p), self.n, entry_base,
+                                 C.byref(opts)))
+        self._h = h
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().swgpu_db_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    @property
+    def device_bytes(self):
+        return lib().swgpu_db_device_bytes(self._h)
+
+    def search(self, query, table, gap_open, gap_extend, out=None):
+        """Host API: H2D query/table, kernels, D2H scores (file order). Returns (scores int32[n], stats dict)."""
+        q, pq = _i8(query)
+        t, pt = _i8(np.asarray(table).reshape(-1))
+        assert t.size == 1024
+        scores = out if out is not None else np.empty(self.n, dtype=np.int32)
+        st = Stats()
+        _check(lib().swgpu_search(self._h, pq, q.size, pt, int(gap_open), int(gap_extend),
+                                  scores.ctypes.data_as(C.c_void_p), C.byref(st)))
+        return scores, st.as_dict()
+
+    def search_resident(self, query, table, gap_open, gap_extend):
+        q, pq = _i8(query)
+        t, pt = _i8(np.asarray(table).reshape(-1))
+        st = Stats()
+        _check(lib().swgpu_search_resident(self._h, pq, q.size, pt, int(gap_open), int(gap_extend), C.byref(st)))
+        return st.as_dict()
+
+    def scores(self):
+        s = np.empty(self.n, dtype=np.int32)
+        _check(lib().swgpu_db_scores_d2h(self._h, s.ctypes.data_as(C.c_void_p)))
+        return s
+
+    def topk(self, k):
+        hits = (Hit * k)()
+        n = C.c_int(0)
+        _check(lib().swgpu_topk(self._h, k, hits, C.byref(n)))
+        return [dict(score=h.score, q_start=h.q_start, q_end=h.q_end, t_start=h.t_start, t_end=h.t_end, entry=h.entry)
+                for h in hits[: n.value]]
+
+
+def fill_batch16(query, batch_interleaved, padded_len, lanes, table, gap_open, gap_extend, device=0):
+    q, pq = _i8(query)
+    b, pb = _i8(batch_interleaved)
+    t, pt = _i8(np.asarray(table).reshape(-1))
+    out = np.zeros(16, dtype=np.int32)
+    _check(lib().swgpu_fill_batch16(device, pq, q.size, pb, padded_len, lanes, pt, gap_open, gap_extend,
+                                    out.ctypes.data_as(C.c_void_p)))
+    return out[:lanes]

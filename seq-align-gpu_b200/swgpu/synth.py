@@ -1,0 +1,90 @@
+"""Synthetic inputs of SURVEY.md 8(d): residues i.i.d. from Swiss-Prot background frequencies over
+the 20 standard letters, log-normal lengths, Philox counter-based PRNG (seeded, reproducible)."""
+from __future__ import annotations
+
+import numpy as np
+
+LETTERS = "ARNDCQEGHILKMFPSTWYV"
+# Swiss-Prot amino-acid composition (percent), release-independent to the digit shown
+FREQ = np.array([8.25, 5.53, 4.06, 5.45, 1.37, 3.93, 6.75, 7.07, 2.27, 5.96,
+                 9.66, 5.84, 2.42, 3.86, 4.70, 6.56, 5.34, 1.08, 2.92, 6.87])
+FREQ = FREQ / FREQ.sum()
+CODES = np.array([ord(c) - 64 for c in LETTERS], dtype=np.int8)   # letters_to_index: A=1 .. Z=26
+C2_QUERY_LENGTHS = [144, 189, 222, 375, 464, 567, 657, 729, 850, 1000, 1500, 2005, 2504, 3005, 3564, 4061,
+                    4548, 4743, 5147, 5478]
+
+
+def rng(seed):
+    return np.random.Generator(np.random.Philox(seed))
+
+
+def residues(g, n, freq=FREQ, codes=CODES):
+    return codes[g.choice(len(codes), size=int(n), p=freq)]
+
+
+def lognormal_lengths(g, n, median=290.0, sigma=0.68, lo=20, hi=35000):
+    return np.clip(np.floor(g.lognormal(np.log(median), sigma, size=n)), lo, hi).astype(np.int64)
+
+
+def make_db(seed, n, median=290.0, sigma=0.68, lo=20, hi=35000, total=None, force_max=None, sort=True):
+    """Returns (codes int8[sum], offsets int64[n+1]); sorted longest first like the reference demands."""
+    g = rng(seed)
+    lens = lognormal_lengths(g, n, median, sigma, lo, hi)
+    if total is not None:                      # rescale to a residue budget (C2: ~205 M)
+        lens = np.clip(np.floor(lens * (total / lens.sum())), lo, hi).astype(np.int64)
+    if force_max is not None:
+        lens[0] = force_max
+    if sort:
+        lens = np.sort(lens)[::-1].copy()
+    off = np.zeros(n + 1, dtype=np.int64)
+    np.cumsum(lens, out=off[1:])
+    return residues(g, off[-1]), off
+
+
+def make_query(seed, length):
+    return residues(rng(seed), length)
+
+
+def config1():
+    """C1: 360-aa query x 10 000 proteins, seed 42."""
+    codes, off = make_db(42, 10000)
+    return make_query(1042, 360), codes, off
+
+
+def config2(n=570000, total=205_000_000):
+    """C2: Swiss-Prot-shaped DB, seed 43 (one target forced to 35 213)."""
+    return make_db(43, n, lo=2, hi=35213, total=total, force_max=35213)
+
+
+def to_fasta(path, codes, off, prefix="sp"):
+    letters = np.frombuffer(b"?ABCDEFGHIJKLMNOPQRSTUVWXYZ????*", dtype=np.uint8)
+    txt = letters[np.asarray(codes, dtype=np.int64)]
+    with open(path, "wb") as f:
+        for i in range(len(off) - 1):
+            f.write(b">%s|%07d len=%d\n" % (prefix.encode(), i, off[i + 1] - off[i]))
+            f.write(txt[off[i]:off[i + 1]].tobytes())
+            f.write(b"\n")
+
+
+def load_matrix(path):
+    """Whitespace-separated matrix file -> (int8[32,32] table, defined_diag uint8[32]); mirrors
+    src/alignment_scoring_load.c:98-151 + scoring_add_mutation (zero-initialised table)."""
+    tab = np.zeros((32, 32), dtype=np.int8)
+    cols = None
+    def idx(ch):
+        if ch == "*":
+            return 31
+        return ord(ch.upper()) - 64
+    with open(path) as f:
+        for line in f:
+            if line.startswith("#") or not line.strip():
+                continue
+            if cols is None:
+                cols = [idx(c) for c in line.split()]
+                continue
+            parts = line.split()
+            r = idx(parts[0])
+            for c, v in zip(cols, parts[1:]):
+                tab[r, c] = int(v)
+    diag = np.array([1 if (i in cols) else 0 for i in range(32)], dtype=np.uint8)
+    return tab, diag
