@@ -1,0 +1,330 @@
+#!/usr/bin/env python
+"""bench.py -- GCUPS of the one-to-many Smith-Waterman scoring path (BASELINE.json metric).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--scale F]
+  torchrun --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...        (N > 1: one rank per GPU, NCCL)
+
+Workload (config 2 of BASELINE.json, SURVEY.md 8(d) "C2"): a Swiss-Prot-shaped synthetic database
+(570 000 sequences, ~205 M residues, log-normal lengths, one 35 213-aa target; seed 43 + rank), BLOSUM62,
+gap open 10 / extend 1, and the classic 20-query length sweep 144..5478 aa.  One "step" = the whole sweep
+over the HBM-resident database = 41 752 x n_residues cell updates per GPU.  N > 1 is weak scaling: every
+rank holds its own 205 M-residue shard (the database shards by residue count, no data-path collective);
+after each step the per-rank top-k lists are merged with one small NCCL all_gather.
+
+value  = GCUPS, device-timed (CUDA events on the engine's stream: first kernel launch -> last result
+         resident in HBM), real unpadded cells of all ranks / max-over-ranks time.
+e2e    = same metric through the host-facing C-ABI call swgpu_search(): query + table in host memory,
+         H2D inside, kernels, D2H of all per-entry scores into host memory, host wall clock.
+roofline = dominant kernel (K1, packed 16-bit inter-sequence) against the measured integer-ALU-pipe
+         cell-update roofline (DESIGN.md "Roofline"); the HBM view is reported beside it.
+cpu_baseline = the reference's own AVX2/OpenMP kernel (oracle/_ref/libalign_ref.so, the unmodified
+         reference sources) on the box's host cores, on a bounded sample of the same workload.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "seq-align-gpu_b200"))
+
+GAP_OPEN, GAP_EXTEND = -10, -1
+N_TARGETS, N_RESIDUES = 570_000, 205_000_000
+TOPK = 100
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return float(d.get("hbm_gbs", 6650.0)), float(d.get("sm_max_mhz", 1965.0)), "measured"
+    return 6650.0, 1965.0, "fallback"
+
+
+def int_pipe_peak():
+    """Measured ALU-pipe rate (warp-instructions / clk / SM for VIMNMX/VIADDMNMX.16x2), written by
+    bench_micro/ubench_int on a B200 of this pool and committed as profiles/int_pipe_peak.json."""
+    p = os.path.join(ROOT, "profiles", "int_pipe_peak.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return float(d["alu_winst_per_clk_sm"]), "measured (profiles/int_pipe_peak.json)"
+    return 2.0, "nominal 64 lanes/clk/SM (no microbenchmark file)"
+
+
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.index)], stdout=subprocess.PIPE, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), line))
+
+    def stop(self, t0, t1):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, pw, reasons = [], 0.0, [], set()
+        for ts, line in self.rows:
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 8 or not (t0 - 0.05 <= ts <= t1 + 0.15):
+                continue
+            try:
+                sm.append(float(f[1])); mx = max(mx, float(f[2])); pw.append(float(f[3]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx or None,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def make_workload(rank, scale):
+    from swgpu import synth
+    n = max(64, int(N_TARGETS * scale))
+    total = int(N_RESIDUES * scale)
+    codes, off = synth.make_db(43 + rank, n, lo=2, hi=35213, total=total, force_max=35213 if scale >= 0.01 else None)
+    queries = [synth.make_query(100 + i, L) for i, L in enumerate(synth.C2_QUERY_LENGTHS)]
+    tab, _ = synth.load_matrix(os.path.join(ROOT, "scoring", "BLOSUM62.txt"))
+    return codes, off, queries, tab
+
+
+def cpu_sample(codes, off, stride):
+    """Every stride-th target of the length-sorted database, padded up to a multiple of 16 targets
+    (the reference needs N % 16 == 0 and a length-sorted input)."""
+    idx = np.arange(0, len(off) - 1, stride)
+    idx = idx[: max(16, len(idx) // 16 * 16)]
+    lens = (off[1:] - off[:-1])[idx]
+    o = np.zeros(len(idx) + 1, dtype=np.int64); np.cumsum(lens, out=o[1:])
+    c = np.concatenate([codes[off[i]:off[i + 1]] for i in idx]) if len(idx) else np.zeros(0, np.int8)
+    return c, o
+
+
+def run_cpu_reference(codes, off, queries, tab, budget_s, qsel=(0, 3, 9)):
+    """Times the reference's own kernel (unmodified sources, oracle/_ref) -- or, if that library did not
+    travel, the C restatement -- with all host threads on a bounded sample.  Returns dict."""
+    from oracle import oracle as O
+    use_ref = O.have_ref()
+    threads = O.ref().refh_max_threads() if use_ref else O.oracle().swo_max_threads()
+    qs = [queries[i] for i in qsel]
+
+    def once(c, o):
+        secs, cells = 0.0, 0
+        for q in qs:
+            if use_ref:
+                _, s = O.ref_search16(q, c, o, tab, GAP_OPEN, GAP_EXTEND, threads=threads)
+            else:
+                t0 = time.perf_counter(); O.search32(q, c, o, tab, GAP_OPEN, GAP_EXTEND, threads=threads); s = time.perf_counter() - t0
+            secs += s; cells += len(q) * int(o[-1])
+        return secs, cells
+
+    stride = 512
+    c, o = cpu_sample(codes, off, stride)
+    s, cells = once(c, o)                                  # calibration (also warms the thread pool)
+    rate = cells / max(s, 1e-6)
+    want_cells = rate * budget_s
+    full = sum(len(q) for q in qs) * int(off[-1])
+    stride = int(max(1, min(512, round(full / max(want_cells, 1)))))
+    c, o = cpu_sample(codes, off, stride)
+    s, cells = once(c, o)
+    return {"value": cells / s / 1e9, "unit": "GCUPS", "cores": int(threads), "kind": "reference" if use_ref else "port",
+            "seconds": s,
+            "sample": f"every {stride}-th target of the length-sorted C2 database ({len(o) - 1} targets, {int(o[-1])} residues) "
+                      f"x queries of {', '.join(str(len(q)) for q in qs)} aa; timer = the reference's own region "
+                      f"(omp parallel for over alignment_fill_matrices)"}, (c, o, qs)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--scale", type=float, default=1.0, help="database size as a fraction of C2 (dev only; 1.0 = the benchmark)")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0)
+    ap.add_argument("--no-cpu", action="store_true")
+    a = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    config = {"workload": "C2: Swiss-Prot-shaped synthetic DB (570k seqs, ~205M residues per GPU), BLOSUM62, gap open 10 / extend 1, "
+                          "20-query sweep 144..5478 aa; one step = the whole sweep",
+              "targets_per_gpu": int(N_TARGETS * a.scale), "queries": 20, "topk": TOPK,
+              "cache": "database + scratch per GPU (>=0.6 GB) exceed L2 (126 MB); every query pass streams the whole DB",
+              "sharding": "one 205M-residue shard per rank, no data-path collective; NCCL all_gather of per-rank top-k"}
+
+    if a.impl == "reference":
+        if rank != 0:
+            return 0
+        codes, off, queries, tab = make_workload(0, a.scale)
+        # each step is a bounded sample sized so steps+warmup finish within a few minutes
+        per_step = max(2.0, min(a.cpu_seconds, 150.0 / max(a.steps + a.warmup, 1)))
+        vals, info = [], None
+        for i in range(a.warmup + a.steps):
+            info, _ = run_cpu_reference(codes, off, queries, tab, per_step)
+            if i >= a.warmup:
+                vals.append(info)
+        cells = sum(v["value"] * v["seconds"] for v in vals); secs = sum(v["seconds"] for v in vals)
+        v = cells / secs
+        line = {"metric": "GCUPS", "value": v, "unit": "GCUPS", "impl": "reference", "n_gpus": a.gpus, "steps": a.steps,
+                "warmup": a.warmup, "ms_per_step": 1e3 * secs / max(a.steps, 1), "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "int16", "data": "synthetic", "config": config,
+                "cpu_baseline": {k: info[k] for k in ("kind", "cores", "sample")} | {"value": v, "unit": "GCUPS"},
+                "e2e": {"value": v, "unit": "GCUPS", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
+        print(json.dumps(line)); return 0
+
+    # ---------------- our arm ----------------
+    import torch
+    import swgpu
+    if not torch.cuda.is_available() or swgpu.lib().swgpu_device_count() < 1:
+        raise SystemExit("bench.py: no CUDA device -- the engine has no CPU fallback")
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    hbm_peak, sm_max, peak_src = load_peaks()
+
+    t0 = time.time()
+    codes, off, queries, tab = make_workload(rank, a.scale)
+    t_gen = time.time() - t0
+    t0 = time.time()
+    db = swgpu.Database(codes, off, device=local, entry_base=rank * (len(off) - 1))
+    t_pack = time.time() - t0
+    n = len(off) - 1
+    n_res = int(off[-1])
+    cells_step = sum(len(q) for q in queries) * n_res
+    host_scores = np.empty(n, dtype=np.int32)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def merge_topk(hits_local):
+        """per-rank top-k -> NCCL all_gather -> deterministic merge (score desc, entry asc)."""
+        t = torch.tensor([[h["score"], h["entry"]] for h in hits_local] + [[-1, -1]] * (TOPK - len(hits_local)),
+                         dtype=torch.int64, device="cuda")
+        if dist is None:
+            return t
+        out = [torch.empty_like(t) for _ in range(world)]
+        dist.all_gather(out, t)
+        allh = torch.cat(out)
+        key = allh[:, 0] * (1 << 40) - allh[:, 1]
+        return allh[torch.argsort(key, descending=True)[:TOPK]]
+
+    def step_resident():
+        ms, launches, k1ms, k1cells, resc = 0.0, 0, 0.0, 0, 0
+        for q in queries:
+            st = db.search_resident(q, tab, GAP_OPEN, GAP_EXTEND)
+            hits = db.topk(TOPK)
+            merge_topk(hits)
+            ms += st["ms_total"] + db.last_topk_ms; launches += st["kernel_launches"] + db.last_topk_launches
+            k1ms += st["ms_inter"]; k1cells += st["cells_inter"]; resc += st["n_rescored"]
+        return ms, launches, k1ms, k1cells, resc
+
+    def step_e2e():
+        t = time.perf_counter()
+        for q in queries:
+            db.search(q, tab, GAP_OPEN, GAP_EXTEND, out=host_scores)
+        return time.perf_counter() - t
+
+    for _ in range(a.warmup):
+        step_resident()
+    barrier()
+    sampler = ClockSampler(local); sampler.start(); time.sleep(0.25)
+    tw0 = time.time()
+    dev_ms, launches, k1ms, k1cells, resc = 0.0, 0, 0.0, 0, 0
+    for _ in range(a.steps):
+        r = step_resident()
+        dev_ms += r[0]; launches += r[1]; k1ms += r[2]; k1cells += r[3]; resc += r[4]
+    barrier()
+    tw1 = time.time()
+    clocks = sampler.stop(tw0, tw1)
+
+    # e2e: host buffers in, host buffers out, wall clock
+    step_e2e()
+    barrier()
+    e2e_s = 0.0
+    for _ in range(a.steps):
+        e2e_s += step_e2e()
+    barrier()
+
+    if dist is not None:
+        v = torch.tensor([dev_ms, e2e_s, tw1 - tw0], dtype=torch.float64, device="cuda")
+        dist.all_reduce(v, op=dist.ReduceOp.MAX)
+        dev_ms_max, e2e_max, wall_max = (float(x) for x in v)
+        c = torch.tensor([cells_step], dtype=torch.float64, device="cuda"); dist.all_reduce(c)
+        cells_all = float(c)
+    else:
+        dev_ms_max, e2e_max, wall_max, cells_all = dev_ms, e2e_s, tw1 - tw0, float(cells_step)
+
+    cpu = None
+    if rank == 0 and world == 1 and not a.no_cpu:
+        cpu, _ = run_cpu_reference(codes, off, queries, tab, a.cpu_seconds)
+        cpu.pop("seconds", None)
+
+    if rank == 0:
+        gcups = cells_all * a.steps / (dev_ms_max * 1e-3) / 1e9
+        alu_rate, alu_src = int_pipe_peak()
+        sm_clk = (clocks.get("sm_mhz") or sm_max)
+        # K1 cell roofline: 4.5 ALU-pipe (max-type DPX) warp-instructions per 64 cells (a warp-wide pair column),
+        # i.e. 2.25 thread-instructions per cell, at the measured ALU-pipe rate and the max SM clock.
+        sms = torch.cuda.get_device_properties(local).multi_processor_count
+        peak_gcups = alu_rate * 32 * sms * sm_max * 1e6 / 2.25 / 1e9
+        k1_gcups = k1cells / (k1ms * 1e-3) / 1e9 if k1ms > 0 else 0.0
+        hbm_ach = (k1cells / max(sum(len(q) for q in queries), 1) * 20 / 1.0) if False else None
+        # algorithmic HBM bytes of K1 per step: 1 B per target residue per query pass + 4 B score per target per query
+        k1_bytes = a.steps * len(queries) * (n_res + 4 * n)
+        hbm_gbs = k1_bytes / (k1ms * 1e-3) / 1e9 if k1ms > 0 else 0.0
+        line = {
+            "metric": "GCUPS", "value": gcups, "unit": "GCUPS", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
+            "ms_per_step": dev_ms_max / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u16x2 (packed 16-bit, 32-bit rescoring of saturated targets)", "data": "synthetic", "config": config,
+            "clocks": clocks, "gpu_launches": launches,
+            "e2e": {"value": cells_all * a.steps / e2e_max / 1e9, "unit": "GCUPS",
+                    "h2d_bytes_per_step": int(sum(len(q) + 1024 for q in queries)),
+                    "d2h_bytes_per_step": int(len(queries) * 4 * n),
+                    "note": "swgpu_search(): host query/table in, all per-entry int32 scores out to host memory, host wall clock; "
+                            "database packed and HBM-resident (one-off cost in setup_s)"},
+            "roofline": {"bound": "int-alu", "kernel": "k1_inter", "achieved": k1_gcups, "peak": peak_gcups, "unit": "GCUPS",
+                         "frac": k1_gcups / peak_gcups if peak_gcups else None,
+                         "peak_how": f"{alu_rate:.3f} warp-inst/clk/SM {alu_src} x 32 lanes x {sms} SMs x {sm_max:.0f} MHz / 2.25 ALU-pipe "
+                                     f"thread-instructions per cell",
+                         "sm_mhz_seen": sm_clk, "k1_ms_per_step": k1ms / a.steps, "k1_share_of_step": k1ms / dev_ms if dev_ms else None,
+                         "traffic": None,
+                         "hbm": {"achieved": hbm_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": hbm_gbs / hbm_peak, "peak_src": peak_src}},
+            "cpu_baseline": cpu,
+            "rescored_per_step": resc / a.steps,
+            "setup_s": {"generate": t_gen, "pack_upload": t_pack}, "wall_s_timed": wall_max,
+        }
+        print(json.dumps(line))
+    if dist is not None:
+        dist.destroy_process_group()
+    db.close()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

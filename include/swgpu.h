@@ -55,6 +55,9 @@ typedef struct {
     int64_t n_long;           /* targets scored by the intra-sequence kernel */
     int32_t kernel_launches;  /* engine kernels launched by this search */
     int32_t tile_rows;        /* query rows per register tile chosen for K1 */
+    double  ms_topk;          /* last swgpu_topk(): selection + coordinate passes */
+    int32_t topk_launches;    /* kernels launched by the last swgpu_topk() */
+    int32_t reserved;
 } swgpu_stats_t;
 
 /* Top hit with coordinates (the reference has no counterpart). */
@@ -106,6 +109,9 @@ int swgpu_db_scores_d2h(swgpu_db_t *db, int32_t *scores);
  * linear-space end/start coordinates recomputed on the GPU for the k hits.
  */
 int swgpu_topk(swgpu_db_t *db, int k, swgpu_hit_t *hits, int *n_hits);
+
+/* Statistics of the last search on this handle, with ms_topk / topk_launches of the last swgpu_topk(). */
+int swgpu_db_last_stats(const swgpu_db_t *db, swgpu_stats_t *out);
 
 /* Single-batch call with the reference's own batch layout: 16 lanes interleaved
  * [pos][lane], pad 31 -- the GPU twin of alignment_fill_matrices(aligner_t*)

@@ -62,7 +62,7 @@ template <int R> struct Tile {
   static constexpr int WORDS = 32 * (SA + SB);
 };
 
-__global__ void build_profile(const int8_t* __restrict__ query, int lq, const int8_t* __restrict__ table,
+static __global__ void build_profile(const int8_t* __restrict__ query, int lq, const int8_t* __restrict__ table,
                               int R, int SA, int SB, int ntiles, unsigned* __restrict__ prof) {
   const int words = 32 * (SA + SB);
   const long total = (long)ntiles * words;
@@ -208,7 +208,7 @@ __global__ void __launch_bounds__(K1_WARPS * 32, 2) k1_inter(const K1Params P) {
 // `limit` sends BOTH its targets to the 32-bit rescoring list (a carry out of the low half
 // would have corrupted the high half).
 // ------------------------------------------------------------------------------------------
-__global__ void k1_finalize(const unsigned* __restrict__ raw, long n_lanes, long first, long n_sorted,
+static __global__ void k1_finalize(const unsigned* __restrict__ raw, long n_lanes, long first, long n_sorted,
                             unsigned B, unsigned limit, const int64_t* __restrict__ order,
                             int32_t* __restrict__ scores_file, int* __restrict__ rescore_list,
                             unsigned* __restrict__ rescore_count) {

@@ -1,6 +1,6 @@
 // swgpu.cu -- implementation of the C-ABI in include/swgpu.h (thin extern "C" layer over the
 // kernels in sw_kernels.cuh).  No CPU fallback: every compute entry point needs a CUDA device.
-#include "../../include/swgpu.h"
+#include "swgpu_internal.h"
 #include "db_pack.h"
 #include "sw_kernels.cuh"
 
@@ -13,53 +13,12 @@
 
 namespace {
 
-thread_local char g_err[512] = "";
-
-int fail(int code, const char* fmt, ...) {
-  va_list ap; va_start(ap, fmt); vsnprintf(g_err, sizeof(g_err), fmt, ap); va_end(ap);
-  return code;
-}
-
-#define CU(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) \
-  return fail(e_ == cudaErrorNoDevice || e_ == cudaErrorInsufficientDriver ? SWGPU_ENODEV : SWGPU_ECUDA, \
-              "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); } while (0)
+using swi::fail;
 
 constexpr int kDefaultLongThreshold = 3072;
 constexpr int kTileChoices[] = {32, 28, 24, 20, 16};
 
 }  // namespace
-
-struct swgpu_db {
-  int device = 0;
-  int sm_count = 0;
-  int64_t n = 0, n_residues = 0, n_long = 0, n_chunks = 0, entry_base = 0;
-  int32_t max_len = 0, max_chunk_cols = 0;
-  // device arrays (database, resident)
-  int8_t*   d_plain = nullptr;
-  int64_t*  d_plain_off = nullptr;
-  int64_t*  d_order = nullptr;
-  uint2*    d_cols = nullptr;
-  int64_t*  d_chunk_off = nullptr;
-  int32_t*  d_chunk_cols = nullptr;
-  // device scratch (per search)
-  int32_t*  d_scores = nullptr;        // file order
-  unsigned* d_raw = nullptr;           // n_chunks*32
-  int*      d_rescore_list = nullptr;  // up to n
-  unsigned* d_counters = nullptr;      // [0]=k1 queue, [1]=k3 long queue, [2]=rescore count, [3]=k3 rescore queue
-  uint2*    d_bnd1 = nullptr;  long long bnd1_stride = 0;  int k1_grid = 0;
-  int2*     d_bnd3 = nullptr;  long long bnd3_stride = 0;  int k3_grid = 0;
-  int8_t*   d_query = nullptr; int64_t query_cap = 0;
-  int8_t*   d_table = nullptr;
-  unsigned* d_prof = nullptr;  size_t prof_cap = 0;
-  int64_t   device_bytes = 0;
-  // host copies needed after packing
-  std::vector<int64_t> h_order;
-  std::vector<int64_t> h_len_sorted_prefix;   // plain_off (sorted)
-  cudaStream_t s_main = nullptr, s_aux = nullptr;
-  cudaEvent_t ev[8] = {};
-  int64_t last_lq = 0;
-  bool have_scores = false;
-};
 
 namespace {
 
@@ -81,7 +40,7 @@ int swgpu_device_count(void) {
   return n;
 }
 
-const char* swgpu_last_error(void) { return g_err; }
+const char* swgpu_last_error(void) { return swi::err_buf(); }
 const char* swgpu_version(void) { return "swgpu 0.1 (sm_100a)"; }
 
 void swgpu_db_destroy(swgpu_db_t* db) {
@@ -91,6 +50,7 @@ void swgpu_db_destroy(swgpu_db_t* db) {
   cudaFree(db->d_chunk_off); cudaFree(db->d_chunk_cols); cudaFree(db->d_scores); cudaFree(db->d_raw);
   cudaFree(db->d_rescore_list); cudaFree(db->d_counters); cudaFree(db->d_bnd1); cudaFree(db->d_bnd3);
   cudaFree(db->d_query); cudaFree(db->d_table); cudaFree(db->d_prof);
+  cudaFree(db->d_keys); cudaFree(db->d_hit_sidx); cudaFree(db->d_sel); cudaFree(db->d_coords); cudaFree(db->d_bnd_loc);
   for (auto& e : db->ev) if (e) cudaEventDestroy(e);
   if (db->s_main) cudaStreamDestroy(db->s_main);
   if (db->s_aux) cudaStreamDestroy(db->s_aux);
@@ -303,6 +263,7 @@ int run_search(swgpu_db* db, const int8_t* query, int64_t lq, const int8_t* tabl
   CU(cudaStreamSynchronize(db->s_aux));
   db->have_scores = true;
   db->last_lq = lq;
+  db->last_oe = oe; db->last_ge = ge;
 
   float ms = 0;
   CU(cudaEventElapsedTime(&ms, e[0], e[2])); st.ms_total = ms;
@@ -330,6 +291,7 @@ int run_search(swgpu_db* db, const int8_t* query, int64_t lq, const int8_t* tabl
       st.ms_intra = st.ms_total; st.n_long = db->n; st.cells_intra = st.cells;
     }
   }
+  db->last_stats = st;
   if (stats) *stats = st;
   return SWGPU_OK;
 }
@@ -362,6 +324,7 @@ int swgpu_search(swgpu_db_t* db, const int8_t* query, int64_t query_len, const i
   CU(cudaEventRecord(db->ev[7], db->s_main));
   CU(cudaStreamSynchronize(db->s_main));
   float ms = 0; CU(cudaEventElapsedTime(&ms, db->ev[6], db->ev[7])); st.ms_d2h = ms;
+  db->last_stats = st;
   if (stats) *stats = st;
   return SWGPU_OK;
 }
@@ -388,4 +351,3 @@ int swgpu_fill_batch16(int device, const int8_t* query, int64_t query_len, const
 
 }  // extern "C"
 
-// top-k + coordinates live in swgpu_topk.cu

@@ -27,6 +27,7 @@ class Stats(C.Structure):
         ("cells", C.c_int64), ("cells_inter", C.c_int64), ("cells_intra", C.c_int64),
         ("cells_rescore", C.c_int64), ("n_rescored", C.c_int64), ("n_long", C.c_int64),
         ("kernel_launches", C.c_int32), ("tile_rows", C.c_int32),
+        ("ms_topk", C.c_double), ("topk_launches", C.c_int32), ("reserved", C.c_int32),
     ]
 
     def as_dict(self):
@@ -73,6 +74,8 @@ def lib():
     L.swgpu_db_scores_d2h.argtypes = [C.c_void_p, C.c_void_p]
     L.swgpu_topk.restype = C.c_int
     L.swgpu_topk.argtypes = [C.c_void_p, C.c_int, P(Hit), P(C.c_int)]
+    L.swgpu_db_last_stats.restype = C.c_int
+    L.swgpu_db_last_stats.argtypes = [C.c_void_p, P(Stats)]
     L.swgpu_fill_batch16.restype = C.c_int
     L.swgpu_fill_batch16.argtypes = [C.c_int, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_int,
                                      C.c_void_p, C.c_int, C.c_int, C.c_void_p]
@@ -138,10 +141,17 @@ class Database:
         _check(lib().swgpu_db_scores_d2h(self._h, s.ctypes.data_as(C.c_void_p)))
         return s
 
+    def last_stats(self):
+        st = Stats()
+        _check(lib().swgpu_db_last_stats(self._h, C.byref(st)))
+        return st.as_dict()
+
     def topk(self, k):
         hits = (Hit * k)()
         n = C.c_int(0)
         _check(lib().swgpu_topk(self._h, k, hits, C.byref(n)))
+        st = self.last_stats()
+        self.last_topk_ms, self.last_topk_launches = st["ms_topk"], st["topk_launches"]
         return [dict(score=h.score, q_start=h.q_start, q_end=h.q_end, t_start=h.t_start, t_end=h.t_end, entry=h.entry)
                 for h in hits[: n.value]]
 
