@@ -49,7 +49,7 @@ __device__ __forceinline__ unsigned do_op(unsigned x, unsigned a, unsigned b, un
 }
 
 constexpr int CH = 8;      // independent chains per op class
-constexpr int ITERS = 2048;
+constexpr int ITERS = 8192;
 
 template <int OP1, int N1, int OP2, int N2>
 __global__ void __launch_bounds__(256) k_mix(const unsigned* __restrict__ in, unsigned* __restrict__ out,
@@ -100,18 +100,19 @@ __global__ void __launch_bounds__(256) k_mix(const unsigned* __restrict__ in, un
   if (threadIdx.x == 0) cyc[blockIdx.x] = t1 - t0;
 }
 
-struct Ctx { unsigned* in; unsigned* out; long long* cyc; int sms; int ctas_per_sm; };
+struct Ctx { unsigned* in; unsigned* out; long long* cyc; int sms; int ctas_per_sm; double max_hz; };
 
 template <int OP1, int N1, int OP2, int N2>
 static void run(const Ctx& c) {
   const int grid = c.sms * c.ctas_per_sm, block = 256;
   cudaEvent_t e0, e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
-  k_mix<OP1, N1, OP2, N2><<<grid, block>>>(c.in, c.out, c.cyc);     // warm-up
+  constexpr int REPS = 24;                                          // long enough for the clocks to settle
+  for (int i = 0; i < 8; ++i) k_mix<OP1, N1, OP2, N2><<<grid, block>>>(c.in, c.out, c.cyc);     // warm-up
   CK(cudaDeviceSynchronize());
   CK(cudaEventRecord(e0));
-  k_mix<OP1, N1, OP2, N2><<<grid, block>>>(c.in, c.out, c.cyc);
+  for (int i = 0; i < REPS; ++i) k_mix<OP1, N1, OP2, N2><<<grid, block>>>(c.in, c.out, c.cyc);
   CK(cudaEventRecord(e1)); CK(cudaEventSynchronize(e1));
-  float ms; CK(cudaEventElapsedTime(&ms, e0, e1));
+  float ms; CK(cudaEventElapsedTime(&ms, e0, e1)); ms /= REPS;
   long long* h = (long long*)malloc(sizeof(long long) * grid);
   CK(cudaMemcpy(h, c.cyc, sizeof(long long) * grid, cudaMemcpyDeviceToHost));
   double avg = 0; for (int i = 0; i < grid; ++i) avg += (double)h[i]; avg /= grid; free(h);
@@ -121,9 +122,14 @@ static void run(const Ctx& c) {
   // all resident CTAs of an SM run concurrently (ctas_per_sm*8 warps <= 64), so per-SM rate = ctas_per_sm * w / cycles
   const double r1 = c.ctas_per_sm * w1 / avg, r2 = c.ctas_per_sm * w2 / avg;
   const double ghz = (avg / (ms * 1e-3)) * 1e-9;
-  printf("{\"op1\":\"%s\",\"n1\":%d,\"op2\":\"%s\",\"n2\":%d,\"ms\":%.4f,\"cycles\":%.0f,\"sm_ghz_eff\":%.3f,"
-         "\"winst_per_clk_sm_op1\":%.3f,\"winst_per_clk_sm_op2\":%.3f,\"winst_per_clk_sm_total\":%.3f}\n",
-         op_name[OP1], N1, op_name[OP2], N2, ms, avg, ghz, r1, r2, r1 + r2);
+  // time-based absolute rates (what a roofline needs): thread-instructions per second over the whole chip,
+  // and the same expressed per SM per clock of the max SM clock (clock64 need not tick at the SM clock)
+  const double t1 = w1 * grid * 32.0 / (ms * 1e-3), t2 = w2 * grid * 32.0 / (ms * 1e-3);
+  const double per = 1.0 / (32.0 * c.sms * c.max_hz);
+  printf("{\"op1\":\"%s\",\"n1\":%d,\"op2\":\"%s\",\"n2\":%d,\"ms\":%.4f,\"cycles\":%.0f,\"clock64_ghz\":%.3f,"
+         "\"winst_per_clk64_sm_total\":%.3f,\"tinst_per_s_op1\":%.4e,\"tinst_per_s_op2\":%.4e,"
+         "\"winst_per_maxclk_sm_op1\":%.3f,\"winst_per_maxclk_sm_op2\":%.3f,\"winst_per_maxclk_sm_total\":%.3f}\n",
+         op_name[OP1], N1, op_name[OP2], N2, ms, avg, ghz, r1 + r2, t1, t2, t1 * per, t2 * per, (t1 + t2) * per);
   fflush(stdout);
   CK(cudaEventDestroy(e0)); CK(cudaEventDestroy(e1));
 }
@@ -131,7 +137,7 @@ static void run(const Ctx& c) {
 int main(int argc, char** argv) {
   int dev = 0; CK(cudaSetDevice(dev));
   cudaDeviceProp p; CK(cudaGetDeviceProperties(&p, dev));
-  Ctx c; c.sms = p.multiProcessorCount; c.ctas_per_sm = (argc > 1) ? atoi(argv[1]) : 4;   // 4 x 256 thr = 32 warps/SM
+  Ctx c; c.sms = p.multiProcessorCount; c.max_hz = p.clockRate * 1e3; c.ctas_per_sm = (argc > 1) ? atoi(argv[1]) : 4;   // 4 x 256 thr = 32 warps/SM
   fprintf(stderr, "device %s, %d SMs, clock %d kHz, ctas/SM %d\n", p.name, c.sms, p.clockRate, c.ctas_per_sm);
   unsigned h[1024 + 64];
   srand(12345);
