@@ -222,17 +222,11 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    from swgpu.shard import gather_topk
+
     def merge_topk(hits_local):
         """per-rank top-k -> NCCL all_gather -> deterministic merge (score desc, entry asc)."""
-        t = torch.tensor([[h["score"], h["entry"]] for h in hits_local] + [[-1, -1]] * (TOPK - len(hits_local)),
-                         dtype=torch.int64, device="cuda")
-        if dist is None:
-            return t
-        out = [torch.empty_like(t) for _ in range(world)]
-        dist.all_gather(out, t)
-        allh = torch.cat(out)
-        key = allh[:, 0] * (1 << 40) - allh[:, 1]
-        return allh[torch.argsort(key, descending=True)[:TOPK]]
+        return gather_topk([[h["score"], h["entry"]] for h in hits_local], TOPK, dist, device="cuda" if dist is not None else None)
 
     def step_resident():
         ms, launches, k1ms, k1cells, resc = 0.0, 0, 0.0, 0, 0
@@ -294,7 +288,6 @@ def main():
         sms = torch.cuda.get_device_properties(local).multi_processor_count
         peak_gcups = alu_rate * 32 * sms * sm_max * 1e6 / 2.25 / 1e9
         k1_gcups = k1cells / (k1ms * 1e-3) / 1e9 if k1ms > 0 else 0.0
-        hbm_ach = (k1cells / max(sum(len(q) for q in queries), 1) * 20 / 1.0) if False else None
         # algorithmic HBM bytes of K1 per step: 1 B per target residue per query pass + 4 B score per target per query
         k1_bytes = a.steps * len(queries) * (n_res + 4 * n)
         hbm_gbs = k1_bytes / (k1ms * 1e-3) / 1e9 if k1ms > 0 else 0.0

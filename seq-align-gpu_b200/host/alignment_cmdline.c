@@ -1,0 +1,386 @@
+/*
+ * alignment_cmdline.c -- command line and the one-to-many driver on top of the GPU engine.
+ * Interface and observable behaviour follow the reference's src/alignment_cmdline.c (flags :177-308,
+ * driver :343-539); see include/alignment_cmdline.h.  The arithmetic lives in libswgpu.so only.
+ */
+#define _POSIX_C_SOURCE 200809L
+#include "alignment_cmdline.h"
+#include "alignment_scoring_load.h"
+#include "fasta_reader.h"
+#include "swgpu.h"
+
+#include <limits.h>
+#include <pthread.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <strings.h>
+#include <zlib.h>
+
+/* ---------------------------------------------------------------- number parsing */
+
+char parse_entire_short(char *str, short *result)
+{
+    char *end = str;
+    const long v = strtol(str, &end, 10);
+    if (end != str + strlen(str) || v > SHRT_MAX || v < SHRT_MIN) return 0;
+    *result = (short)v; return 1;
+}
+
+char parse_entire_ushort(char *str, unsigned short *result)
+{
+    char *end = str;
+    const long v = strtol(str, &end, 10);
+    if (end != str + strlen(str) || v > USHRT_MAX) return 0;
+    *result = (unsigned short)v; return 1;
+}
+
+char parse_entire_int(char *str, int *result)
+{
+    char *end = str;
+    const long v = strtol(str, &end, 10);
+    if (end != str + strlen(str) || v > INT_MAX || v < INT_MIN) return 0;
+    *result = (int)v; return 1;
+}
+
+char parse_entire_uint(char *str, unsigned int *result)
+{
+    char *end = str;
+    const unsigned long v = strtoul(str, &end, 10);
+    if (end != str + strlen(str) || v > UINT_MAX) return 0;
+    *result = (unsigned int)v; return 1;
+}
+
+char parse_entire_score_t(char *str, score_t *result)
+{
+    short v;                                   /* score_t is int16_t (include/alignment_scoring.h) */
+    if (!parse_entire_short(str, &v)) return 0;
+    *result = v; return 1;
+}
+
+/* ---------------------------------------------------------------- usage */
+
+static void usage_exit(const score_t defaults[4], const char *prog, const char *fmt, ...)
+    __attribute__((format(printf, 3, 4))) __attribute__((noreturn));
+
+static void usage_exit(const score_t defaults[4], const char *prog, const char *fmt, ...)
+{
+    if (fmt) {
+        va_list ap;
+        fprintf(stderr, "Error: ");
+        va_start(ap, fmt); vfprintf(stderr, fmt, ap); va_end(ap);
+        if (fmt[strlen(fmt) - 1] != '\n') fputc('\n', stderr);
+    }
+    fprintf(stderr, "usage: %s [OPTIONS] [seq1 seq2]\n", prog);
+    fprintf(stderr,
+            "  Smith-Waterman optimal local alignment (maximises score).  \n"
+            "  Scores ONE query sequence against every sequence of a database file on the GPU\n"
+            "  (B200, sm_100a).  Can read gzip files, FASTA and FASTQ.\n\n"
+            "  OPTIONS:\n"
+            "    --file <file>        Sequence file reading with gzip support\n"
+            "    --files <f1> <f2>    Query file <f1> (first record) against database file <f2>\n"
+            "    --stdin              Read from STDIN (same as '--file -')\n"
+            "\n"
+            "    --match <score>      [default: %i]\n"
+            "    --mismatch <score>   [default: %i]\n"
+            "    --gapopen <score>    [default: %i]\n"
+            "    --gapextend <score>  [default: %i]\n"
+            "\n"
+            "    --substitution_matrix <file>  see details for formatting\n\n"
+            "    --minscore <score>   Minimum required score\n"
+            "\n"
+            "    --printseq           Print sequences before local alignments\n"
+            "    --printmatrices      Print dynamic programming matrices\n"
+            "    --printfasta         Print fasta header lines\n"
+            "    --pretty             Print with a descriptor line\n"
+            "    --colour             Print with colour\n"
+            "\n",
+            defaults[0], defaults[1], defaults[2], defaults[3]);
+    printf("\n"
+           " DETAILS:\n"
+           "  * Gap (of length N) penalty is: (open+N*extend)\n"
+           "  * To do alignment without affine gap penalty, set '--gapopen 0'.\n"
+           "  * Scoring files should be matrices, with entries separated by a single\n"
+           "    character or whitespace. See files in the 'scoring' directory for examples.\n"
+           "  * Environment: SWGPU_GPUS=<n> shards the database over n GPUs,\n"
+           "    SWGPU_TOPK=<k> prints only the k best entries (with coordinates).\n"
+           "\n");
+    exit(EXIT_FAILURE);
+}
+
+void cmdline_free(cmdline_t *cmd) { free(cmd); }
+void cmdline_set_files(cmdline_t *cmd, char *p1, char *p2) { cmd->file_path1 = p1; cmd->file_path2 = p2; }
+char *cmdline_get_file1(cmdline_t *cmd) { return cmd->file_path1; }
+char *cmdline_get_file2(cmdline_t *cmd) { return cmd->file_path2; }
+
+#define USAGE(...) usage_exit(defaults, argv[0], __VA_ARGS__)
+
+cmdline_t *cmdline_new(int argc, char **argv, scoring_t *scoring, enum SeqAlignCmdType cmd_type)
+{
+    (void)cmd_type;
+    cmdline_t *cmd = (cmdline_t *)calloc(1, sizeof(cmdline_t));
+    const score_t defaults[4] = {(score_t)scoring->match, (score_t)scoring->mismatch, scoring->gap_open, scoring->gap_extend};
+    if (argc == 1) USAGE(NULL);
+    for (int i = 1; i < argc; i++)
+        if (!strcasecmp(argv[i], "--help") || !strcasecmp(argv[i], "-help") || !strcasecmp(argv[i], "-h")) USAGE(NULL);
+
+    bool matrix_set = false, match_set = false;
+    for (int i = 1; i < argc; i++) {
+        char *a = argv[i];
+        if (a[0] != '-') {
+            if (argc - i != 2) USAGE("Unknown options: '%s'", a);
+            break;
+        }
+        if (!strcasecmp(a, "--printseq")) cmd->print_seq = true;
+        else if (!strcasecmp(a, "--printmatrices")) cmd->print_matrices = true;
+        else if (!strcasecmp(a, "--printfasta")) cmd->print_fasta = true;
+        else if (!strcasecmp(a, "--pretty")) cmd->print_pretty = true;
+        else if (!strcasecmp(a, "--colour")) cmd->print_colour = true;
+        else if (!strcasecmp(a, "--stdin")) { cmdline_set_files(cmd, "", NULL); cmd->interactive = true; }
+        else if (i == argc - 1) USAGE("Unknown argument without parameter: %s", a);
+        else if (!strcasecmp(a, "--scoring")) i++;                       /* accepted and ignored, like the reference */
+        else if (!strcasecmp(a, "--substitution_matrix")) {
+            gzFile f = gzopen(argv[i + 1], "r");
+            if (!f) USAGE("Couldn't read: %s", argv[i + 1]);
+            align_scoring_load_matrix(f, argv[i + 1], scoring, true);
+            gzclose(f);
+            matrix_set = true; i++;
+        }
+        else if (!strcasecmp(a, "--match")) {
+            if (!parse_entire_int(argv[i + 1], &scoring->match)) USAGE("Invalid --match argument ('%s') must be an int", argv[i + 1]);
+            match_set = true; i++;
+        }
+        else if (!strcasecmp(a, "--mismatch")) {
+            if (!parse_entire_int(argv[i + 1], &scoring->mismatch)) USAGE("Invalid --mismatch argument ('%s') must be an int", argv[i + 1]);
+            i++;
+        }
+        else if (!strcasecmp(a, "--gapopen")) {
+            if (!parse_entire_score_t(argv[i + 1], &scoring->gap_open)) USAGE("Invalid --gapopen argument ('%s') must be an int", argv[i + 1]);
+            i++;
+        }
+        else if (!strcasecmp(a, "--gapextend")) {
+            if (!parse_entire_score_t(argv[i + 1], &scoring->gap_extend)) USAGE("Invalid --gapextend argument ('%s') must be an int", argv[i + 1]);
+            i++;
+        }
+        else if (!strcasecmp(a, "--minscore")) i++;                      /* listed in the usage text; no effect on the scoring path */
+        else if (!strcasecmp(a, "--file")) { cmdline_set_files(cmd, argv[i + 1], NULL); i++; }
+        else if (!strcasecmp(a, "--files")) {
+            if (i >= argc - 2) USAGE("--files option takes 2 arguments");
+            printf("Query File=%s and Database File=%s\n", argv[i + 1], argv[i + 2]);
+            if (!strcmp(argv[i + 1], "-") && !strcmp(argv[i + 2], "-")) cmdline_set_files(cmd, argv[i + 1], NULL);
+            else cmdline_set_files(cmd, argv[i + 1], argv[i + 2]);
+            i += 2;
+        }
+        else USAGE("Unknown argument '%s'", a);
+    }
+    if (matrix_set && !match_set) scoring->use_match_mismatch = 0;
+    if (scoring->use_match_mismatch && scoring->match < scoring->mismatch) USAGE("Match value should not be less than mismatch penalty");
+    if (cmd->file_path1 == NULL || cmd->file_path2 == NULL) USAGE("No input specified");
+    return cmd;
+}
+
+/* ---------------------------------------------------------------- one-to-many driver */
+
+typedef struct {
+    char **names, **seqs;          /* per entry, file order (seqs kept only for --printseq callers) */
+    int8_t *codes; int64_t *off;   /* encoded residues back to back + prefix offsets */
+    size_t n, cap; size_t res_cap;
+} dbmem_t;
+
+static void db_push(dbmem_t *d, const swfa_record_t *rec)
+{
+    if (d->n == d->cap) {
+        d->cap = d->cap ? d->cap * 2 : 4096;
+        d->names = (char **)realloc(d->names, d->cap * sizeof(char *));
+        d->seqs = (char **)realloc(d->seqs, d->cap * sizeof(char *));
+        d->off = (int64_t *)realloc(d->off, (d->cap + 1) * sizeof(int64_t));
+        if (!d->names || !d->seqs || !d->off) { fprintf(stderr, "Error: out of memory\n"); exit(EXIT_FAILURE); }
+        if (d->n == 0) d->off[0] = 0;
+    }
+    const size_t base = (size_t)d->off[d->n];
+    if (base + rec->seq_len > d->res_cap) {
+        d->res_cap = d->res_cap ? d->res_cap * 2 : (1u << 20);
+        while (base + rec->seq_len > d->res_cap) d->res_cap *= 2;
+        d->codes = (int8_t *)realloc(d->codes, d->res_cap);
+        if (!d->codes) { fprintf(stderr, "Error: out of memory\n"); exit(EXIT_FAILURE); }
+    }
+    /* same encoding, same failure mode (stdout message + exit(1)) as src/alignment_cmdline.c:444-446 */
+    for (size_t i = 0; i < rec->seq_len; i++) d->codes[base + i] = letters_to_index(rec->seq[i]);
+    d->names[d->n] = strdup(rec->name);
+    d->seqs[d->n] = strdup(rec->seq);
+    d->off[d->n + 1] = (int64_t)(base + rec->seq_len);
+    d->n++;
+}
+
+typedef struct {
+    int device;
+    const int8_t *codes; const int64_t *off; int64_t n;   /* this shard */
+    const int64_t *entry;                                 /* shard index -> file index (NULL = identity) */
+    const int8_t *query; int64_t lq; const scoring_t *sc;
+    int32_t *scores_file;                                 /* shared output, file order */
+    int topk; swgpu_hit_t *hits; int n_hits;
+    double ms; int rc; char err[512];
+} shard_job_t;
+
+static void *shard_run(void *arg)
+{
+    shard_job_t *j = (shard_job_t *)arg;
+    swgpu_db_t *db = NULL;
+    j->rc = swgpu_db_create(&db, j->device, j->codes, j->off, j->n, 0, NULL);
+    if (j->rc == SWGPU_OK) {
+        int32_t *tmp = (int32_t *)malloc(sizeof(int32_t) * (size_t)(j->n ? j->n : 1));
+        swgpu_stats_t st;
+        j->rc = swgpu_search(db, j->query, j->lq, &j->sc->swap_scores[0][0], j->sc->gap_open, j->sc->gap_extend, tmp, &st);
+        if (j->rc == SWGPU_OK) {
+            j->ms = st.ms_total;
+            for (int64_t i = 0; i < j->n; i++) j->scores_file[j->entry ? j->entry[i] : i] = tmp[i];
+            if (j->topk > 0) {
+                j->rc = swgpu_topk(db, j->topk, j->hits, &j->n_hits);
+                for (int h = 0; h < j->n_hits && j->entry; h++) j->hits[h].entry = j->entry[j->hits[h].entry];
+            }
+        }
+        free(tmp);
+    }
+    if (j->rc != SWGPU_OK) snprintf(j->err, sizeof(j->err), "%s", swgpu_last_error());
+    swgpu_db_destroy(db);
+    return NULL;
+}
+
+static int hit_cmp(const void *a, const void *b)
+{
+    const swgpu_hit_t *x = (const swgpu_hit_t *)a, *y = (const swgpu_hit_t *)b;
+    if (x->score != y->score) return x->score > y->score ? -1 : 1;
+    return x->entry < y->entry ? -1 : (x->entry > y->entry);
+}
+
+/* length-balanced sharding: deal the targets, longest first, round-robin over the GPUs, so every
+ * shard gets the same length mix and (to within one target per round) the same residue count */
+static void make_shards(const dbmem_t *d, int g, int8_t **codes, int64_t **off, int64_t **entry, int64_t *cnt)
+{
+    const size_t n = d->n;
+    int64_t maxlen = 0;
+    for (size_t t = 0; t < n; t++) { const int64_t l = d->off[t + 1] - d->off[t]; if (l > maxlen) maxlen = l; }
+    int64_t *bucket = (int64_t *)calloc((size_t)maxlen + 2, sizeof(int64_t));
+    int64_t *order = (int64_t *)malloc(sizeof(int64_t) * (n ? n : 1));
+    for (size_t t = 0; t < n; t++) bucket[maxlen - (d->off[t + 1] - d->off[t]) + 1]++;
+    for (int64_t l = 0; l <= maxlen; l++) bucket[l + 1] += bucket[l];
+    for (size_t t = 0; t < n; t++) order[bucket[maxlen - (d->off[t + 1] - d->off[t])]++] = (int64_t)t;
+    free(bucket);
+    for (int s = 0; s < g; s++) {
+        int64_t m = 0, res = 0;
+        for (size_t r = (size_t)s; r < n; r += (size_t)g) { m++; res += d->off[order[r] + 1] - d->off[order[r]]; }
+        cnt[s] = m;
+        codes[s] = (int8_t *)malloc((size_t)(res ? res : 1));
+        off[s] = (int64_t *)malloc(sizeof(int64_t) * (size_t)(m + 1));
+        entry[s] = (int64_t *)malloc(sizeof(int64_t) * (size_t)(m ? m : 1));
+        int64_t k = 0; off[s][0] = 0;
+        for (size_t r = (size_t)s; r < n; r += (size_t)g, k++) {
+            const int64_t t = order[r], l = d->off[t + 1] - d->off[t];
+            memcpy(codes[s] + off[s][k], d->codes + d->off[t], (size_t)l);
+            off[s][k + 1] = off[s][k] + l;
+            entry[s][k] = t;
+        }
+    }
+    free(order);
+}
+
+void align_from_query_and_db(const char *query_path, const char *db_path, scoring_t *scoring,
+                             void (print_alignment)(aligner_t *aligner, size_t total_cnt), bool use_zlib)
+{
+    swfa_reader_t *qf = swfa_open(query_path, use_zlib);
+    if (!qf) { fprintf(stderr, "Error: couldn't open query file %s\n", query_path); fflush(stderr); return; }
+    swfa_reader_t *df = swfa_open(db_path, use_zlib);
+    if (!df) { fprintf(stderr, "Error: couldn't open database file %s\n", db_path); fflush(stderr); swfa_close(qf); return; }
+
+    swfa_record_t q = {0}, rec = {0};
+    if (swfa_read(qf, &q) <= 0 || q.seq_len == 0) {
+        fprintf(stderr, "Error: Query file %s is empty or invalid\n", query_path); fflush(stderr);
+        swfa_close(qf); swfa_close(df); swfa_record_free(&q); return;
+    }
+    /* query encode; letters whose diagonal the matrix never defined become 'X' (src/alignment_cmdline.c:388-396) */
+    int8_t *qi = (int8_t *)malloc(q.seq_len);
+    for (size_t i = 0; i < q.seq_len; i++) {
+        qi[i] = letters_to_index(q.seq[i]);
+        if (!get_swap_bit(scoring, qi[i], qi[i])) qi[i] = letters_to_index('X');
+    }
+
+    dbmem_t d; memset(&d, 0, sizeof(d));
+    int st;
+    while ((st = swfa_read(df, &rec)) > 0) db_push(&d, &rec);
+    if (d.n == 0) { d.off = (int64_t *)calloc(1, sizeof(int64_t)); }
+
+    /* ---- GPU search (the reference's timed `omp parallel for`, src/alignment_cmdline.c:503-509) ---- */
+    int ndev = swgpu_device_count();
+    if (ndev < 1) { fprintf(stderr, "Error: no CUDA device available (this build has no CPU path)\n"); exit(EXIT_FAILURE); }
+    int g = 1;
+    const char *eg = getenv("SWGPU_GPUS");
+    if (eg && atoi(eg) > 0) g = atoi(eg);
+    if (g > ndev) g = ndev;
+    if ((size_t)g > d.n) g = d.n ? (int)d.n : 1;
+    int topk = 0;
+    const char *ek = getenv("SWGPU_TOPK");
+    if (ek && atoi(ek) > 0) topk = atoi(ek);
+
+    int32_t *scores = (int32_t *)calloc(d.n ? d.n : 1, sizeof(int32_t));
+    shard_job_t *jobs = (shard_job_t *)calloc((size_t)g, sizeof(shard_job_t));
+    int8_t **sc_codes = (int8_t **)calloc((size_t)g, sizeof(*sc_codes));
+    int64_t **sc_off = (int64_t **)calloc((size_t)g, sizeof(*sc_off)), **sc_entry = (int64_t **)calloc((size_t)g, sizeof(*sc_entry));
+    int64_t *sc_cnt = (int64_t *)calloc((size_t)g, sizeof(int64_t));
+    if (g > 1) make_shards(&d, g, sc_codes, sc_off, sc_entry, sc_cnt);
+    pthread_t *th = (pthread_t *)calloc((size_t)g, sizeof(pthread_t));
+    for (int s = 0; s < g; s++) {
+        shard_job_t *j = &jobs[s];
+        j->device = s; j->query = qi; j->lq = (int64_t)q.seq_len; j->sc = scoring; j->scores_file = scores;
+        j->topk = topk; j->hits = topk ? (swgpu_hit_t *)calloc((size_t)topk, sizeof(swgpu_hit_t)) : NULL;
+        if (g > 1) { j->codes = sc_codes[s]; j->off = sc_off[s]; j->n = sc_cnt[s]; j->entry = sc_entry[s]; }
+        else { j->codes = d.codes; j->off = d.off; j->n = (int64_t)d.n; j->entry = NULL; }
+        if (g > 1) pthread_create(&th[s], NULL, shard_run, j); else shard_run(j);
+    }
+    double total_ms = 0;
+    for (int s = 0; s < g; s++) {
+        if (g > 1) pthread_join(th[s], NULL);
+        if (jobs[s].rc != SWGPU_OK) { fprintf(stderr, "Error: GPU search failed on device %d: %s\n", s, jobs[s].err); exit(EXIT_FAILURE); }
+        if (jobs[s].ms > total_ms) total_ms = jobs[s].ms;          /* GPUs run concurrently: max, not sum */
+    }
+
+    /* ---- hand-off: the reference's callback over groups of 16 entries in file order (:511-512) ---- */
+    if (topk > 0) {
+        swgpu_hit_t *all = (swgpu_hit_t *)calloc((size_t)topk * (size_t)g, sizeof(swgpu_hit_t));
+        int m = 0;
+        for (int s = 0; s < g; s++) for (int h = 0; h < jobs[s].n_hits; h++) all[m++] = jobs[s].hits[h];
+        qsort(all, (size_t)m, sizeof(swgpu_hit_t), hit_cmp);       /* score desc, entry asc: independent of the GPU count */
+        if (m > topk) m = topk;
+        for (int h = 0; h < m; h++)
+            printf("Hit #%d: entry %lld score %d query [%d..%d] target [%d..%d] %s\n", h, (long long)all[h].entry, all[h].score,
+                   all[h].q_start, all[h].q_end, all[h].t_start, all[h].t_end, d.names[all[h].entry]);
+        free(all);
+    } else {
+        aligner_t view; aligner_init(&view);
+        score_t s16[16]; int32_t s32[16];
+        view.scoring = scoring; view.seq_a_indexes = qi; view.seq_a_str = q.seq; view.seq_a_fasta = q.name;
+        view.score_width = q.seq_len + 1; view.max_scores = s16; view.max_scores32 = s32;
+        for (size_t first = 0; first < d.n; first += 16) {
+            const size_t lanes = d.n - first < 16 ? d.n - first : 16;
+            view.vector_size = lanes;
+            view.seq_b_str_batch = d.seqs + first; view.seq_b_fasta_batch = d.names + first;
+            size_t maxlen = 0;
+            for (size_t l = 0; l < lanes; l++) {
+                s32[l] = scores[first + l];
+                s16[l] = (score_t)(s32[l] > 32767 ? 32767 : s32[l]);
+                const size_t len = (size_t)(d.off[first + l + 1] - d.off[first + l]);
+                if (len > maxlen) maxlen = len;
+            }
+            view.score_height = maxlen + 1;
+            print_alignment(&view, first);
+        }
+    }
+    printf("Total Time: %f\n", total_ms * 1e-3);
+    printf("Total Entries: %lu\n", (unsigned long)d.n);
+
+    for (int s = 0; s < g; s++) { free(jobs[s].hits); free(sc_codes[s]); free(sc_off[s]); free(sc_entry[s]); }
+    free(jobs); free(sc_codes); free(sc_off); free(sc_entry); free(sc_cnt); free(th); free(scores);
+    for (size_t i = 0; i < d.n; i++) { free(d.names[i]); free(d.seqs[i]); }
+    free(d.names); free(d.seqs); free(d.codes); free(d.off);
+    free(qi); swfa_record_free(&q); swfa_record_free(&rec);
+    swfa_close(qf); swfa_close(df);
+}

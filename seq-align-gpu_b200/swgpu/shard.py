@@ -1,0 +1,56 @@
+"""Multi-GPU host logic: residue-balanced sharding of a database and the deterministic top-k merge.
+
+The scoring path shards by independent targets (the reference's `omp parallel for` over batches,
+src/alignment_cmdline.c:504-507 of the reference tree): no data-path collective.  The only exchange is
+the gather of the per-rank top-k lists, merged with the rule of SURVEY.md A.7 (score descending, then
+file-order entry ascending), which makes the result independent of the number of GPUs."""
+from __future__ import annotations
+
+import numpy as np
+
+
+def deal_shards(offsets, world):
+    """Deal targets, longest first, round-robin over `world` ranks.  Returns a list of int64 arrays of
+    file-order entry indices; every rank gets the same length mix and (within one target per round) the
+    same residue count.  Same rule as make_shards() in host/alignment_cmdline.c."""
+    offsets = np.asarray(offsets, dtype=np.int64)
+    lens = offsets[1:] - offsets[:-1]
+    order = np.argsort(-lens, kind="stable")
+    return [order[r::world].copy() for r in range(world)]
+
+
+def take_shard(codes, offsets, entries):
+    offsets = np.asarray(offsets, dtype=np.int64)
+    lens = (offsets[1:] - offsets[:-1])[entries]
+    off = np.zeros(len(entries) + 1, dtype=np.int64)
+    np.cumsum(lens, out=off[1:])
+    out = np.empty(int(off[-1]), dtype=np.int8)
+    for k, e in enumerate(entries):
+        out[off[k]:off[k + 1]] = codes[offsets[e]:offsets[e + 1]]
+    return out, off
+
+
+def merge_topk(score_entry_lists, k):
+    """score_entry_lists: iterable of int64 arrays [m_i, 2] = (score, global entry); rows with entry < 0 are
+    padding.  Returns the k best as an int64 array [<=k, 2]."""
+    allh = np.concatenate([np.asarray(x, dtype=np.int64).reshape(-1, 2) for x in score_entry_lists])
+    allh = allh[allh[:, 1] >= 0]
+    order = np.lexsort((allh[:, 1], -allh[:, 0]))
+    return allh[order[:k]]
+
+
+def gather_topk(local_hits, k, dist=None, device=None):
+    """All-gathers fixed-size [k, 2] hit lists over torch.distributed (NCCL on GPUs, gloo in CPU tests)
+    and merges them.  With dist=None it is the single-rank merge."""
+    import torch
+    pad = np.full((k, 2), -1, dtype=np.int64)
+    lh = np.asarray(local_hits, dtype=np.int64).reshape(-1, 2)[:k]
+    pad[: len(lh)] = lh
+    if dist is None or not dist.is_initialized() or dist.get_world_size() == 1:
+        return merge_topk([pad], k)
+    t = torch.from_numpy(pad)
+    if device is not None:
+        t = t.to(device)
+    out = [torch.empty_like(t) for _ in range(dist.get_world_size())]
+    dist.all_gather(out, t)
+    return merge_topk([o.cpu().numpy() for o in out], k)
