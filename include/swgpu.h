@@ -38,8 +38,10 @@ typedef struct swgpu_db swgpu_db_t;   /* packed, HBM-resident database on one GP
 
 /* Packing knobs (0 = engine default). */
 typedef struct {
-    int32_t long_threshold;   /* targets longer than this go to the intra-sequence kernel */
-    int32_t reserved[7];
+    int32_t long_threshold;   /* chunk kernel only: targets longer than this go to the intra-sequence kernel */
+    int32_t stream_cols;      /* systolic kernel: target length of one stream of concatenated target pairs */
+    int32_t use_chunk_kernel; /* 1 = score with the first-generation chunk kernel (k1_inter) instead of k1s */
+    int32_t reserved[5];
 } swgpu_pack_opts_t;
 
 /* Per-search statistics, all device-timed with CUDA events on the engine's stream. */
@@ -54,9 +56,11 @@ typedef struct {
     int64_t n_rescored;       /* targets whose 16-bit result saturated */
     int64_t n_long;           /* targets scored by the intra-sequence kernel */
     int32_t kernel_launches;  /* engine kernels launched by this search */
-    int32_t tile_rows;        /* query rows per register tile chosen for K1 */
+    int32_t tile_rows;        /* query rows per lane (register tile) chosen for the 16-bit kernel */
     double  ms_topk;          /* last swgpu_topk(): selection + coordinate passes */
     int32_t topk_launches;    /* kernels launched by the last swgpu_topk() */
+    int32_t lanes_per_pair;   /* K1S plan: lanes that share one target pair (8, 16 or 32) */
+    int32_t passes;           /* K1S plan: query stripes of lanes_per_pair * tile_rows rows */
     int32_t reserved;
 } swgpu_stats_t;
 

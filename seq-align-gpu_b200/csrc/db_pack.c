@@ -8,10 +8,14 @@ void swpack_free(swpack_t *p)
     if (!p) return;
     free(p->order); free(p->plain_off); free(p->plain);
     free(p->chunk_cols); free(p->chunk_off); free(p->cols);
+    free(p->scols); free(p->stream_off); free(p->stream_ncols); free(p->stream_pair0);
     memset(p, 0, sizeof(*p));
 }
 
-int swpack_build(swpack_t *p, const int8_t *codes, const int64_t *offsets, int64_t n, int32_t long_threshold)
+static int build_streams(swpack_t *p, int32_t stream_cols);
+
+int swpack_build(swpack_t *p, const int8_t *codes, const int64_t *offsets, int64_t n, int32_t long_threshold,
+                 int32_t stream_cols)
 {
     memset(p, 0, sizeof(*p));
     if (n < 0) return -1;
@@ -90,6 +94,69 @@ int swpack_build(swpack_t *p, const int8_t *codes, const int64_t *offsets, int64
                 for (int64_t j = 0; j < len; j++)
                     base[(j >> 2) * 32 + lane] |= (uint64_t)(uint8_t)src[j] << (16 * (j & 3) + 8 * h);
             }
+        }
+    }
+    return build_streams(p, stream_cols);
+}
+
+/* 4. streams of paired targets for the systolic kernel (see db_pack.h) */
+static int build_streams(swpack_t *p, int32_t stream_cols)
+{
+    const int64_t n = p->n_targets;
+    const int64_t n_pairs = (n + 1) / 2;
+    p->n_pairs = n_pairs;
+    if (stream_cols < 32) stream_cols = 32;
+    /* pass 1: count streams.  pair length = its first (longer) member; an empty pair still takes one
+     * (flagged, all-padding) column so that every pair has a flush point */
+    int64_t n_streams = 0, cur = 0;
+    for (int64_t q = 0; q < n_pairs; q++) {
+        int64_t len = p->plain_off[2 * q + 1] - p->plain_off[2 * q];
+        if (len < 1) len = 1;
+        if (cur == 0) n_streams++;
+        cur += len;
+        if (cur >= stream_cols) cur = 0;
+    }
+    p->n_streams = n_streams;
+    p->stream_off = (int64_t *)malloc(sizeof(int64_t) * (size_t)(n_streams + 1));
+    p->stream_ncols = (int32_t *)malloc(sizeof(int32_t) * (size_t)(n_streams ? n_streams : 1));
+    p->stream_pair0 = (int64_t *)malloc(sizeof(int64_t) * (size_t)(n_streams ? n_streams : 1));
+    if (!p->stream_off || !p->stream_ncols || !p->stream_pair0) { swpack_free(p); return -1; }
+    int64_t s = -1, off = 0; cur = 0;
+    int32_t maxc = 0;
+    for (int64_t q = 0; q < n_pairs; q++) {
+        int64_t len = p->plain_off[2 * q + 1] - p->plain_off[2 * q];
+        if (len < 1) len = 1;
+        if (cur == 0) { s++; p->stream_off[s] = off; p->stream_pair0[s] = q; }
+        cur += len;
+        if (cur > 0x7fffff00) { swpack_free(p); return -1; }
+        if (cur >= stream_cols || q == n_pairs - 1) {
+            p->stream_ncols[s] = (int32_t)cur;
+            if (cur > maxc) maxc = (int32_t)cur;
+            off += (cur + 63) & ~(int64_t)63;
+            cur = 0;
+        }
+    }
+    p->stream_off[n_streams] = off;
+    p->scols_len = off;
+    p->max_stream_cols = maxc;
+    p->scols = (uint16_t *)calloc((size_t)(off ? off : 1), sizeof(uint16_t));
+    if (!p->scols) { swpack_free(p); return -1; }
+#pragma omp parallel for schedule(dynamic, 64)
+    for (int64_t st = 0; st < n_streams; st++) {
+        uint16_t *dst = p->scols + p->stream_off[st];
+        const int64_t q_end = (st + 1 < n_streams) ? p->stream_pair0[st + 1] : n_pairs;
+        for (int64_t q = p->stream_pair0[st]; q < q_end; q++) {
+            const int8_t *a = p->plain + p->plain_off[2 * q];
+            const int64_t la = p->plain_off[2 * q + 1] - p->plain_off[2 * q];
+            const int64_t lb = (2 * q + 1 < n) ? p->plain_off[2 * q + 2] - p->plain_off[2 * q + 1] : 0;
+            const int8_t *b = a + la;
+            const int64_t len = la < 1 ? 1 : la;
+            for (int64_t j = 0; j < len; j++) {
+                const unsigned ca = j < la ? (uint8_t)a[j] : 0u, cb = j < lb ? (uint8_t)b[j] : 0u;
+                dst[j] = (uint16_t)(ca | (cb << 8));
+            }
+            dst[0] |= 0x80u;
+            dst += len;
         }
     }
     return 0;

@@ -12,6 +12,11 @@
  *     words holding 4 columns x (codeA | codeB << 8) -- the GPU twin of the reference's
  *     16-lane [pos][lane] interleave (alignment_cmdline.c:445); padding uses code 0
  *     instead of the reference's '*' (=31, :448-450) so padded cells can never score.
+ *   - STREAMS for the systolic inter-sequence kernel (k1s): consecutive targets of the sorted
+ *     list are PAIRED (2p, 2p+1 -> the two u16 halves of one packed register); pairs are
+ *     concatenated into streams of about stream_cols columns.  One column = 16 bits:
+ *     low byte = code of target 2p (bit 7 set on the first column of a pair), high byte = code
+ *     of target 2p+1 (0 once the shorter one has ended).  A pair never straddles two streams.
  */
 #ifndef SWGPU_DB_PACK_H
 #define SWGPU_DB_PACK_H
@@ -34,11 +39,19 @@ typedef struct {
     int64_t *chunk_off;       /* [n_chunks] offset into cols, in 8-byte words         */
     uint64_t *cols;           /* interleaved chunk data                               */
     int64_t  cols_words;
+    /* streams (systolic kernel): all targets, sorted order, paired */
+    int64_t  n_pairs, n_streams;
+    int32_t  max_stream_cols;
+    uint16_t *scols;          /* [scols_len] stream columns, each stream 64-column aligned */
+    int64_t  scols_len;
+    int64_t *stream_off;      /* [n_streams+1] start column of each stream in scols      */
+    int32_t *stream_ncols;    /* [n_streams]   real columns                              */
+    int64_t *stream_pair0;    /* [n_streams]   index of the stream's first pair          */
 } swpack_t;
 
 /* returns 0, or -1 on allocation failure / bad input (negative length, code > 31) */
 int  swpack_build(swpack_t *p, const int8_t *codes, const int64_t *offsets, int64_t n_targets,
-                  int32_t long_threshold);
+                  int32_t long_threshold, int32_t stream_cols);
 void swpack_free(swpack_t *p);
 
 #ifdef __cplusplus

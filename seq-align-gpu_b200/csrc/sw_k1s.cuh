@@ -1,0 +1,247 @@
+// sw_k1s.cuh -- K1S: systolic inter-sequence kernel, packed 2 x u16 (sm_100a).
+//
+// Same recurrence and the same biased-u16 cell update as k1_inter (sw_kernels.cuh; reference
+// src/alignment.c:117-176), but a different decomposition, chosen after profiling k1_inter
+// (profiles/r1a_*: 31 GB of DRAM traffic per launch for the per-column boundary rows, 35 % of
+// warp stalls on those loads):
+//
+//   * one PAIR of targets (the two u16 halves of every register) is owned by a group of g lanes
+//     (g = 8, 16 or 32); lane l of the group keeps R consecutive query rows of the current
+//     g*R-row stripe in registers, so a query of up to 32*32 = 1024 residues lives entirely in
+//     the register file of one warp and NO boundary row ever goes to memory;
+//   * the target streams through the lanes systolically: at step s lane l works on column
+//     s - l and takes H(row above) / V from lane l-1 by __shfl_up_sync;
+//   * pairs are concatenated into streams (db_pack.h), a flag bit in the column word marks the
+//     first column of a pair: the lane flushes its running maximum for the finished pair and
+//     resets its rows.  The pipeline therefore fills and drains once per STREAM, not once per
+//     target, which is what keeps short targets efficient;
+//   * the query profile is private per lane, PL[code][word][lane] in shared memory: every lane
+//     is at a different column (different residue), bank == lane, conflict-free by construction;
+//   * queries longer than 32*R rows take several passes (stripes); only then the stripe's bottom
+//     row is carried through a per-warp linear-space buffer (8 bytes per column per pass).
+#pragma once
+#include "sw_kernels.cuh"
+
+namespace swk {
+
+template <int R> struct SProf {
+  static_assert(R % 2 == 0 && R >= 4 && R <= 32, "R must be even, 4..32");
+  static constexpr int WA = (R + 3) / 4;            // int8x4 words: s(k..k+3) for the LOW-half target
+  static constexpr int WB = R / 2;                  // int8x4 words: s(k),s(k),s(k+1),s(k+1) for the HIGH-half target
+  static constexpr int WORDS = 32 * (WA + WB) * 32; // [code][word][lane] for A, then for B
+};
+
+// prof[pass][A: code][w][lane] | [B: code][w][lane]; lane l of a g-lane group owns rows
+// pass*g*R + (l % g)*R + k.  Code 0 (padding) and rows past the query end score -128.
+static __global__ void build_sprofile(const int8_t* __restrict__ query, int lq, const int8_t* __restrict__ table,
+                                      int R, int g, int npass, unsigned* __restrict__ prof) {
+  const int WA = (R + 3) / 4, WB = R / 2;
+  const int words = 32 * (WA + WB) * 32;
+  const long total = (long)npass * words;
+  for (long idx = blockIdx.x * (long)blockDim.x + threadIdx.x; idx < total; idx += (long)gridDim.x * blockDim.x) {
+    const int pass = (int)(idx / words), w = (int)(idx % words);
+    const int lane = w & 31, cw = w >> 5;
+    const long row0 = (long)pass * g * R + (long)(lane & (g - 1)) * R;
+    auto score = [&](int c, int k) -> unsigned {
+      const long i = row0 + k;
+      const int s = (c == 0 || k >= R || i >= lq) ? -128 : (int)table[(query[i] & 31) * 32 + c];
+      return (unsigned)(s & 0xff);
+    };
+    unsigned out;
+    if (cw < 32 * WA) {
+      const int c = cw / WA, k4 = cw % WA;
+      out = score(c, 4 * k4) | (score(c, 4 * k4 + 1) << 8) | (score(c, 4 * k4 + 2) << 16) | (score(c, 4 * k4 + 3) << 24);
+    } else {
+      const int v = cw - 32 * WA, c = v / WB, k2 = v % WB;
+      const unsigned s0 = score(c, 2 * k2), s1 = score(c, 2 * k2 + 1);
+      out = s0 | (s0 << 8) | (s1 << 16) | (s1 << 24);
+    }
+    prof[idx] = out;
+  }
+}
+
+struct K1SParams {
+  const uint16_t* scols;        // stream columns (db_pack.h)
+  const int64_t*  stream_off;
+  const int32_t*  stream_ncols;
+  const int64_t*  stream_pair0;
+  int             n_streams;
+  int             n_items;      // warp-items: ceil(n_streams / (32/g))
+  const unsigned* prof;         // npass x SProf<R>::WORDS
+  int             npass;
+  int             g, g_log2;    // lanes per stream
+  uint2*          bnd;          // multi-pass only: per warp slot, bnd_stride columns of (H, V)
+  long long       bnd_stride;
+  unsigned*       counter;      // work queue head
+  unsigned*       raw;          // [pair][g] packed biased running maxima
+  unsigned        BB, OE32, GE2, one;
+};
+
+constexpr int K1S_WARPS = 8;
+
+template <int R>
+constexpr size_t k1s_smem_bytes() {
+  return (size_t)SProf<R>::WORDS * 4 + (size_t)K1S_WARPS * (128 * 2 + 32 * 8) + 16;
+}
+
+// MULTI = false: the whole query fits one stripe; warps pull items independently.
+// MULTI = true : g == 32, several stripes; the CTA pulls 8 items at a time and reloads the
+//                shared profile between stripes.
+template <int R, bool MULTI>
+__global__ void __launch_bounds__(K1S_WARPS * 32, 2) k1s(const K1SParams P) {
+  using S = SProf<R>;
+  extern __shared__ __align__(16) unsigned smem_u32[];
+  unsigned* prof_s = smem_u32;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  unsigned short* ring = reinterpret_cast<unsigned short*>(smem_u32 + S::WORDS) + warp * 128;
+  uint2* ring2 = reinterpret_cast<uint2*>(reinterpret_cast<unsigned short*>(smem_u32 + S::WORDS) + K1S_WARPS * 128) + warp * 32;
+  __shared__ unsigned cta_item;
+
+  const int g = MULTI ? 32 : P.g, g_log2 = MULTI ? 5 : P.g_log2;
+  const int lane_g = lane & (g - 1), grp = lane >> g_log2, per_warp = 32 >> g_log2;
+  const int rmask = 4 * g - 1;                       // ring of 4g columns per group (g-step blocks, generous slack)
+  unsigned short* gring = ring + grp * (4 * g);
+  const unsigned BB = P.BB, OE32 = P.OE32, GE2 = P.GE2, one = P.one;
+  const unsigned pa_lane = (unsigned)__cvta_generic_to_shared(prof_s) + lane * 4;
+  const unsigned pb_lane = pa_lane + 32 * S::WA * 128;
+  uint2* bnd = MULTI ? P.bnd + (size_t)(blockIdx.x * K1S_WARPS + warp) * (size_t)P.bnd_stride : nullptr;
+
+  auto load_profile = [&](int pass) {
+    const uint4* src = reinterpret_cast<const uint4*>(P.prof + (size_t)pass * S::WORDS);
+    uint4* dst = reinterpret_cast<uint4*>(prof_s);
+    for (int i = threadIdx.x; i < S::WORDS / 4; i += K1S_WARPS * 32) dst[i] = src[i];
+  };
+  if (!MULTI) { load_profile(0); __syncthreads(); }
+
+  for (;;) {
+    int item;
+    if (MULTI) {
+      __syncthreads();
+      if (threadIdx.x == 0) cta_item = atomicAdd(P.counter, 1u);
+      __syncthreads();
+      if ((long)cta_item * K1S_WARPS >= P.n_items) break;
+      item = (int)cta_item * K1S_WARPS + warp;
+    } else {
+      item = 0;
+      if (lane == 0) item = (int)atomicAdd(P.counter, 1u);
+      item = __shfl_sync(0xffffffffu, item, 0);
+      if (item >= P.n_items) break;
+    }
+    const long st = (long)item * per_warp + grp;
+    const bool valid = item < P.n_items && st < P.n_streams;
+    const int ncols = valid ? P.stream_ncols[st] : 0;
+    const long pair0 = valid ? (long)P.stream_pair0[st] : 0;
+    const unsigned short* cp = P.scols + (valid ? P.stream_off[st] : 0);
+    int maxcols = ncols;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) maxcols = max(maxcols, __shfl_xor_sync(0xffffffffu, maxcols, o));
+    const int nsteps = maxcols > 0 ? maxcols + g - 1 : 0;
+
+    for (int pass = 0; pass < (MULTI ? P.npass : 1); ++pass) {
+      if (MULTI) { __syncthreads(); load_profile(pass); __syncthreads(); }
+      const bool first = (pass == 0), last = !MULTI || (pass == P.npass - 1);
+      unsigned H[R], G[R];
+#pragma unroll
+      for (int k = 0; k < R; ++k) { H[k] = BB; G[k] = BB; }
+      unsigned out_h = BB, out_v = BB, diag_in = BB, best = BB;
+      long pair_idx = pair0 - 1;
+      __syncwarp();
+      for (int i = lane; i < 128; i += 32) ring[i] = 0;
+      unsigned pre = (lane_g < ncols) ? (unsigned)cp[lane_g] : 0u;
+      uint2 pre_b = make_uint2(BB, BB);
+      if (MULTI && !first && lane < ncols) pre_b = bnd[lane];
+      __syncwarp();
+
+      auto flush = [&]() {
+        if (pair_idx >= pair0) {
+          unsigned* slot = P.raw + ((size_t)pair_idx << g_log2) + lane_g;
+          *slot = (MULTI && !first) ? __vmaxu2(*slot, best) : best;
+        }
+      };
+
+      for (int s = 0; s < nsteps; ++s) {
+        if ((s & (g - 1)) == 0) {                  // every g steps: publish the prefetched block, fetch the next
+          __syncwarp();
+          gring[(s + lane_g) & rmask] = (unsigned short)pre;
+          const int c = s + g + lane_g;
+          pre = (c < ncols) ? (unsigned)cp[c] : 0u;
+          if (MULTI) {
+            ring2[lane] = pre_b;
+            pre_b = make_uint2(BB, BB);
+            if (!first && c < ncols) pre_b = bnd[c];
+          }
+          __syncwarp();
+        }
+        const unsigned cw = gring[(s - lane_g) & rmask];
+        unsigned h_up = __shfl_up_sync(0xffffffffu, out_h, 1, g);
+        unsigned v_in = __shfl_up_sync(0xffffffffu, out_v, 1, g);
+        if (lane_g == 0) {
+          h_up = BB; v_in = BB;
+          if (MULTI && !first) { const uint2 b = ring2[s & 31]; h_up = b.x; v_in = b.y; }
+        }
+        if (cw & 0x80u) {                          // first column of a new pair: flush, reset the rows
+          flush();
+          ++pair_idx; best = BB; diag_in = BB;
+#pragma unroll
+          for (int k = 0; k < R; ++k) { H[k] = BB; G[k] = BB; }
+        }
+        const unsigned aoff = pa_lane + (cw & 0x1fu) * (S::WA * 128);
+        const unsigned boff = pb_lane + ((cw >> 8) & 0x1fu) * (S::WB * 128);
+        unsigned d = diag_in;
+        diag_in = h_up;
+        unsigned V = v_in;
+        unsigned wA = 0, wB = 0, hprev = BB;
+#pragma unroll
+        for (int k = 0; k < R; ++k) {
+          if ((k & 3) == 0) wA = lds32(aoff + (k >> 2) * 128);
+          if ((k & 1) == 0) wB = lds32(boff + (k >> 1) * 128);
+          unsigned t = add_byte(wA, 1u << (8 * (k & 3)), d);
+          t = (k & 1) ? add_hi_hi(wB, t) : add_hi_lo(wB, t);
+          const unsigned ef = __vimax3_u16x2(G[k], V, BB);
+          const unsigned h = __vmaxu2(t, ef);
+          d = H[k];
+          H[k] = h;
+          const unsigned u = add_fma(h, one, OE32);
+          G[k] = __viaddmax_u16x2(G[k], GE2, u);
+          V = __viaddmax_u16x2(V, GE2, u);
+          if (k & 1) best = __vimax3_u16x2(best, hprev, h); else hprev = h;
+        }
+        out_h = H[R - 1];
+        out_v = V;
+        if (MULTI && !last && lane == 31) {
+          const int j = s - 31;
+          if (j >= 0 && j < ncols) bnd[j] = make_uint2(out_h, out_v);
+        }
+      }
+      flush();
+    }
+  }
+}
+
+// reduce the g per-lane maxima of every pair, un-bias, detect saturation, scatter to file order
+static __global__ void k1s_finalize(const unsigned* __restrict__ raw, long n_pairs, int g_log2, long n_sorted,
+                                    unsigned B, unsigned limit, const int64_t* __restrict__ order,
+                                    int32_t* __restrict__ scores_file, int* __restrict__ rescore_list,
+                                    unsigned* __restrict__ rescore_count) {
+  const int g = 1 << g_log2;
+  for (long p = blockIdx.x * (long)blockDim.x + threadIdx.x; p < n_pairs; p += (long)gridDim.x * blockDim.x) {
+    const unsigned* r = raw + ((size_t)p << g_log2);
+    unsigned m = r[0];
+    for (int i = 1; i < g; ++i) m = __vmaxu2(m, r[i]);
+    const unsigned lo = m & 0xffffu, hi = m >> 16;
+    const bool sat = (lo >= limit) || (hi >= limit);
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const long s = 2 * p + h;
+      if (s >= n_sorted) continue;
+      if (sat) {
+        const unsigned slot = atomicAdd(rescore_count, 1u);
+        rescore_list[slot] = (int)s;
+      } else {
+        scores_file[order[s]] = (int32_t)((h ? hi : lo) - B);
+      }
+    }
+  }
+}
+
+}  // namespace swk

@@ -3,6 +3,7 @@
 #include "swgpu_internal.h"
 #include "db_pack.h"
 #include "sw_kernels.cuh"
+#include "sw_k1s.cuh"
 
 #include <cstdio>
 #include <cstdlib>
@@ -16,6 +17,7 @@ namespace {
 using swi::fail;
 
 constexpr int kDefaultLongThreshold = 3072;
+constexpr int kDefaultStreamCols = 1536;
 constexpr int kTileChoices[] = {32, 28, 24, 20, 16};
 
 }  // namespace
@@ -50,6 +52,8 @@ void swgpu_db_destroy(swgpu_db_t* db) {
   cudaFree(db->d_chunk_off); cudaFree(db->d_chunk_cols); cudaFree(db->d_scores); cudaFree(db->d_raw);
   cudaFree(db->d_rescore_list); cudaFree(db->d_counters); cudaFree(db->d_bnd1); cudaFree(db->d_bnd3);
   cudaFree(db->d_query); cudaFree(db->d_table); cudaFree(db->d_prof);
+  cudaFree(db->d_scols); cudaFree(db->d_stream_off); cudaFree(db->d_stream_ncols); cudaFree(db->d_stream_pair0);
+  cudaFree(db->d_raw_s); cudaFree(db->d_bnd_s); cudaFree(db->d_sprof);
   cudaFree(db->d_keys); cudaFree(db->d_hit_sidx); cudaFree(db->d_sel); cudaFree(db->d_coords); cudaFree(db->d_bnd_loc);
   for (auto& e : db->ev) if (e) cudaEventDestroy(e);
   if (db->s_main) cudaStreamDestroy(db->s_main);
@@ -70,7 +74,8 @@ int swgpu_db_create(swgpu_db_t** out, int device, const int8_t* codes, const int
   const int long_thr = (opts && opts->long_threshold > 0) ? opts->long_threshold : kDefaultLongThreshold;
   swpack_t pk;
   static const int64_t zero_off[1] = {0};
-  if (swpack_build(&pk, codes, n_targets ? offsets : zero_off, n_targets, long_thr) != 0)
+  const int stream_cols = (opts && opts->stream_cols > 0) ? opts->stream_cols : kDefaultStreamCols;
+  if (swpack_build(&pk, codes, n_targets ? offsets : zero_off, n_targets, long_thr, stream_cols) != 0)
     return fail(SWGPU_EINVAL, "database packing failed (residue code outside 0..31, negative length, or out of memory)");
 
   swgpu_db* db = new swgpu_db();
@@ -107,6 +112,21 @@ int swgpu_db_create(swgpu_db_t** out, int device, const int8_t* codes, const int
     CU(cudaMemcpy(db->d_chunk_off, pk.chunk_off, sizeof(int64_t) * ((size_t)pk.n_chunks + 1), cudaMemcpyHostToDevice));
     CU(cudaMemcpy(db->d_chunk_cols, pk.chunk_cols, sizeof(int32_t) * (size_t)pk.n_chunks, cudaMemcpyHostToDevice));
 
+    // streams
+    db->n_pairs = pk.n_pairs; db->n_streams = pk.n_streams; db->max_stream_cols = pk.max_stream_cols;
+    db->use_old_k1 = (opts && opts->use_chunk_kernel) ? 1 : 0;
+    if ((r = dalloc(db, &db->d_scols, (size_t)pk.scols_len + 64))) return r;
+    if ((r = dalloc(db, &db->d_stream_off, (size_t)pk.n_streams + 1))) return r;
+    if ((r = dalloc(db, &db->d_stream_ncols, (size_t)pk.n_streams))) return r;
+    if ((r = dalloc(db, &db->d_stream_pair0, (size_t)pk.n_streams))) return r;
+    if ((r = dalloc(db, &db->d_raw_s, (size_t)pk.n_pairs * 32))) return r;
+    CU(cudaMemcpy(db->d_scols, pk.scols, sizeof(uint16_t) * (size_t)pk.scols_len, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(db->d_stream_off, pk.stream_off, sizeof(int64_t) * ((size_t)pk.n_streams + 1), cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(db->d_stream_ncols, pk.stream_ncols, sizeof(int32_t) * (size_t)pk.n_streams, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(db->d_stream_pair0, pk.stream_pair0, sizeof(int64_t) * (size_t)pk.n_streams, cudaMemcpyHostToDevice));
+    db->k1s_grid = db->sm_count * 2;
+    db->bnd_s_stride = ((long long)std::max<int32_t>(pk.max_stream_cols, 64) + 63) & ~63ll;
+    if ((r = dalloc(db, &db->d_bnd_s, (size_t)db->k1s_grid * swk::K1S_WARPS * (size_t)db->bnd_s_stride))) return r;
     // persistent grids: K1 two CTAs of 8 warps per SM; K3 eight CTAs of 4 warps per SM at most
     db->k1_grid = (int)std::min<int64_t>((int64_t)db->sm_count * 2, (pk.n_chunks + swk::K1_WARPS - 1) / swk::K1_WARPS);
     db->k1_grid = std::max(db->k1_grid, 1);
@@ -150,6 +170,56 @@ int launch_k3(swgpu_db* db, cudaStream_t st, const swk::K3Params& P, int lq) {
   return SWGPU_OK;
 }
 
+// K1S plan: lanes per target pair (g), query rows per lane (R), stripes (npass).
+// Cost model: padded rows x (cell work + per-step overhead / R); ties go to the larger g (more parallel items).
+struct K1SPlan { int g, g_log2, R, npass; };
+
+K1SPlan plan_k1s(int64_t lq, int64_t n_streams, int warp_slots) {
+  K1SPlan best{32, 5, 32, 1}; double best_cost = -1;
+  for (int gl = 3; gl <= 5; ++gl) {
+    const int g = 1 << gl;
+    int R = (int)((lq + g - 1) / g); R += R & 1; if (R < 8) R = 8;
+    if (R > 32) continue;
+    double cost = (double)g * R * (9.0 * R + 16.0) / R;
+    const double items = (double)n_streams * g / 32.0;                 // few items -> idle warps
+    if (items < 2.0 * warp_slots) cost *= (2.0 * warp_slots) / std::max(items, 1.0);
+    if (best_cost < 0 || cost <= best_cost) { best_cost = cost; best = K1SPlan{g, gl, R, 1}; }
+  }
+  if (best_cost < 0) {
+    for (int R = 24; R <= 32; R += 2) {
+      const int np = (int)((lq + 32 * R - 1) / (32 * R));
+      const double cost = (double)np * 32 * R * (9.0 * R + 18.0) / R;
+      if (best_cost < 0 || cost < best_cost) { best_cost = cost; best = K1SPlan{32, 5, R, np}; }
+    }
+  }
+  return best;
+}
+
+template <int R, bool MULTI>
+int launch_k1s_t(swgpu_db* db, const swk::K1SParams& P) {
+  const size_t smem = swk::k1s_smem_bytes<R>();
+  static thread_local bool attr_done[8] = {};
+  if (!attr_done[db->device & 7]) {
+    CU(cudaFuncSetAttribute(swk::k1s<R, MULTI>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    attr_done[db->device & 7] = true;
+  }
+  swk::k1s<R, MULTI><<<db->k1s_grid, swk::K1S_WARPS * 32, smem, db->s_main>>>(P);
+  CU(cudaGetLastError());
+  return SWGPU_OK;
+}
+
+int launch_k1s(swgpu_db* db, const swk::K1SParams& P, int R, bool multi) {
+#define K1S_CASE(r) case r: return multi ? launch_k1s_t<r, true>(db, P) : launch_k1s_t<r, false>(db, P);
+#define K1S_CASE1(r) case r: return launch_k1s_t<r, false>(db, P);
+  switch (R) {
+    K1S_CASE1(8) K1S_CASE1(10) K1S_CASE1(12) K1S_CASE1(14) K1S_CASE1(16) K1S_CASE1(18) K1S_CASE1(20) K1S_CASE1(22)
+    K1S_CASE(24) K1S_CASE(26) K1S_CASE(28) K1S_CASE(30) K1S_CASE(32)
+    default: return fail(SWGPU_EINVAL, "no k1s instantiation for R=%d", R);
+  }
+#undef K1S_CASE
+#undef K1S_CASE1
+}
+
 int pick_tile_rows(int64_t lq) {
   int best_r = kTileChoices[0]; int64_t best_pad = -1;
   for (int r : kTileChoices) {
@@ -186,11 +256,22 @@ int run_search(swgpu_db* db, const int8_t* query, int64_t lq, const int8_t* tabl
   CU(cudaEventRecord(e[7], db->s_main));
 
   const unsigned B = 128u + (unsigned)(-oe) + (unsigned)(-ge);
-  const bool use16 = (B <= 16384u) && db->n_chunks > 0 && lq > 0;
+  const bool use_s = !db->use_old_k1;
+  const bool use16 = (B <= 16384u) && (use_s ? db->n_streams > 0 : db->n_chunks > 0) && lq > 0;
+  const K1SPlan plan = plan_k1s(std::max<int64_t>(lq, 1), db->n_streams, db->k1s_grid * swk::K1S_WARPS);
   const int R = pick_tile_rows(lq);
   const int ntiles = lq > 0 ? (int)((lq + R - 1) / R) : 0;
-  st.tile_rows = use16 ? R : 0;
-  if (use16) {
+  st.tile_rows = use16 ? (use_s ? plan.R : R) : 0;
+  st.lanes_per_pair = (use16 && use_s) ? plan.g : 0; st.passes = (use16 && use_s) ? plan.npass : 0;
+  if (use16 && use_s) {
+    const size_t need = (size_t)plan.npass * 32 * ((plan.R + 3) / 4 + plan.R / 2) * 32;
+    if (need > db->sprof_cap) {
+      if (db->d_sprof) { cudaFree(db->d_sprof); db->d_sprof = nullptr; }
+      db->sprof_cap = need + need / 2;
+      CU(cudaMalloc((void**)&db->d_sprof, db->sprof_cap * sizeof(unsigned)));
+    }
+  }
+  if (use16 && !use_s) {
     const size_t need = (size_t)ntiles * 32 * (((R / 4) | 1) + ((R / 2) | 1));
     if (need > db->prof_cap) {
       if (db->d_prof) { cudaFree(db->d_prof); db->d_prof = nullptr; }
@@ -211,7 +292,31 @@ int run_search(swgpu_db* db, const int8_t* query, int64_t lq, const int8_t* tabl
     P3.plain = db->d_plain; P3.plain_off = db->d_plain_off; P3.query = db->d_query; P3.lq = (int)lq;
     P3.table = db->d_table; P3.oe = oe; P3.ge = ge; P3.bnd = db->d_bnd3; P3.bnd_stride = db->bnd3_stride;
     P3.order = db->d_order; P3.scores_file = db->d_scores; P3.one = 1u;
-    if (use16) {
+    if (use16 && use_s) {
+      // systolic kernel over ALL targets (streams of paired targets), then 32-bit rescoring of saturated pairs
+      swk::build_sprofile<<<std::min(2048, (int)((size_t)plan.npass * 24 * 1024 / 256) + 1), 256, 0, db->s_main>>>(
+          db->d_query, (int)lq, db->d_table, plan.R, plan.g, plan.npass, db->d_sprof);
+      CU(cudaGetLastError()); st.kernel_launches++;
+      swk::K1SParams PS; memset(&PS, 0, sizeof(PS));
+      PS.scols = db->d_scols; PS.stream_off = db->d_stream_off; PS.stream_ncols = db->d_stream_ncols;
+      PS.stream_pair0 = db->d_stream_pair0; PS.n_streams = (int)db->n_streams;
+      const int per_warp = 32 / plan.g;
+      PS.n_items = (int)((db->n_streams + per_warp - 1) / per_warp);
+      PS.prof = db->d_sprof; PS.npass = plan.npass; PS.g = plan.g; PS.g_log2 = plan.g_log2;
+      PS.bnd = db->d_bnd_s; PS.bnd_stride = db->bnd_s_stride; PS.counter = db->d_counters + 0; PS.raw = db->d_raw_s;
+      PS.BB = B | (B << 16); PS.OE32 = (unsigned)(oe * 65537); PS.GE2 = ((unsigned)ge & 0xffffu) * 0x10001u; PS.one = 1u;
+      int r = launch_k1s(db, PS, plan.R, plan.npass > 1); if (r) return r;
+      st.kernel_launches++;
+      swk::k1s_finalize<<<(int)std::min<int64_t>((db->n_pairs + 255) / 256, 4096), 256, 0, db->s_main>>>(
+          db->d_raw_s, (long)db->n_pairs, plan.g_log2, (long)db->n, B, 65535u - 129u, db->d_order, db->d_scores,
+          db->d_rescore_list, db->d_counters + 2);
+      CU(cudaGetLastError()); st.kernel_launches++;
+      CU(cudaEventRecord(e[1], db->s_main));
+      swk::K3Params PR = P3; PR.worklist = db->d_rescore_list; PR.work_count = db->d_counters + 2; PR.counter = db->d_counters + 3;
+      r = launch_k3(db, db->s_main, PR, (int)lq); if (r) return r;
+      st.kernel_launches++;
+      CU(cudaEventRecord(e[2], db->s_main));
+    } else if (use16) {
       // long targets on the aux stream, concurrently with K1
       CU(cudaEventRecord(e[3], db->s_main));
       if (db->n_long > 0) {
@@ -273,9 +378,10 @@ int run_search(swgpu_db* db, const int8_t* query, int64_t lq, const int8_t* tabl
     if (use16) {
       CU(cudaEventElapsedTime(&ms, e[0], e[1])); st.ms_inter = ms;
       CU(cudaEventElapsedTime(&ms, e[1], e[2])); st.ms_rescore = ms;
-      if (db->n_long > 0) { CU(cudaEventElapsedTime(&ms, e[3], e[4])); st.ms_intra = ms; }
-      st.n_long = db->n_long;
-      st.cells_intra = lq * db->h_len_sorted_prefix[db->n_long];
+      const int64_t n_long = use_s ? 0 : db->n_long;
+      if (n_long > 0) { CU(cudaEventElapsedTime(&ms, e[3], e[4])); st.ms_intra = ms; }
+      st.n_long = n_long;
+      st.cells_intra = lq * db->h_len_sorted_prefix[n_long];
       st.cells_inter = st.cells - st.cells_intra;
       unsigned nres = 0;
       CU(cudaMemcpy(&nres, db->d_counters + 2, sizeof(unsigned), cudaMemcpyDeviceToHost));

@@ -34,6 +34,17 @@ struct swgpu_db {
   uint2*    d_cols = nullptr;
   int64_t*  d_chunk_off = nullptr;
   int32_t*  d_chunk_cols = nullptr;
+  // streams of paired targets (systolic kernel K1S)
+  uint16_t* d_scols = nullptr;
+  int64_t*  d_stream_off = nullptr;
+  int32_t*  d_stream_ncols = nullptr;
+  int64_t*  d_stream_pair0 = nullptr;
+  int64_t   n_pairs = 0, n_streams = 0;
+  int32_t   max_stream_cols = 0;
+  unsigned* d_raw_s = nullptr;         // n_pairs * 32
+  uint2*    d_bnd_s = nullptr;  long long bnd_s_stride = 0;  int k1s_grid = 0;
+  unsigned* d_sprof = nullptr;  size_t sprof_cap = 0;
+  int       use_old_k1 = 0;
   // device scratch (per search)
   int32_t*  d_scores = nullptr;        // file order
   unsigned* d_raw = nullptr;           // n_chunks*32
