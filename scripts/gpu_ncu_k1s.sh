@@ -3,7 +3,7 @@ set -x
 mkdir -p gpurun_out
 for lq in 1000 144; do
 timeout 300 python scripts/prof_one.py --lq $lq --reps 2 > gpurun_out/plain_$lq.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:k1s -s 1 -c 1 -f -o gpurun_out/k1s_lq$lq \
+ncu --set full --clock-control none --import-source on -k "regex:^k1s$" -s 1 -c 1 -f -o gpurun_out/k1s_lq$lq \
     python scripts/prof_one.py --lq $lq --reps 2 > gpurun_out/ncu_k1s_$lq.log 2>&1
 done
 ls -la gpurun_out

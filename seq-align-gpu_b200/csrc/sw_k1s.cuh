@@ -74,7 +74,7 @@ struct K1SParams {
   long long       bnd_stride;
   unsigned*       counter;      // work queue head
   unsigned*       raw;          // [pair][g] packed biased running maxima
-  unsigned        BB, OE32, GE2, one;
+  unsigned        BB, BBM, OE2, GE2;   // bias, bias - oe, packed oe, packed ge (u16 x 2)
 };
 
 constexpr int K1S_WARPS = 8;
@@ -101,7 +101,7 @@ __global__ void __launch_bounds__(K1S_WARPS * 32, 2) k1s(const K1SParams P) {
   const int lane_g = lane & (g - 1), grp = lane >> g_log2, per_warp = 32 >> g_log2;
   const int rmask = 4 * g - 1;                       // ring of 4g columns per group (g-step blocks, generous slack)
   unsigned short* gring = ring + grp * (4 * g);
-  const unsigned BB = P.BB, OE32 = P.OE32, GE2 = P.GE2, one = P.one;
+  const unsigned BB = P.BB, BBM = P.BBM, OE2 = P.OE2, GE2 = P.GE2;
   const unsigned pa_lane = (unsigned)__cvta_generic_to_shared(prof_s) + lane * 4;
   const unsigned pb_lane = pa_lane + 32 * S::WA * 128;
   uint2* bnd = MULTI ? P.bnd + (size_t)(blockIdx.x * K1S_WARPS + warp) * (size_t)P.bnd_stride : nullptr;
@@ -142,13 +142,13 @@ __global__ void __launch_bounds__(K1S_WARPS * 32, 2) k1s(const K1SParams P) {
       const bool first = (pass == 0), last = !MULTI || (pass == P.npass - 1);
       unsigned H[R], G[R];
 #pragma unroll
-      for (int k = 0; k < R; ++k) { H[k] = BB; G[k] = BB; }
-      unsigned out_h = BB, out_v = BB, diag_in = BB, best = BB;
+      for (int k = 0; k < R; ++k) { H[k] = BB; G[k] = BBM; }
+      unsigned out_h = BB, out_v = BBM, diag_in = BB, best = BB;
       long pair_idx = pair0 - 1;
       __syncwarp();
       for (int i = lane; i < 128; i += 32) ring[i] = 0;
       unsigned pre = (lane_g < ncols) ? (unsigned)cp[lane_g] : 0u;
-      uint2 pre_b = make_uint2(BB, BB);
+      uint2 pre_b = make_uint2(BB, BBM);
       if (MULTI && !first && lane < ncols) pre_b = bnd[lane];
       __syncwarp();
 
@@ -167,7 +167,7 @@ __global__ void __launch_bounds__(K1S_WARPS * 32, 2) k1s(const K1SParams P) {
           pre = (c < ncols) ? (unsigned)cp[c] : 0u;
           if (MULTI) {
             ring2[lane] = pre_b;
-            pre_b = make_uint2(BB, BB);
+            pre_b = make_uint2(BB, BBM);
             if (!first && c < ncols) pre_b = bnd[c];
           }
           __syncwarp();
@@ -176,35 +176,44 @@ __global__ void __launch_bounds__(K1S_WARPS * 32, 2) k1s(const K1SParams P) {
         unsigned h_up = __shfl_up_sync(0xffffffffu, out_h, 1, g);
         unsigned v_in = __shfl_up_sync(0xffffffffu, out_v, 1, g);
         if (lane_g == 0) {
-          h_up = BB; v_in = BB;
+          h_up = BB; v_in = BBM;
           if (MULTI && !first) { const uint2 b = ring2[s & 31]; h_up = b.x; v_in = b.y; }
         }
         if (cw & 0x80u) {                          // first column of a new pair: flush, reset the rows
           flush();
           ++pair_idx; best = BB; diag_in = BB;
 #pragma unroll
-          for (int k = 0; k < R; ++k) { H[k] = BB; G[k] = BB; }
+          for (int k = 0; k < R; ++k) { H[k] = BB; G[k] = BBM; }
         }
         const unsigned aoff = pa_lane + (cw & 0x1fu) * (S::WA * 128);
         const unsigned boff = pb_lane + ((cw >> 8) & 0x1fu) * (S::WB * 128);
-        unsigned d = diag_in;
-        diag_in = h_up;
+        // Cell update.  G and V are kept SHIFTED by -oe (Gs = G - oe, Vs = V - oe), which turns
+        //   G' = max(G + ge, H + oe)  into  Gs' = max(Gs + ge, H)          (no separate H + oe add)
+        //   H  = max(0, t, G, V)      into  H   = max(max3(Gs, Vs, 0 - oe) + oe, t)
+        // i.e. per cell pair: 2 IDP (FMA pipe) + VIMNMX3 + 3 VIADDMNMX + half a VIMNMX3 (ALU pipe).
+        // t of row k+1 is formed from H[k] of the previous column BEFORE H[k] is overwritten, so the
+        // row registers are updated in place (no register moves).
         unsigned V = v_in;
-        unsigned wA = 0, wB = 0, hprev = BB;
+        unsigned wA = lds32(aoff), wB = lds32(boff), hprev = BB;
+        unsigned t = add_hi_lo(wB, add_byte(wA, 1u, diag_in));
+        diag_in = h_up;
 #pragma unroll
         for (int k = 0; k < R; ++k) {
-          if ((k & 3) == 0) wA = lds32(aoff + (k >> 2) * 128);
-          if ((k & 1) == 0) wB = lds32(boff + (k >> 1) * 128);
-          unsigned t = add_byte(wA, 1u << (8 * (k & 3)), d);
-          t = (k & 1) ? add_hi_hi(wB, t) : add_hi_lo(wB, t);
-          const unsigned ef = __vimax3_u16x2(G[k], V, BB);
-          const unsigned h = __vmaxu2(t, ef);
-          d = H[k];
+          unsigned tn = 0;
+          if (k + 1 < R) {
+            const int k1 = k + 1;
+            if ((k1 & 3) == 0) wA = lds32(aoff + (k1 >> 2) * 128);
+            if ((k1 & 1) == 0) wB = lds32(boff + (k1 >> 1) * 128);
+            tn = add_byte(wA, 1u << (8 * (k1 & 3)), H[k]);
+            tn = (k1 & 1) ? add_hi_hi(wB, tn) : add_hi_lo(wB, tn);
+          }
+          const unsigned ef = __vimax3_u16x2(G[k], V, BBM);
+          const unsigned h = __viaddmax_u16x2(ef, OE2, t);
           H[k] = h;
-          const unsigned u = add_fma(h, one, OE32);
-          G[k] = __viaddmax_u16x2(G[k], GE2, u);
-          V = __viaddmax_u16x2(V, GE2, u);
+          G[k] = __viaddmax_u16x2(G[k], GE2, h);
+          V = __viaddmax_u16x2(V, GE2, h);
           if (k & 1) best = __vimax3_u16x2(best, hprev, h); else hprev = h;
+          t = tn;
         }
         out_h = H[R - 1];
         out_v = V;

@@ -304,7 +304,8 @@ int run_search(swgpu_db* db, const int8_t* query, int64_t lq, const int8_t* tabl
       PS.n_items = (int)((db->n_streams + per_warp - 1) / per_warp);
       PS.prof = db->d_sprof; PS.npass = plan.npass; PS.g = plan.g; PS.g_log2 = plan.g_log2;
       PS.bnd = db->d_bnd_s; PS.bnd_stride = db->bnd_s_stride; PS.counter = db->d_counters + 0; PS.raw = db->d_raw_s;
-      PS.BB = B | (B << 16); PS.OE32 = (unsigned)(oe * 65537); PS.GE2 = ((unsigned)ge & 0xffffu) * 0x10001u; PS.one = 1u;
+      PS.BB = B * 0x10001u; PS.BBM = (B + (unsigned)(-oe)) * 0x10001u;
+      PS.OE2 = ((unsigned)oe & 0xffffu) * 0x10001u; PS.GE2 = ((unsigned)ge & 0xffffu) * 0x10001u;
       int r = launch_k1s(db, PS, plan.R, plan.npass > 1); if (r) return r;
       st.kernel_launches++;
       swk::k1s_finalize<<<(int)std::min<int64_t>((db->n_pairs + 255) / 256, 4096), 256, 0, db->s_main>>>(
