@@ -137,6 +137,9 @@ static int build_streams(swpack_t *p, int32_t stream_cols)
         }
     }
     p->stream_off[n_streams] = off;
+    p->n_long_streams = 0;
+    while (p->n_long_streams < n_streams && p->stream_ncols[p->n_long_streams] > SWPACK_LONG_STREAM_COLS) p->n_long_streams++;
+    p->n_long_pairs = p->n_long_streams < n_streams ? p->stream_pair0[p->n_long_streams] : n_pairs;
     p->scols_len = off;
     p->max_stream_cols = maxc;
     p->scols = (uint16_t *)calloc((size_t)(off ? off : 1), sizeof(uint16_t));

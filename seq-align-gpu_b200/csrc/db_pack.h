@@ -26,6 +26,8 @@
 extern "C" {
 #endif
 
+#define SWPACK_LONG_STREAM_COLS 4096
+
 typedef struct {
     int64_t  n_targets, n_residues;
     int64_t  n_long;          /* sorted[0 .. n_long) go to the intra-sequence kernel */
@@ -42,6 +44,8 @@ typedef struct {
     /* streams (systolic kernel): all targets, sorted order, paired */
     int64_t  n_pairs, n_streams;
     int32_t  max_stream_cols;
+    int64_t  n_long_streams;  /* leading streams with more than SWPACK_LONG_STREAM_COLS columns */
+    int64_t  n_long_pairs;    /* pairs inside those streams                                   */
     uint16_t *scols;          /* [scols_len] stream columns, each stream 64-column aligned */
     int64_t  scols_len;
     int64_t *stream_off;      /* [n_streams+1] start column of each stream in scols      */

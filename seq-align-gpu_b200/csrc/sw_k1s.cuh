@@ -65,11 +65,13 @@ struct K1SParams {
   const int64_t*  stream_off;
   const int32_t*  stream_ncols;
   const int64_t*  stream_pair0;
-  int             n_streams;
+  int             stream_begin; // first stream of this launch
+  int             n_streams;    // streams in this launch
   int             n_items;      // warp-items: ceil(n_streams / (32/g))
   const unsigned* prof;         // npass x SProf<R>::WORDS
   int             npass;
   int             g, g_log2;    // lanes per stream
+  int             active_warps; // single-pass only: warps of a CTA that pull work (1 for the long-stream launch)
   uint2*          bnd;          // multi-pass only: per warp slot, bnd_stride columns of (H, V)
   long long       bnd_stride;
   unsigned*       counter;      // work queue head
@@ -111,7 +113,7 @@ __global__ void __launch_bounds__(K1S_WARPS * 32, 2) k1s(const K1SParams P) {
     uint4* dst = reinterpret_cast<uint4*>(prof_s);
     for (int i = threadIdx.x; i < S::WORDS / 4; i += K1S_WARPS * 32) dst[i] = src[i];
   };
-  if (!MULTI) { load_profile(0); __syncthreads(); }
+  if (!MULTI) { load_profile(0); __syncthreads(); if (warp >= P.active_warps) return; }
 
   for (;;) {
     int item;
@@ -127,8 +129,9 @@ __global__ void __launch_bounds__(K1S_WARPS * 32, 2) k1s(const K1SParams P) {
       item = __shfl_sync(0xffffffffu, item, 0);
       if (item >= P.n_items) break;
     }
-    const long st = (long)item * per_warp + grp;
-    const bool valid = item < P.n_items && st < P.n_streams;
+    const long st_local = (long)item * per_warp + grp;
+    const bool valid = item < P.n_items && st_local < P.n_streams;
+    const long st = P.stream_begin + st_local;
     const int ncols = valid ? P.stream_ncols[st] : 0;
     const long pair0 = valid ? (long)P.stream_pair0[st] : 0;
     const unsigned short* cp = P.scols + (valid ? P.stream_off[st] : 0);
@@ -228,12 +231,12 @@ __global__ void __launch_bounds__(K1S_WARPS * 32, 2) k1s(const K1SParams P) {
 }
 
 // reduce the g per-lane maxima of every pair, un-bias, detect saturation, scatter to file order
-static __global__ void k1s_finalize(const unsigned* __restrict__ raw, long n_pairs, int g_log2, long n_sorted,
+static __global__ void k1s_finalize(const unsigned* __restrict__ raw, long pair_begin, long n_pairs, int g_log2, long n_sorted,
                                     unsigned B, unsigned limit, const int64_t* __restrict__ order,
                                     int32_t* __restrict__ scores_file, int* __restrict__ rescore_list,
                                     unsigned* __restrict__ rescore_count) {
   const int g = 1 << g_log2;
-  for (long p = blockIdx.x * (long)blockDim.x + threadIdx.x; p < n_pairs; p += (long)gridDim.x * blockDim.x) {
+  for (long p = pair_begin + blockIdx.x * (long)blockDim.x + threadIdx.x; p < n_pairs; p += (long)gridDim.x * blockDim.x) {
     const unsigned* r = raw + ((size_t)p << g_log2);
     unsigned m = r[0];
     for (int i = 1; i < g; ++i) m = __vmaxu2(m, r[i]);

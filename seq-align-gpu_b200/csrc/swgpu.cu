@@ -53,7 +53,7 @@ void swgpu_db_destroy(swgpu_db_t* db) {
   cudaFree(db->d_rescore_list); cudaFree(db->d_counters); cudaFree(db->d_bnd1); cudaFree(db->d_bnd3);
   cudaFree(db->d_query); cudaFree(db->d_table); cudaFree(db->d_prof);
   cudaFree(db->d_scols); cudaFree(db->d_stream_off); cudaFree(db->d_stream_ncols); cudaFree(db->d_stream_pair0);
-  cudaFree(db->d_raw_s); cudaFree(db->d_bnd_s); cudaFree(db->d_sprof);
+  cudaFree(db->d_raw_s); cudaFree(db->d_bnd_s); cudaFree(db->d_sprof); cudaFree(db->d_sprof2);
   cudaFree(db->d_keys); cudaFree(db->d_hit_sidx); cudaFree(db->d_sel); cudaFree(db->d_coords); cudaFree(db->d_bnd_loc);
   for (auto& e : db->ev) if (e) cudaEventDestroy(e);
   if (db->s_main) cudaStreamDestroy(db->s_main);
@@ -114,6 +114,7 @@ int swgpu_db_create(swgpu_db_t** out, int device, const int8_t* codes, const int
 
     // streams
     db->n_pairs = pk.n_pairs; db->n_streams = pk.n_streams; db->max_stream_cols = pk.max_stream_cols;
+    db->n_long_streams = pk.n_long_streams; db->n_long_pairs = pk.n_long_pairs;
     db->use_old_k1 = (opts && opts->use_chunk_kernel) ? 1 : 0;
     if ((r = dalloc(db, &db->d_scols, (size_t)pk.scols_len + 64))) return r;
     if ((r = dalloc(db, &db->d_stream_off, (size_t)pk.n_streams + 1))) return r;
@@ -196,21 +197,21 @@ K1SPlan plan_k1s(int64_t lq, int64_t n_streams, int warp_slots) {
 }
 
 template <int R, bool MULTI>
-int launch_k1s_t(swgpu_db* db, const swk::K1SParams& P) {
+int launch_k1s_t(swgpu_db* db, const swk::K1SParams& P, cudaStream_t stream, int grid) {
   const size_t smem = swk::k1s_smem_bytes<R>();
   static thread_local bool attr_done[8] = {};
   if (!attr_done[db->device & 7]) {
     CU(cudaFuncSetAttribute(swk::k1s<R, MULTI>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attr_done[db->device & 7] = true;
   }
-  swk::k1s<R, MULTI><<<db->k1s_grid, swk::K1S_WARPS * 32, smem, db->s_main>>>(P);
+  swk::k1s<R, MULTI><<<grid, swk::K1S_WARPS * 32, smem, stream>>>(P);
   CU(cudaGetLastError());
   return SWGPU_OK;
 }
 
-int launch_k1s(swgpu_db* db, const swk::K1SParams& P, int R, bool multi) {
-#define K1S_CASE(r) case r: return multi ? launch_k1s_t<r, true>(db, P) : launch_k1s_t<r, false>(db, P);
-#define K1S_CASE1(r) case r: return launch_k1s_t<r, false>(db, P);
+int launch_k1s(swgpu_db* db, const swk::K1SParams& P, int R, bool multi, cudaStream_t stream, int grid) {
+#define K1S_CASE(r) case r: return multi ? launch_k1s_t<r, true>(db, P, stream, grid) : launch_k1s_t<r, false>(db, P, stream, grid);
+#define K1S_CASE1(r) case r: return launch_k1s_t<r, false>(db, P, stream, grid);
   switch (R) {
     K1S_CASE1(8) K1S_CASE1(10) K1S_CASE1(12) K1S_CASE1(14) K1S_CASE1(16) K1S_CASE1(18) K1S_CASE1(20) K1S_CASE1(22)
     K1S_CASE(24) K1S_CASE(26) K1S_CASE(28) K1S_CASE(30) K1S_CASE(32)
@@ -271,6 +272,21 @@ int run_search(swgpu_db* db, const int8_t* query, int64_t lq, const int8_t* tabl
       CU(cudaMalloc((void**)&db->d_sprof, db->sprof_cap * sizeof(unsigned)));
     }
   }
+  // Long streams (one target pair of thousands of columns) are latency-bound on their serial column
+  // chain: when the bulk plan uses fewer than 32 lanes per pair they get their own launch with all
+  // 32 lanes and the fewest rows per lane, started first on the second stream.
+  K1SPlan plan_long = plan;
+  const bool split_long = use16 && use_s && plan.npass == 1 && plan.g < 32 && db->n_long_streams > 0;
+  if (split_long) {
+    int R = (int)((lq + 31) / 32); R += R & 1; if (R < 8) R = 8;
+    plan_long = K1SPlan{32, 5, R, 1};
+    const size_t need = (size_t)32 * ((R + 3) / 4 + R / 2) * 32;
+    if (need > db->sprof2_cap) {
+      if (db->d_sprof2) { cudaFree(db->d_sprof2); db->d_sprof2 = nullptr; }
+      db->sprof2_cap = need * 2;
+      CU(cudaMalloc((void**)&db->d_sprof2, db->sprof2_cap * sizeof(unsigned)));
+    }
+  }
   if (use16 && !use_s) {
     const size_t need = (size_t)ntiles * 32 * (((R / 4) | 1) + ((R / 2) | 1));
     if (need > db->prof_cap) {
@@ -294,24 +310,51 @@ int run_search(swgpu_db* db, const int8_t* query, int64_t lq, const int8_t* tabl
     P3.order = db->d_order; P3.scores_file = db->d_scores; P3.one = 1u;
     if (use16 && use_s) {
       // systolic kernel over ALL targets (streams of paired targets), then 32-bit rescoring of saturated pairs
+      swk::K1SParams PS; memset(&PS, 0, sizeof(PS));
+      PS.scols = db->d_scols; PS.stream_off = db->d_stream_off; PS.stream_ncols = db->d_stream_ncols;
+      PS.stream_pair0 = db->d_stream_pair0;
+      PS.bnd = db->d_bnd_s; PS.bnd_stride = db->bnd_s_stride;
+      PS.BB = B * 0x10001u; PS.BBM = (B + (unsigned)(-oe)) * 0x10001u;
+      PS.OE2 = ((unsigned)oe & 0xffffu) * 0x10001u; PS.GE2 = ((unsigned)ge & 0xffffu) * 0x10001u;
+      const int fin_grid = (int)std::min<int64_t>((db->n_pairs + 255) / 256, 4096);
+      int r = SWGPU_OK;
+      const int64_t nls = split_long ? db->n_long_streams : 0, nlp = split_long ? db->n_long_pairs : 0;
+      if (split_long) {
+        CU(cudaEventRecord(e[3], db->s_main));
+        CU(cudaStreamWaitEvent(db->s_aux, e[3], 0));
+        swk::build_sprofile<<<32, 256, 0, db->s_aux>>>(db->d_query, (int)lq, db->d_table, plan_long.R, 32, 1, db->d_sprof2);
+        swk::K1SParams PL = PS;
+        PL.stream_begin = 0; PL.n_streams = (int)nls; PL.n_items = (int)nls; PL.prof = db->d_sprof2; PL.npass = 1;
+        PL.g = 32; PL.g_log2 = 5; PL.counter = db->d_counters + 1; PL.raw = db->d_raw_s;
+        PL.active_warps = 1;                                  // one long stream per CTA: spread them over the SMs
+        r = launch_k1s(db, PL, plan_long.R, false, db->s_aux, (int)std::min<int64_t>(nls, db->k1s_grid));
+        if (r) return r;
+        swk::k1s_finalize<<<std::max(1, (int)((nlp + 255) / 256)), 256, 0, db->s_aux>>>(
+            db->d_raw_s, 0, (long)nlp, 5, (long)db->n, B, 65535u - 129u, db->d_order, db->d_scores,
+            db->d_rescore_list, db->d_counters + 2);
+        CU(cudaGetLastError()); st.kernel_launches += 3;
+        CU(cudaEventRecord(e[4], db->s_aux));
+      }
       swk::build_sprofile<<<std::min(2048, (int)((size_t)plan.npass * 24 * 1024 / 256) + 1), 256, 0, db->s_main>>>(
           db->d_query, (int)lq, db->d_table, plan.R, plan.g, plan.npass, db->d_sprof);
       CU(cudaGetLastError()); st.kernel_launches++;
-      swk::K1SParams PS; memset(&PS, 0, sizeof(PS));
-      PS.scols = db->d_scols; PS.stream_off = db->d_stream_off; PS.stream_ncols = db->d_stream_ncols;
-      PS.stream_pair0 = db->d_stream_pair0; PS.n_streams = (int)db->n_streams;
       const int per_warp = 32 / plan.g;
-      PS.n_items = (int)((db->n_streams + per_warp - 1) / per_warp);
+      PS.stream_begin = (int)nls; PS.n_streams = (int)(db->n_streams - nls);
+      PS.n_items = (PS.n_streams + per_warp - 1) / per_warp;
       PS.prof = db->d_sprof; PS.npass = plan.npass; PS.g = plan.g; PS.g_log2 = plan.g_log2;
-      PS.bnd = db->d_bnd_s; PS.bnd_stride = db->bnd_s_stride; PS.counter = db->d_counters + 0; PS.raw = db->d_raw_s;
-      PS.BB = B * 0x10001u; PS.BBM = (B + (unsigned)(-oe)) * 0x10001u;
-      PS.OE2 = ((unsigned)oe & 0xffffu) * 0x10001u; PS.GE2 = ((unsigned)ge & 0xffffu) * 0x10001u;
-      int r = launch_k1s(db, PS, plan.R, plan.npass > 1); if (r) return r;
-      st.kernel_launches++;
-      swk::k1s_finalize<<<(int)std::min<int64_t>((db->n_pairs + 255) / 256, 4096), 256, 0, db->s_main>>>(
-          db->d_raw_s, (long)db->n_pairs, plan.g_log2, (long)db->n, B, 65535u - 129u, db->d_order, db->d_scores,
-          db->d_rescore_list, db->d_counters + 2);
-      CU(cudaGetLastError()); st.kernel_launches++;
+      PS.counter = db->d_counters + 0;
+      // the bulk's [pair][g] maxima start after the long launch's [pair][32] region
+      PS.raw = db->d_raw_s + (size_t)nlp * 32 - ((size_t)nlp << plan.g_log2);
+      if (PS.n_streams > 0) {
+        PS.active_warps = swk::K1S_WARPS;
+        r = launch_k1s(db, PS, plan.R, plan.npass > 1, db->s_main, db->k1s_grid); if (r) return r;
+        st.kernel_launches++;
+        swk::k1s_finalize<<<fin_grid, 256, 0, db->s_main>>>(
+            PS.raw, (long)nlp, (long)db->n_pairs, plan.g_log2, (long)db->n, B, 65535u - 129u, db->d_order, db->d_scores,
+            db->d_rescore_list, db->d_counters + 2);
+        CU(cudaGetLastError()); st.kernel_launches++;
+      }
+      if (split_long) CU(cudaStreamWaitEvent(db->s_main, e[4], 0));
       CU(cudaEventRecord(e[1], db->s_main));
       swk::K3Params PR = P3; PR.worklist = db->d_rescore_list; PR.work_count = db->d_counters + 2; PR.counter = db->d_counters + 3;
       r = launch_k3(db, db->s_main, PR, (int)lq); if (r) return r;

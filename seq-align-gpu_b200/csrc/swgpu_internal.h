@@ -42,6 +42,8 @@ struct swgpu_db {
   int64_t   n_pairs = 0, n_streams = 0;
   int32_t   max_stream_cols = 0;
   unsigned* d_raw_s = nullptr;         // n_pairs * 32
+  int64_t   n_long_streams = 0, n_long_pairs = 0;   // leading long streams get their own low-latency launch
+  unsigned* d_sprof2 = nullptr;  size_t sprof2_cap = 0;
   uint2*    d_bnd_s = nullptr;  long long bnd_s_stride = 0;  int k1s_grid = 0;
   unsigned* d_sprof = nullptr;  size_t sprof_cap = 0;
   int       use_old_k1 = 0;
