@@ -260,6 +260,7 @@ struct K3Params {
   const int64_t* order;
   int32_t*       scores_file;
   unsigned       one;
+  int            max_len;      // targets longer than this are left to the wavefront kernel k3w (0 = no limit)
 };
 
 constexpr int K3_WARPS = 4;
@@ -288,6 +289,7 @@ __global__ void __launch_bounds__(K3_WARPS * 32) k3_intra(const K3Params P) {
     const int sidx = P.worklist ? P.worklist[w] : w;
     const int8_t* tp = P.plain + P.plain_off[sidx];
     const int lt = (int)(P.plain_off[sidx + 1] - P.plain_off[sidx]);
+    if (P.max_len > 0 && lt > P.max_len) continue;
     int best = 0;
 
     for (int pass = 0; pass < npass; ++pass) {

@@ -4,6 +4,7 @@
 #include "db_pack.h"
 #include "sw_kernels.cuh"
 #include "sw_k1s.cuh"
+#include "sw_k3w.cuh"
 
 #include <cstdio>
 #include <cstdlib>
@@ -221,6 +222,29 @@ int launch_k1s(swgpu_db* db, const swk::K1SParams& P, int R, bool multi, cudaStr
 #undef K1S_CASE1
 }
 
+// 32-bit rescoring of the device-side list: k3_intra (one warp per target) takes the targets up to
+// kWaveMinLen residues, the wavefront kernel k3w (one CTA per target) the longer ones.
+constexpr int kWaveMinLen = 4096;
+
+int launch_rescore(swgpu_db* db, const swk::K3Params& P3, int lq, int oe, int ge, int* launches) {
+  swk::K3Params PR = P3;
+  PR.worklist = db->d_rescore_list; PR.work_count = db->d_counters + 2; PR.counter = db->d_counters + 3;
+  PR.max_len = kWaveMinLen - 1;
+  int r = launch_k3(db, db->s_main, PR, lq); if (r) return r;
+  ++*launches;
+  if (db->max_len >= kWaveMinLen) {
+    swk::K3WParams PW; memset(&PW, 0, sizeof(PW));
+    PW.sidx_list = db->d_rescore_list; PW.work_count = db->d_counters + 2; PW.counter = db->d_counters + 4;
+    PW.plain = db->d_plain; PW.plain_off = db->d_plain_off; PW.query = db->d_query; PW.lq = lq; PW.table = db->d_table;
+    PW.oe = oe; PW.ge = ge; PW.bnd = db->d_bnd3; PW.bnd_stride = db->bnd3_stride;
+    PW.order = db->d_order; PW.scores_file = db->d_scores; PW.error_flag = db->d_counters + 6; PW.min_len = kWaveMinLen;
+    swk::k3w<false><<<db->sm_count * 2, swk::K3W_WARPS * 32, 0, db->s_main>>>(PW);
+    CU(cudaGetLastError());
+    ++*launches;
+  }
+  return SWGPU_OK;
+}
+
 int pick_tile_rows(int64_t lq) {
   int best_r = kTileChoices[0]; int64_t best_pad = -1;
   for (int r : kTileChoices) {
@@ -356,9 +380,7 @@ int run_search(swgpu_db* db, const int8_t* query, int64_t lq, const int8_t* tabl
       }
       if (split_long) CU(cudaStreamWaitEvent(db->s_main, e[4], 0));
       CU(cudaEventRecord(e[1], db->s_main));
-      swk::K3Params PR = P3; PR.worklist = db->d_rescore_list; PR.work_count = db->d_counters + 2; PR.counter = db->d_counters + 3;
-      r = launch_k3(db, db->s_main, PR, (int)lq); if (r) return r;
-      st.kernel_launches++;
+      r = launch_rescore(db, P3, (int)lq, oe, ge, &st.kernel_launches); if (r) return r;
       CU(cudaEventRecord(e[2], db->s_main));
     } else if (use16) {
       // long targets on the aux stream, concurrently with K1
@@ -395,9 +417,7 @@ int run_search(swgpu_db* db, const int8_t* query, int64_t lq, const int8_t* tabl
       CU(cudaGetLastError()); st.kernel_launches++;
       CU(cudaEventRecord(e[1], db->s_main));
       // 32-bit rescoring of saturated targets (count lives on the device)
-      swk::K3Params PR = P3; PR.worklist = db->d_rescore_list; PR.work_count = db->d_counters + 2; PR.counter = db->d_counters + 3;
-      r = launch_k3(db, db->s_main, PR, (int)lq); if (r) return r;
-      st.kernel_launches++;
+      r = launch_rescore(db, P3, (int)lq, oe, ge, &st.kernel_launches); if (r) return r;
       if (db->n_long > 0) CU(cudaStreamWaitEvent(db->s_main, e[4], 0));
       CU(cudaEventRecord(e[2], db->s_main));
     } else {
@@ -427,8 +447,10 @@ int run_search(swgpu_db* db, const int8_t* query, int64_t lq, const int8_t* tabl
       st.n_long = n_long;
       st.cells_intra = lq * db->h_len_sorted_prefix[n_long];
       st.cells_inter = st.cells - st.cells_intra;
-      unsigned nres = 0;
-      CU(cudaMemcpy(&nres, db->d_counters + 2, sizeof(unsigned), cudaMemcpyDeviceToHost));
+      unsigned ctr[8] = {};
+      CU(cudaMemcpy(ctr, db->d_counters, sizeof(ctr), cudaMemcpyDeviceToHost));
+      if (ctr[6]) return fail(SWGPU_ECUDA, "32-bit wavefront rescoring stalled (internal error)");
+      const unsigned nres = ctr[2];
       st.n_rescored = nres;
       if (nres) {
         std::vector<int> lst(nres);

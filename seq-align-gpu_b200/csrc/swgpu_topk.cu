@@ -15,6 +15,7 @@
 // tracking the first maximum.
 #include "swgpu_internal.h"
 #include "sw_kernels.cuh"
+#include "sw_k3w.cuh"
 
 #include <algorithm>
 #include <cstring>
@@ -93,148 +94,8 @@ __global__ void topk_ranksort(const unsigned long long* __restrict__ keys, const
   if (i < k) { keys_out[rank] = mine; sidx_out[rank] = sidx[i]; }
 }
 
-// ------------------------------------------------------------------------------------------
-// Coordinates.  Same systolic 32-bit recurrence as k3_intra (one warp per hit, lane l owns R3 rows
-// of the current 32*R3-row stripe, the target streams through the lanes, the stripe's bottom row is
-// carried in a linear-space buffer), plus first-maximum tracking.  phase 0 = forward (finds the
-// end cell), phase 1 = the reversed prefixes (finds the start cell).
-// ------------------------------------------------------------------------------------------
-struct LocParams {
-  const int*     sidx;         // [k] sorted positions of the hits
-  int            k;
-  const int8_t*  plain;
-  const int64_t* plain_off;
-  const int8_t*  query;
-  int            lq;
-  const int8_t*  table;
-  int            oe, ge;
-  int2*          bnd;
-  long long      bnd_stride;
-  int4*          coords;       // [k] (q_start, q_end, t_start, t_end); phase 0 writes y,w; phase 1 writes x,z
-  int*           best_out;     // [k] score found by phase 0 (cross-check against the search result)
-  int            phase;
-  unsigned       one;
-};
-
-constexpr int LOC_WARPS = 4;
-constexpr int LOC_R = 8;
-
-__device__ __forceinline__ bool loc_better(int s, int j, int i, int bs, int bj, int bi) {
-  return s > bs || (s == bs && (j < bj || (j == bj && i < bi)));
-}
-
-__global__ void __launch_bounds__(LOC_WARPS * 32) k_locate(const LocParams P) {
-  constexpr int R3 = LOC_R, W = R3 / 4;
-  __shared__ unsigned pl_all[LOC_WARPS][32 * W * 32];
-  __shared__ int8_t tab[32 * 32];
-  for (int i = threadIdx.x; i < 1024; i += blockDim.x) tab[i] = P.table[i];
-  __syncthreads();
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int hit = blockIdx.x * LOC_WARPS + warp;
-  if (hit >= P.k) return;
-  unsigned* pl = pl_all[warp];
-  const unsigned pl_addr = (unsigned)__cvta_generic_to_shared(pl) + lane * 4;
-  int2* bnd = P.bnd + (size_t)hit * (size_t)P.bnd_stride;
-  const int sidx = P.sidx[hit];
-  const int8_t* tp = P.plain + P.plain_off[sidx];
-  int lt = (int)(P.plain_off[sidx + 1] - P.plain_off[sidx]);
-  int lq = P.lq;
-  const int8_t* qp = P.query;
-  int qstep = 1, tstep = 1;
-  if (P.phase == 1) {
-    const int4 c = P.coords[hit];
-    if (c.y < 0) { if (lane == 0) P.coords[hit] = make_int4(-1, -1, -1, -1); return; }
-    lq = c.y + 1; lt = c.w + 1; qp += c.y; tp += c.w; qstep = -1; tstep = -1;
-  }
-  const int oe = P.oe, ge = P.ge;
-  const int npass = (lq + 32 * R3 - 1) / (32 * R3);
-  int best = 0, bj = 0x7fffffff, bi = 0x7fffffff;
-
-  for (int pass = 0; pass < npass; ++pass) {
-    const int row0 = pass * 32 * R3 + lane * R3;
-    __syncwarp();
-    for (int c = 0; c < 32; ++c) {
-#pragma unroll
-      for (int ww = 0; ww < W; ++ww) {
-        unsigned word = 0;
-#pragma unroll
-        for (int b = 0; b < 4; ++b) {
-          const int i = row0 + ww * 4 + b;
-          const int s = (c == 0 || i >= lq) ? -128 : (int)tab[(qp[(long)i * qstep] & 31) * 32 + c];
-          word |= (unsigned)(s & 0xff) << (8 * b);
-        }
-        pl[(c * W + ww) * 32 + lane] = word;
-      }
-    }
-    __syncwarp();
-    int H[R3], G[R3];
-#pragma unroll
-    for (int k = 0; k < R3; ++k) { H[k] = 0; G[k] = 0; }
-    int diag_in = 0, out_h = 0, out_v = 0, my_code = 0;
-    int pre_code = 0, pre_h = 0, pre_v = 0;
-    const bool first = (pass == 0), last = (pass == npass - 1);
-    const int nsteps = lt + 31;
-    for (int s = 0; s < nsteps; ++s) {
-      if ((s & 31) == 0) {
-        const int j = s + lane;
-        pre_code = (j < lt) ? (int)tp[(long)j * tstep] : 0;
-        int2 b = make_int2(0, 0);
-        if (!first && j < lt) b = bnd[j];
-        pre_h = b.x; pre_v = b.y;
-      }
-      int code = __shfl_up_sync(0xffffffffu, my_code, 1);
-      int h_up = __shfl_up_sync(0xffffffffu, out_h, 1);
-      int v_in = __shfl_up_sync(0xffffffffu, out_v, 1);
-      const int c0 = __shfl_sync(0xffffffffu, pre_code, s & 31);
-      const int h0 = __shfl_sync(0xffffffffu, pre_h, s & 31);
-      const int v0 = __shfl_sync(0xffffffffu, pre_v, s & 31);
-      if (lane == 0) { code = c0; h_up = h0; v_in = v0; }
-      my_code = code;
-      const int j = s - lane;
-      if (j >= 0 && j < lt) {
-        int d = diag_in;
-        diag_in = h_up;
-        int V = v_in;
-        unsigned wreg[W];
-#pragma unroll
-        for (int ww = 0; ww < W; ++ww) wreg[ww] = lds32(pl_addr + ((code & 31) * W + ww) * 128);
-        int colbest = 0, colk = 0;
-#pragma unroll
-        for (int k = 0; k < R3; ++k) {
-          const int t = (int)add_byte(wreg[k >> 2], 1u << (8 * (k & 3)), (unsigned)d);
-          const int h = __vimax3_s32_relu(t, G[k], V);
-          d = H[k];
-          H[k] = h;
-          const int u = h + oe;
-          G[k] = __viaddmax_s32(G[k], ge, u);
-          V = __viaddmax_s32(V, ge, u);
-          if (h > colbest) { colbest = h; colk = k; }          // strict: first (smallest i) maximum of the column
-        }
-        if (loc_better(colbest, j, row0 + colk, best, bj, bi)) { best = colbest; bj = j; bi = row0 + colk; }
-        out_h = H[R3 - 1];
-        out_v = V;
-        if (lane == 31 && !last) bnd[j] = make_int2(out_h, out_v);
-      }
-    }
-  }
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
-    const int s2 = __shfl_xor_sync(0xffffffffu, best, o);
-    const int j2 = __shfl_xor_sync(0xffffffffu, bj, o);
-    const int i2 = __shfl_xor_sync(0xffffffffu, bi, o);
-    if (loc_better(s2, j2, i2, best, bj, bi)) { best = s2; bj = j2; bi = i2; }
-  }
-  if (lane == 0) {
-    int4 c = P.coords[hit];
-    if (P.phase == 0) {
-      if (best > 0) { c.y = bi; c.w = bj; } else { c = make_int4(-1, -1, -1, -1); }
-      P.best_out[hit] = best;
-    } else {
-      c.x = c.y - bi; c.z = c.w - bj;
-    }
-    P.coords[hit] = c;
-  }
-}
+// Coordinates: the wavefront kernel k3w<TRACK> (sw_k3w.cuh), one CTA per hit; phase 0 = forward (end cell),
+// phase 1 = the reversed prefixes (start cell).
 
 }  // namespace swk
 
@@ -288,6 +149,7 @@ extern "C" int swgpu_topk(swgpu_db_t* db, int k, swgpu_hit_t* hits, int* n_hits)
   CU(cudaStreamSynchronize(st));
   std::vector<int4> hc(k, make_int4(-1, -1, -1, -1));
   std::vector<int> hb(k, 0);
+  unsigned loc_err = 0;
   const int lq = (int)db->last_lq;
   int n_pos = 0;
   while (n_pos < k && (hk[n_pos] >> 32) != 0) ++n_pos;          // hits with score 0 have no coordinates
@@ -301,15 +163,17 @@ extern "C" int swgpu_topk(swgpu_db_t* db, int k, swgpu_hit_t* hits, int* n_hits)
       db->bnd_loc_stride = std::max(need, db->bnd_loc_stride); db->loc_slots = std::max(n_pos, db->loc_slots);
       CU(cudaMalloc((void**)&db->d_bnd_loc, sizeof(int2) * (size_t)db->bnd_loc_stride * (size_t)db->loc_slots));
     }
-    swk::LocParams P; memset(&P, 0, sizeof(P));
-    P.sidx = sidx_s; P.k = n_pos; P.plain = db->d_plain; P.plain_off = db->d_plain_off; P.query = db->d_query; P.lq = lq;
-    P.table = db->d_table; P.oe = db->last_oe; P.ge = db->last_ge; P.bnd = db->d_bnd_loc; P.bnd_stride = db->bnd_loc_stride;
-    P.coords = db->d_coords; P.best_out = best_out; P.one = 1u;
-    const int lgrid = (n_pos + swk::LOC_WARPS - 1) / swk::LOC_WARPS;
-    P.phase = 0; swk::k_locate<<<lgrid, swk::LOC_WARPS * 32, 0, st>>>(P);
-    P.phase = 1; swk::k_locate<<<lgrid, swk::LOC_WARPS * 32, 0, st>>>(P);
+    swk::K3WParams P; memset(&P, 0, sizeof(P));
+    P.sidx_list = sidx_s; P.n_work = n_pos; P.plain = db->d_plain; P.plain_off = db->d_plain_off; P.query = db->d_query;
+    P.lq = lq; P.table = db->d_table; P.oe = db->last_oe; P.ge = db->last_ge; P.bnd = db->d_bnd_loc;
+    P.bnd_stride = db->bnd_loc_stride; P.coords = db->d_coords; P.best_out = best_out;
+    P.error_flag = db->d_counters + 7;
+    CU(cudaMemsetAsync(db->d_counters + 7, 0, sizeof(unsigned), st));
+    P.phase = 0; swk::k3w<true><<<n_pos, swk::K3W_WARPS * 32, 0, st>>>(P);
+    P.phase = 1; swk::k3w<true><<<n_pos, swk::K3W_WARPS * 32, 0, st>>>(P);
     launches += 2;
     CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(&loc_err, db->d_counters + 7, sizeof(unsigned), cudaMemcpyDeviceToHost, st));
     CU(cudaMemcpyAsync(hc.data(), db->d_coords, sizeof(int4) * n_pos, cudaMemcpyDeviceToHost, st));
     CU(cudaMemcpyAsync(hb.data(), best_out, sizeof(int) * n_pos, cudaMemcpyDeviceToHost, st));
   }
@@ -317,6 +181,7 @@ extern "C" int swgpu_topk(swgpu_db_t* db, int k, swgpu_hit_t* hits, int* n_hits)
   CU(cudaStreamSynchronize(st));
   float ms = 0; CU(cudaEventElapsedTime(&ms, db->ev[4], db->ev[5]));
   db->last_stats.ms_topk = ms; db->last_stats.topk_launches = launches;
+  if (loc_err) return fail(SWGPU_ECUDA, "swgpu_topk: coordinate pipeline stalled (internal error)");
   for (int i = 0; i < k; ++i) {
     swgpu_hit_t& h = hits[i];
     h.score = (int32_t)(hk[i] >> 32);
