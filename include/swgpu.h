@@ -38,23 +38,22 @@ typedef struct swgpu_db swgpu_db_t;   /* packed, HBM-resident database on one GP
 
 /* Packing knobs (0 = engine default). */
 typedef struct {
-    int32_t long_threshold;   /* chunk kernel only: targets longer than this go to the intra-sequence kernel */
-    int32_t stream_cols;      /* systolic kernel: target length of one stream of concatenated target pairs */
-    int32_t use_chunk_kernel; /* 1 = score with the first-generation chunk kernel (k1_inter) instead of k1s */
-    int32_t reserved[5];
+    int32_t long_threshold;   /* > 0: targets longer than this are always scored by the 32-bit kernels */
+    int32_t stream_cols;      /* length of one stream of concatenated target pairs (16-bit kernel); default 1536 */
+    int32_t reserved[6];
 } swgpu_pack_opts_t;
 
 /* Per-search statistics, all device-timed with CUDA events on the engine's stream. */
 typedef struct {
     double  ms_total;         /* first kernel launch -> last result resident in HBM */
-    double  ms_inter;         /* inter-sequence packed 16-bit kernel (K1) */
-    double  ms_intra;         /* intra-sequence 32-bit kernel, long targets (K3) */
-    double  ms_rescore;       /* 32-bit rescoring of saturated targets (K2 = K3 code path) */
+    double  ms_inter;         /* packed 16-bit systolic kernel K1S incl. profile build and finalize */
+    double  ms_intra;         /* the separate low-latency K1S launch for long streams (runs concurrently) */
+    double  ms_rescore;       /* 32-bit kernels: rescoring of saturated targets (K3 / K3W) */
     double  ms_h2d, ms_d2h;   /* query/table upload, score download (host API only) */
     int64_t cells;            /* sum over targets of Lq * Lt, real residues */
     int64_t cells_inter, cells_intra, cells_rescore;
     int64_t n_rescored;       /* targets whose 16-bit result saturated */
-    int64_t n_long;           /* targets scored by the intra-sequence kernel */
+    int64_t n_long;           /* targets handled by the long-stream launch */
     int32_t kernel_launches;  /* engine kernels launched by this search */
     int32_t tile_rows;        /* query rows per lane (register tile) chosen for the 16-bit kernel */
     double  ms_topk;          /* last swgpu_topk(): selection + coordinate passes */
@@ -78,8 +77,8 @@ const char *swgpu_version(void);
 /*
  * Database packing.  Replaces the batch build of src/alignment_cmdline.c:422-457
  * (encode, 16-lane interleave, '*' padding): here targets are sorted by length
- * inside the engine (the reference demands a pre-sorted file, :431-439), grouped
- * into 64-target chunks, column-interleaved and uploaded once.
+ * inside the engine (the reference demands a pre-sorted file, :431-439), paired,
+ * concatenated into streams of 16-bit columns and uploaded once.
  *   codes    n_residues residue codes, targets back to back, file order
  *   offsets  n_targets+1 prefix offsets into codes
  *   entry_base  file-order index of target 0 of this shard (multi-GPU sharding)

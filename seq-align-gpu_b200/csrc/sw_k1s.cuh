@@ -230,9 +230,12 @@ __global__ void __launch_bounds__(K1S_WARPS * 32, 2) k1s(const K1SParams P) {
   }
 }
 
-// reduce the g per-lane maxima of every pair, un-bias, detect saturation, scatter to file order
+// reduce the g per-lane maxima of every pair, un-bias, detect saturation, scatter to file order.
+// A pair whose either half reached `limit` sends BOTH members to the 32-bit list (a carry out of the low
+// half would have corrupted the high half); long_thr > 0 also sends every target longer than that.
 static __global__ void k1s_finalize(const unsigned* __restrict__ raw, long pair_begin, long n_pairs, int g_log2, long n_sorted,
                                     unsigned B, unsigned limit, const int64_t* __restrict__ order,
+                                    const int64_t* __restrict__ plain_off, int long_thr,
                                     int32_t* __restrict__ scores_file, int* __restrict__ rescore_list,
                                     unsigned* __restrict__ rescore_count) {
   const int g = 1 << g_log2;
@@ -246,7 +249,8 @@ static __global__ void k1s_finalize(const unsigned* __restrict__ raw, long pair_
     for (int h = 0; h < 2; ++h) {
       const long s = 2 * p + h;
       if (s >= n_sorted) continue;
-      if (sat) {
+      const bool force = long_thr > 0 && (plain_off[s + 1] - plain_off[s]) > long_thr;
+      if (sat || force) {
         const unsigned slot = atomicAdd(rescore_count, 1u);
         rescore_list[slot] = (int)s;
       } else {

@@ -1,4 +1,4 @@
-// sw_kernels.cuh -- sm_100a kernels of the Smith-Waterman database-search engine.
+// sw_kernels.cuh -- shared device helpers and K3, the 32-bit intra-sequence kernel (sm_100a).
 //
 // The recurrence is the reference's 3-state affine form (src/alignment.c:117-176 of the
 // reference tree), evaluated in the score-equivalent 2-gap-state (Gotoh) form that
@@ -9,10 +9,10 @@
 //     score  = max H                                   (:133, :186)
 // i = query position, j = target position, oe = gap_open + gap_extend (:58), ge = gap_extend (:59).
 //
-// K1  k1_inter<R>   inter-sequence, packed 2 x u16 per register, one lane = one PAIR of targets.
-// K3  k3_intra<R3>  intra-sequence, 32-bit, one warp = one target (long targets and
-//                   rescoring of targets whose 16-bit result saturated -- the reference's
-//                   16-bit / 32-bit split, README.md:11).
+// K1S (sw_k1s.cuh)  inter-sequence, packed 2 x u16, the dominant kernel
+// K3  k3_intra<R3>  32-bit, one warp per target: rescoring of targets whose 16-bit result
+//                   saturated -- the reference's 16-bit / 32-bit split, README.md:11
+// K3W (sw_k3w.cuh)  32-bit wavefront, one CTA per target: long targets, top-k coordinates
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -43,191 +43,6 @@ __device__ __forceinline__ unsigned add_hi_hi(unsigned b, unsigned c) {
 // a + b as IMAD (FMA-heavy pipe); `one` is an opaque register holding 1.
 __device__ __forceinline__ unsigned add_fma(unsigned a, unsigned one, unsigned b) {
   unsigned d; asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(one), "r"(b)); return d;
-}
-
-// ------------------------------------------------------------------------------------------
-// Query-profile tiles for K1.
-// One tile = R consecutive query rows.  Per tile and per residue code c (0..31):
-//   PA[c][k/4]  int8 x 4 : s(q_{i0+k}, c)                      (target in the LOW  u16 half)
-//   PB[c][k/2]  int8 x 4 : s(k), s(k), s(k+1), s(k+1)            (target in the HIGH u16 half)
-// Row strides SA = (R/4)|1 and SB = (R/2)|1 words are odd, so the 32 lanes of a warp, which
-// read the SAME k with DIFFERENT codes, hit 32 different banks (code -> code*odd mod 32 is a
-// bijection) or the same word (broadcast): the lookups are bank-conflict-free by construction.
-// Code 0 (padding) and rows past the query end score -128 (below every legal matrix entry,
-// src/alignment_scoring.c:61), so padded cells can never raise the running maximum.
-// ------------------------------------------------------------------------------------------
-template <int R> struct Tile {
-  static constexpr int SA = (R / 4) | 1;
-  static constexpr int SB = (R / 2) | 1;
-  static constexpr int WORDS = 32 * (SA + SB);
-};
-
-static __global__ void build_profile(const int8_t* __restrict__ query, int lq, const int8_t* __restrict__ table,
-                              int R, int SA, int SB, int ntiles, unsigned* __restrict__ prof) {
-  const int words = 32 * (SA + SB);
-  const long total = (long)ntiles * words;
-  for (long idx = blockIdx.x * (long)blockDim.x + threadIdx.x; idx < total; idx += (long)gridDim.x * blockDim.x) {
-    const int tile = (int)(idx / words), w = (int)(idx % words);
-    unsigned out = 0;
-    auto score = [&](int c, int k) -> unsigned {
-      const long i = (long)tile * R + k;
-      int s = (c == 0 || i >= lq || k >= R) ? -128 : (int)table[(query[i] & 31) * 32 + c];
-      return (unsigned)(s & 0xff);
-    };
-    if (w < 32 * SA) {
-      const int c = w / SA, k4 = w % SA;
-      if (k4 < R / 4) for (int b = 0; b < 4; ++b) out |= score(c, 4 * k4 + b) << (8 * b);
-    } else {
-      const int v = w - 32 * SA, c = v / SB, k2 = v % SB;
-      if (k2 < R / 2) {
-        const unsigned s0 = score(c, 2 * k2), s1 = score(c, 2 * k2 + 1);
-        out = s0 | (s0 << 8) | (s1 << 16) | (s1 << 24);
-      }
-    }
-    prof[idx] = out;
-  }
-}
-
-// ------------------------------------------------------------------------------------------
-// K1: inter-sequence kernel.
-//
-// A 64-target chunk of the length-sorted database is owned by one warp: lane l holds targets
-// 2l (low u16 half) and 2l+1 (high half) of the chunk.  The warp walks the chunk's columns
-// (target positions); per column every lane updates R query rows kept in registers
-// (H and G per row).  All lanes work on the SAME query rows at the same time, which is what
-// makes the profile lookups conflict-free.  The query is covered in ceil(Lq/R) passes; the
-// bottom row (H, V) of a pass is carried to the next pass through a per-warp column buffer
-// in global memory, [column][lane] of uint2, coalesced.
-//
-// Arithmetic is BIASED unsigned 16-bit: every stored value is true value + B with
-// B >= 128 + |oe| + |ge|.  With the bias no partial result is ever negative, so a 32-bit
-// integer add of (sA + 65536*sB) to the packed register cannot borrow across the halves;
-// that is what lets the substitution add (IDP.4A + IDP.2A) and the H+oe add (IMAD) run on
-// the FMA-heavy pipe while the ALU pipe does only the four max-type DPX ops per cell pair:
-//     ef = VIMNMX3.U16x2(G, V, BB)        floor at the bias == the reference's clamp at 0
-//     h  = VIMNMX.U16x2(t, ef)
-//     G' = VIADDMNMX.U16x2(G, ge, u)      u = h + oe
-//     V' = VIADDMNMX.U16x2(V, ge, u)
-// plus half a VIMNMX3 for the running maximum.  A half that reaches 65535-128-1 may have
-// carried into its neighbour: both targets of such a lane are rescored in 32 bits (K3).
-// ------------------------------------------------------------------------------------------
-struct K1Params {
-  const uint2*   cols;        // [chunk][col/4][lane] : 4 columns x (codeA | codeB << 8)
-  const int64_t* chunk_off;   // per chunk, offset into cols (uint2 units)
-  const int32_t* chunk_cols;  // per chunk, padded column count (multiple of 4)
-  int            n_chunks;
-  const unsigned* prof;       // ntiles x Tile<R>::WORDS
-  int            ntiles;
-  uint2*         bnd;         // per warp slot: bnd_stride uint2
-  long long      bnd_stride;
-  unsigned*      counter;     // work-queue head (chunks are sorted longest first)
-  unsigned*      raw_out;     // [chunk][lane] packed biased best
-  unsigned       BB, OE32, GE2, one;
-};
-
-constexpr int K1_WARPS = 8;
-
-template <int R>
-__global__ void __launch_bounds__(K1_WARPS * 32, 2) k1_inter(const K1Params P) {
-  using T = Tile<R>;
-  extern __shared__ unsigned smem_u32[];
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  unsigned* pw = smem_u32 + warp * T::WORDS;
-  const unsigned pa_addr = (unsigned)__cvta_generic_to_shared(pw);
-  const unsigned pb_addr = pa_addr + 32 * T::SA * 4;
-  uint2* bnd = P.bnd + (size_t)(blockIdx.x * K1_WARPS + warp) * (size_t)P.bnd_stride + lane;
-  const unsigned BB = P.BB, OE32 = P.OE32, GE2 = P.GE2, one = P.one;
-
-  for (;;) {
-    int chunk = 0;
-    if (lane == 0) chunk = (int)atomicAdd(P.counter, 1u);
-    chunk = __shfl_sync(0xffffffffu, chunk, 0);
-    if (chunk >= P.n_chunks) break;
-    const int ngroups = P.chunk_cols[chunk] >> 2;
-    const uint2* cp = P.cols + P.chunk_off[chunk] + lane;
-    unsigned best = BB;
-
-    for (int tile = 0; tile < P.ntiles; ++tile) {
-      __syncwarp();
-      {
-        const unsigned* g = P.prof + (size_t)tile * T::WORDS;
-        for (int i = lane; i < T::WORDS; i += 32) pw[i] = g[i];
-      }
-      __syncwarp();
-      const bool first = (tile == 0), last = (tile == P.ntiles - 1);
-      unsigned H[R], G[R];
-#pragma unroll
-      for (int k = 0; k < R; ++k) { H[k] = BB; G[k] = BB; }
-      unsigned hin_prev = BB;                       // H(i0-1, j-1)
-      uint2 letters = cp[0];
-      uint2 bin = first ? make_uint2(BB, BB) : bnd[0];
-
-      for (int g4 = 0; g4 < ngroups; ++g4) {
-        const uint2 letters_next = (g4 + 1 < ngroups) ? cp[(size_t)(g4 + 1) * 32] : make_uint2(0u, 0u);
-#pragma unroll
-        for (int c = 0; c < 4; ++c) {
-          const int col = g4 * 4 + c;
-          uint2 bin_next = make_uint2(BB, BB);
-          if (!first && (c < 3 || g4 + 1 < ngroups)) bin_next = bnd[(size_t)(col + 1) * 32];
-          const unsigned lw = ((c < 2) ? letters.x : letters.y) >> (16 * (c & 1));
-          const unsigned aoff = pa_addr + (lw & 0xffu) * (T::SA * 4);
-          const unsigned boff = pb_addr + ((lw >> 8) & 0xffu) * (T::SB * 4);
-          unsigned d = hin_prev;
-          hin_prev = bin.x;
-          unsigned V = bin.y;
-          unsigned wA = 0, wB = 0, hprev = BB;
-#pragma unroll
-          for (int k = 0; k < R; ++k) {
-            if ((k & 3) == 0) wA = lds32(aoff + k);          // word k/4
-            if ((k & 1) == 0) wB = lds32(boff + 2 * k);      // word k/2
-            unsigned t = add_byte(wA, 1u << (8 * (k & 3)), d);
-            t = (k & 1) ? add_hi_hi(wB, t) : add_hi_lo(wB, t);
-            const unsigned ef = __vimax3_u16x2(G[k], V, BB);
-            const unsigned h = __vmaxu2(t, ef);
-            d = H[k];
-            H[k] = h;
-            const unsigned u = add_fma(h, one, OE32);
-            G[k] = __viaddmax_u16x2(G[k], GE2, u);
-            V = __viaddmax_u16x2(V, GE2, u);
-            if (k & 1) best = __vimax3_u16x2(best, hprev, h); else hprev = h;
-          }
-          if (R & 1) best = __vmaxu2(best, hprev);
-          if (!last) bnd[(size_t)col * 32] = make_uint2(H[R - 1], V);
-          bin = bin_next;
-        }
-        letters = letters_next;
-      }
-    }
-    P.raw_out[(size_t)chunk * 32 + lane] = best;
-  }
-}
-
-// ------------------------------------------------------------------------------------------
-// K1 epilogue: un-bias, detect saturation, scatter to file order.
-// sorted index s = first + chunk*64 + lane*2 + half.  A lane whose either half reached
-// `limit` sends BOTH its targets to the 32-bit rescoring list (a carry out of the low half
-// would have corrupted the high half).
-// ------------------------------------------------------------------------------------------
-static __global__ void k1_finalize(const unsigned* __restrict__ raw, long n_lanes, long first, long n_sorted,
-                            unsigned B, unsigned limit, const int64_t* __restrict__ order,
-                            int32_t* __restrict__ scores_file, int* __restrict__ rescore_list,
-                            unsigned* __restrict__ rescore_count) {
-  for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < n_lanes; i += (long)gridDim.x * blockDim.x) {
-    const unsigned r = raw[i], lo = r & 0xffffu, hi = r >> 16;
-    const bool sat = (lo >= limit) || (hi >= limit);
-    const long s0 = first + 2 * i;
-#pragma unroll
-    for (int h = 0; h < 2; ++h) {
-      const long s = s0 + h;
-      if (s >= n_sorted) continue;
-      if (sat) {
-        const unsigned slot = atomicAdd(rescore_count, 1u);
-        rescore_list[slot] = (int)s;
-      } else {
-        scores_file[order[s]] = (int32_t)((h ? hi : lo) - B);
-      }
-    }
-  }
 }
 
 // ------------------------------------------------------------------------------------------

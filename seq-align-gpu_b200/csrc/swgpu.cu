@@ -1,15 +1,14 @@
-// swgpu.cu -- implementation of the C-ABI in include/swgpu.h (thin extern "C" layer over the
-// kernels in sw_kernels.cuh).  No CPU fallback: every compute entry point needs a CUDA device.
+// swgpu.cu -- implementation of the C-ABI in include/swgpu.h: database handle, search orchestration.
+// Thin extern "C" layer over the kernels in sw_k1s.cuh (16-bit systolic), sw_kernels.cuh (K3, 32-bit)
+// and sw_k3w.cuh (32-bit wavefront).  No CPU fallback: every compute entry point needs a CUDA device.
 #include "swgpu_internal.h"
 #include "db_pack.h"
 #include "sw_kernels.cuh"
 #include "sw_k1s.cuh"
 #include "sw_k3w.cuh"
 
-#include <cstdio>
 #include <cstdlib>
 #include <cstring>
-#include <cstdarg>
 #include <vector>
 #include <algorithm>
 
@@ -17,13 +16,8 @@ namespace {
 
 using swi::fail;
 
-constexpr int kDefaultLongThreshold = 3072;
 constexpr int kDefaultStreamCols = 1536;
-constexpr int kTileChoices[] = {32, 28, 24, 20, 16};
-
-}  // namespace
-
-namespace {
+constexpr int kWaveMinLen = 4096;          // 32-bit path: targets at least this long take k3w (one CTA each)
 
 template <typename T>
 int dalloc(swgpu_db* db, T** p, size_t count) {
@@ -44,17 +38,16 @@ int swgpu_device_count(void) {
 }
 
 const char* swgpu_last_error(void) { return swi::err_buf(); }
-const char* swgpu_version(void) { return "swgpu 0.1 (sm_100a)"; }
+const char* swgpu_version(void) { return "swgpu 0.2 (sm_100a)"; }
 
 void swgpu_db_destroy(swgpu_db_t* db) {
   if (!db) return;
   cudaSetDevice(db->device);
-  cudaFree(db->d_plain); cudaFree(db->d_plain_off); cudaFree(db->d_order); cudaFree(db->d_cols);
-  cudaFree(db->d_chunk_off); cudaFree(db->d_chunk_cols); cudaFree(db->d_scores); cudaFree(db->d_raw);
-  cudaFree(db->d_rescore_list); cudaFree(db->d_counters); cudaFree(db->d_bnd1); cudaFree(db->d_bnd3);
-  cudaFree(db->d_query); cudaFree(db->d_table); cudaFree(db->d_prof);
+  cudaFree(db->d_plain); cudaFree(db->d_plain_off); cudaFree(db->d_order);
   cudaFree(db->d_scols); cudaFree(db->d_stream_off); cudaFree(db->d_stream_ncols); cudaFree(db->d_stream_pair0);
-  cudaFree(db->d_raw_s); cudaFree(db->d_bnd_s); cudaFree(db->d_sprof); cudaFree(db->d_sprof2);
+  cudaFree(db->d_scores); cudaFree(db->d_raw_s); cudaFree(db->d_rescore_list); cudaFree(db->d_counters);
+  cudaFree(db->d_bnd_s); cudaFree(db->d_bnd3); cudaFree(db->d_query); cudaFree(db->d_table);
+  cudaFree(db->d_sprof); cudaFree(db->d_sprof2);
   cudaFree(db->d_keys); cudaFree(db->d_hit_sidx); cudaFree(db->d_sel); cudaFree(db->d_coords); cudaFree(db->d_bnd_loc);
   for (auto& e : db->ev) if (e) cudaEventDestroy(e);
   if (db->s_main) cudaStreamDestroy(db->s_main);
@@ -65,6 +58,7 @@ void swgpu_db_destroy(swgpu_db_t* db) {
 int swgpu_db_create(swgpu_db_t** out, int device, const int8_t* codes, const int64_t* offsets,
                     int64_t n_targets, int64_t entry_base, const swgpu_pack_opts_t* opts) {
   if (!out || n_targets < 0 || (n_targets > 0 && (!codes || !offsets))) return fail(SWGPU_EINVAL, "swgpu_db_create: bad argument");
+  if (n_targets > 0x7ffffff0ll) return fail(SWGPU_EINVAL, "swgpu_db_create: more than 2^31 targets per GPU; shard the database");
   *out = nullptr;
   int ndev = 0;
   CU(cudaGetDeviceCount(&ndev));
@@ -72,21 +66,20 @@ int swgpu_db_create(swgpu_db_t** out, int device, const int8_t* codes, const int
   if (device < 0 || device >= ndev) return fail(SWGPU_EINVAL, "device %d out of range (%d devices)", device, ndev);
   CU(cudaSetDevice(device));
 
-  const int long_thr = (opts && opts->long_threshold > 0) ? opts->long_threshold : kDefaultLongThreshold;
+  const int stream_cols = (opts && opts->stream_cols > 0) ? opts->stream_cols : kDefaultStreamCols;
   swpack_t pk;
   static const int64_t zero_off[1] = {0};
-  const int stream_cols = (opts && opts->stream_cols > 0) ? opts->stream_cols : kDefaultStreamCols;
-  if (swpack_build(&pk, codes, n_targets ? offsets : zero_off, n_targets, long_thr, stream_cols) != 0)
+  if (swpack_build(&pk, codes, n_targets ? offsets : zero_off, n_targets, stream_cols) != 0)
     return fail(SWGPU_EINVAL, "database packing failed (residue code outside 0..31, negative length, or out of memory)");
 
   swgpu_db* db = new swgpu_db();
   db->device = device;
-  db->n = pk.n_targets; db->n_residues = pk.n_residues; db->n_long = pk.n_long; db->n_chunks = pk.n_chunks;
-  db->max_len = pk.max_len; db->max_chunk_cols = pk.max_chunk_cols; db->entry_base = entry_base;
-  db->h_order.assign(pk.order, pk.order + pk.n_targets);
+  db->n = pk.n_targets; db->n_residues = pk.n_residues; db->max_len = pk.max_len; db->entry_base = entry_base;
+  db->long_threshold = (opts && opts->long_threshold > 0) ? opts->long_threshold : 0;
   db->h_len_sorted_prefix.assign(pk.plain_off, pk.plain_off + pk.n_targets + 1);
+  db->n_pairs = pk.n_pairs; db->n_streams = pk.n_streams; db->max_stream_cols = pk.max_stream_cols;
+  db->n_long_streams = pk.n_long_streams; db->n_long_pairs = pk.n_long_pairs;
 
-  int rc = SWGPU_OK;
   auto body = [&]() -> int {
     cudaDeviceProp prop;
     CU(cudaGetDeviceProperties(&prop, device));
@@ -98,48 +91,32 @@ int swgpu_db_create(swgpu_db_t** out, int device, const int8_t* codes, const int
     if ((r = dalloc(db, &db->d_plain, (size_t)pk.n_residues))) return r;
     if ((r = dalloc(db, &db->d_plain_off, (size_t)pk.n_targets + 1))) return r;
     if ((r = dalloc(db, &db->d_order, (size_t)pk.n_targets))) return r;
-    if ((r = dalloc(db, &db->d_cols, (size_t)pk.cols_words))) return r;
-    if ((r = dalloc(db, &db->d_chunk_off, (size_t)pk.n_chunks + 1))) return r;
-    if ((r = dalloc(db, &db->d_chunk_cols, (size_t)pk.n_chunks))) return r;
+    if ((r = dalloc(db, &db->d_scols, (size_t)pk.scols_len + 64))) return r;
+    if ((r = dalloc(db, &db->d_stream_off, (size_t)pk.n_streams + 1))) return r;
+    if ((r = dalloc(db, &db->d_stream_ncols, (size_t)pk.n_streams))) return r;
+    if ((r = dalloc(db, &db->d_stream_pair0, (size_t)pk.n_streams))) return r;
     if ((r = dalloc(db, &db->d_scores, (size_t)pk.n_targets))) return r;
-    if ((r = dalloc(db, &db->d_raw, (size_t)pk.n_chunks * 32))) return r;
+    if ((r = dalloc(db, &db->d_raw_s, (size_t)pk.n_pairs * 32))) return r;
     if ((r = dalloc(db, &db->d_rescore_list, (size_t)pk.n_targets))) return r;
     if ((r = dalloc(db, &db->d_counters, 8))) return r;
     if ((r = dalloc(db, &db->d_table, 1024))) return r;
     CU(cudaMemcpy(db->d_plain, pk.plain, (size_t)pk.n_residues, cudaMemcpyHostToDevice));
     CU(cudaMemcpy(db->d_plain_off, pk.plain_off, sizeof(int64_t) * ((size_t)pk.n_targets + 1), cudaMemcpyHostToDevice));
     CU(cudaMemcpy(db->d_order, pk.order, sizeof(int64_t) * (size_t)pk.n_targets, cudaMemcpyHostToDevice));
-    CU(cudaMemcpy(db->d_cols, pk.cols, sizeof(uint64_t) * (size_t)pk.cols_words, cudaMemcpyHostToDevice));
-    CU(cudaMemcpy(db->d_chunk_off, pk.chunk_off, sizeof(int64_t) * ((size_t)pk.n_chunks + 1), cudaMemcpyHostToDevice));
-    CU(cudaMemcpy(db->d_chunk_cols, pk.chunk_cols, sizeof(int32_t) * (size_t)pk.n_chunks, cudaMemcpyHostToDevice));
-
-    // streams
-    db->n_pairs = pk.n_pairs; db->n_streams = pk.n_streams; db->max_stream_cols = pk.max_stream_cols;
-    db->n_long_streams = pk.n_long_streams; db->n_long_pairs = pk.n_long_pairs;
-    db->use_old_k1 = (opts && opts->use_chunk_kernel) ? 1 : 0;
-    if ((r = dalloc(db, &db->d_scols, (size_t)pk.scols_len + 64))) return r;
-    if ((r = dalloc(db, &db->d_stream_off, (size_t)pk.n_streams + 1))) return r;
-    if ((r = dalloc(db, &db->d_stream_ncols, (size_t)pk.n_streams))) return r;
-    if ((r = dalloc(db, &db->d_stream_pair0, (size_t)pk.n_streams))) return r;
-    if ((r = dalloc(db, &db->d_raw_s, (size_t)pk.n_pairs * 32))) return r;
     CU(cudaMemcpy(db->d_scols, pk.scols, sizeof(uint16_t) * (size_t)pk.scols_len, cudaMemcpyHostToDevice));
     CU(cudaMemcpy(db->d_stream_off, pk.stream_off, sizeof(int64_t) * ((size_t)pk.n_streams + 1), cudaMemcpyHostToDevice));
     CU(cudaMemcpy(db->d_stream_ncols, pk.stream_ncols, sizeof(int32_t) * (size_t)pk.n_streams, cudaMemcpyHostToDevice));
     CU(cudaMemcpy(db->d_stream_pair0, pk.stream_pair0, sizeof(int64_t) * (size_t)pk.n_streams, cudaMemcpyHostToDevice));
+    // persistent grids: k1s two CTAs of 8 warps per SM; k3 at most four CTAs of 4 warps per SM
     db->k1s_grid = db->sm_count * 2;
     db->bnd_s_stride = ((long long)std::max<int32_t>(pk.max_stream_cols, 64) + 63) & ~63ll;
     if ((r = dalloc(db, &db->d_bnd_s, (size_t)db->k1s_grid * swk::K1S_WARPS * (size_t)db->bnd_s_stride))) return r;
-    // persistent grids: K1 two CTAs of 8 warps per SM; K3 eight CTAs of 4 warps per SM at most
-    db->k1_grid = (int)std::min<int64_t>((int64_t)db->sm_count * 2, (pk.n_chunks + swk::K1_WARPS - 1) / swk::K1_WARPS);
-    db->k1_grid = std::max(db->k1_grid, 1);
-    db->bnd1_stride = (long long)std::max<int32_t>(pk.max_chunk_cols, 4) * 32;
-    if ((r = dalloc(db, &db->d_bnd1, (size_t)db->k1_grid * swk::K1_WARPS * (size_t)db->bnd1_stride))) return r;
     db->k3_grid = db->sm_count * 4;
     db->bnd3_stride = std::max<int32_t>(pk.max_len, 32);
     if ((r = dalloc(db, &db->d_bnd3, (size_t)db->k3_grid * swk::K3_WARPS * (size_t)db->bnd3_stride))) return r;
     return SWGPU_OK;
   };
-  rc = body();
+  const int rc = body();
   swpack_free(&pk);
   if (rc != SWGPU_OK) { swgpu_db_destroy(db); return rc; }
   *out = db;
@@ -157,23 +134,8 @@ int64_t swgpu_db_device_bytes(const swgpu_db_t* db) { return db ? db->device_byt
 // ------------------------------------------------------------------------------------------
 namespace {
 
-template <int R>
-int launch_k1(swgpu_db* db, const swk::K1Params& P) {
-  const size_t smem = (size_t)swk::K1_WARPS * swk::Tile<R>::WORDS * sizeof(unsigned);
-  swk::k1_inter<R><<<db->k1_grid, swk::K1_WARPS * 32, smem, db->s_main>>>(P);
-  CU(cudaGetLastError());
-  return SWGPU_OK;
-}
-
-int launch_k3(swgpu_db* db, cudaStream_t st, const swk::K3Params& P, int lq) {
-  if (lq <= 128) swk::k3_intra<4><<<db->k3_grid, swk::K3_WARPS * 32, 0, st>>>(P);
-  else           swk::k3_intra<8><<<db->k3_grid, swk::K3_WARPS * 32, 0, st>>>(P);
-  CU(cudaGetLastError());
-  return SWGPU_OK;
-}
-
 // K1S plan: lanes per target pair (g), query rows per lane (R), stripes (npass).
-// Cost model: padded rows x (cell work + per-step overhead / R); ties go to the larger g (more parallel items).
+// Cost model: padded rows x (cell work + per-step overhead / R); few work items -> prefer more lanes per pair.
 struct K1SPlan { int g, g_log2, R, npass; };
 
 K1SPlan plan_k1s(int64_t lq, int64_t n_streams, int warp_slots) {
@@ -183,7 +145,7 @@ K1SPlan plan_k1s(int64_t lq, int64_t n_streams, int warp_slots) {
     int R = (int)((lq + g - 1) / g); R += R & 1; if (R < 8) R = 8;
     if (R > 32) continue;
     double cost = (double)g * R * (9.0 * R + 16.0) / R;
-    const double items = (double)n_streams * g / 32.0;                 // few items -> idle warps
+    const double items = (double)n_streams * g / 32.0;
     if (items < 2.0 * warp_slots) cost *= (2.0 * warp_slots) / std::max(items, 1.0);
     if (best_cost < 0 || cost <= best_cost) { best_cost = cost; best = K1SPlan{g, gl, R, 1}; }
   }
@@ -200,10 +162,10 @@ K1SPlan plan_k1s(int64_t lq, int64_t n_streams, int warp_slots) {
 template <int R, bool MULTI>
 int launch_k1s_t(swgpu_db* db, const swk::K1SParams& P, cudaStream_t stream, int grid) {
   const size_t smem = swk::k1s_smem_bytes<R>();
-  static thread_local bool attr_done[8] = {};
-  if (!attr_done[db->device & 7]) {
+  static thread_local bool attr_done[16] = {};
+  if (!attr_done[db->device & 15]) {
     CU(cudaFuncSetAttribute(swk::k1s<R, MULTI>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    attr_done[db->device & 7] = true;
+    attr_done[db->device & 15] = true;
   }
   swk::k1s<R, MULTI><<<grid, swk::K1S_WARPS * 32, smem, stream>>>(P);
   CU(cudaGetLastError());
@@ -222,37 +184,35 @@ int launch_k1s(swgpu_db* db, const swk::K1SParams& P, int R, bool multi, cudaStr
 #undef K1S_CASE1
 }
 
-// 32-bit rescoring of the device-side list: k3_intra (one warp per target) takes the targets up to
-// kWaveMinLen residues, the wavefront kernel k3w (one CTA per target) the longer ones.
-constexpr int kWaveMinLen = 4096;
-
-int launch_rescore(swgpu_db* db, const swk::K3Params& P3, int lq, int oe, int ge, int* launches) {
-  swk::K3Params PR = P3;
-  PR.worklist = db->d_rescore_list; PR.work_count = db->d_counters + 2; PR.counter = db->d_counters + 3;
-  PR.max_len = kWaveMinLen - 1;
-  int r = launch_k3(db, db->s_main, PR, lq); if (r) return r;
+// 32-bit scoring of a work list (device-side count) or of all targets (list == nullptr): k3_intra (one warp per
+// target) takes the targets shorter than kWaveMinLen, the wavefront kernel k3w (one CTA per target) the rest.
+int launch_32bit(swgpu_db* db, const int* list, const unsigned* list_count, int n_all, int lq, int oe, int ge,
+                 unsigned* q_k3, unsigned* q_k3w, int* launches) {
+  swk::K3Params P; memset(&P, 0, sizeof(P));
+  P.worklist = list; P.work_count = list_count; P.n_work = n_all; P.counter = q_k3;
+  P.plain = db->d_plain; P.plain_off = db->d_plain_off; P.query = db->d_query; P.lq = lq; P.table = db->d_table;
+  P.oe = oe; P.ge = ge; P.bnd = db->d_bnd3; P.bnd_stride = db->bnd3_stride; P.order = db->d_order;
+  P.scores_file = db->d_scores; P.one = 1u; P.max_len = kWaveMinLen - 1;
+  if (lq <= 128) swk::k3_intra<4><<<db->k3_grid, swk::K3_WARPS * 32, 0, db->s_main>>>(P);
+  else           swk::k3_intra<8><<<db->k3_grid, swk::K3_WARPS * 32, 0, db->s_main>>>(P);
+  CU(cudaGetLastError());
   ++*launches;
   if (db->max_len >= kWaveMinLen) {
-    swk::K3WParams PW; memset(&PW, 0, sizeof(PW));
-    PW.sidx_list = db->d_rescore_list; PW.work_count = db->d_counters + 2; PW.counter = db->d_counters + 4;
-    PW.plain = db->d_plain; PW.plain_off = db->d_plain_off; PW.query = db->d_query; PW.lq = lq; PW.table = db->d_table;
-    PW.oe = oe; PW.ge = ge; PW.bnd = db->d_bnd3; PW.bnd_stride = db->bnd3_stride;
-    PW.order = db->d_order; PW.scores_file = db->d_scores; PW.error_flag = db->d_counters + 6; PW.min_len = kWaveMinLen;
-    swk::k3w<false><<<db->sm_count * 2, swk::K3W_WARPS * 32, 0, db->s_main>>>(PW);
+    swk::K3WParams W; memset(&W, 0, sizeof(W));
+    W.sidx_list = list; W.work_count = list_count; W.n_work = n_all; W.counter = q_k3w;
+    W.plain = db->d_plain; W.plain_off = db->d_plain_off; W.query = db->d_query; W.lq = lq; W.table = db->d_table;
+    W.oe = oe; W.ge = ge; W.bnd = db->d_bnd3; W.bnd_stride = db->bnd3_stride;
+    W.order = db->d_order; W.scores_file = db->d_scores; W.error_flag = db->d_counters + 6; W.min_len = kWaveMinLen;
+    swk::k3w<false><<<db->sm_count * 2, swk::K3W_WARPS * 32, 0, db->s_main>>>(W);   // after k3 on the same stream: d_bnd3 is shared
     CU(cudaGetLastError());
     ++*launches;
   }
   return SWGPU_OK;
 }
 
-int pick_tile_rows(int64_t lq) {
-  int best_r = kTileChoices[0]; int64_t best_pad = -1;
-  for (int r : kTileChoices) {
-    const int64_t padded = (lq + r - 1) / r * r;
-    if (best_pad < 0 || padded < best_pad) { best_pad = padded; best_r = r; }
-  }
-  return best_r;
-}
+}  // namespace
+
+namespace {
 
 int run_search(swgpu_db* db, const int8_t* query, int64_t lq, const int8_t* table, int gap_open, int gap_extend,
                swgpu_stats_t* stats) {
@@ -267,6 +227,8 @@ int run_search(swgpu_db* db, const int8_t* query, int64_t lq, const int8_t* tabl
   CU(cudaSetDevice(db->device));
   swgpu_stats_t st; memset(&st, 0, sizeof(st));
   db->have_scores = false;
+  cudaEvent_t* e = db->ev;
+  cudaStream_t sm = db->s_main, sa = db->s_aux;
 
   // ---- uploads (query, table) ----
   if (lq > db->query_cap) {
@@ -274,193 +236,127 @@ int run_search(swgpu_db* db, const int8_t* query, int64_t lq, const int8_t* tabl
     db->query_cap = std::max<int64_t>(lq, 1024);
     CU(cudaMalloc((void**)&db->d_query, (size_t)db->query_cap));
   }
-  cudaEvent_t *e = db->ev;
-  CU(cudaEventRecord(e[6], db->s_main));
-  if (lq > 0) CU(cudaMemcpyAsync(db->d_query, query, (size_t)lq, cudaMemcpyHostToDevice, db->s_main));
-  CU(cudaMemcpyAsync(db->d_table, table, 1024, cudaMemcpyHostToDevice, db->s_main));
-  CU(cudaEventRecord(e[7], db->s_main));
+  CU(cudaEventRecord(e[6], sm));
+  if (lq > 0) CU(cudaMemcpyAsync(db->d_query, query, (size_t)lq, cudaMemcpyHostToDevice, sm));
+  CU(cudaMemcpyAsync(db->d_table, table, 1024, cudaMemcpyHostToDevice, sm));
+  CU(cudaEventRecord(e[7], sm));
 
+  // ---- plan ----
+  // 16-bit path: biased unsigned arithmetic with B = 128 + |oe| + |ge| (sw_k1s.cuh); huge gap penalties go 32-bit.
   const unsigned B = 128u + (unsigned)(-oe) + (unsigned)(-ge);
-  const bool use_s = !db->use_old_k1;
-  const bool use16 = (B <= 16384u) && (use_s ? db->n_streams > 0 : db->n_chunks > 0) && lq > 0;
+  const bool use16 = (B <= 16384u) && db->n_streams > 0 && lq > 0;
   const K1SPlan plan = plan_k1s(std::max<int64_t>(lq, 1), db->n_streams, db->k1s_grid * swk::K1S_WARPS);
-  const int R = pick_tile_rows(lq);
-  const int ntiles = lq > 0 ? (int)((lq + R - 1) / R) : 0;
-  st.tile_rows = use16 ? (use_s ? plan.R : R) : 0;
-  st.lanes_per_pair = (use16 && use_s) ? plan.g : 0; st.passes = (use16 && use_s) ? plan.npass : 0;
-  if (use16 && use_s) {
-    const size_t need = (size_t)plan.npass * 32 * ((plan.R + 3) / 4 + plan.R / 2) * 32;
-    if (need > db->sprof_cap) {
-      if (db->d_sprof) { cudaFree(db->d_sprof); db->d_sprof = nullptr; }
-      db->sprof_cap = need + need / 2;
-      CU(cudaMalloc((void**)&db->d_sprof, db->sprof_cap * sizeof(unsigned)));
-    }
-  }
-  // Long streams (one target pair of thousands of columns) are latency-bound on their serial column
-  // chain: when the bulk plan uses fewer than 32 lanes per pair they get their own launch with all
-  // 32 lanes and the fewest rows per lane, started first on the second stream.
+  // Long streams (one target pair of thousands of columns) are latency-bound on their serial column chain: when the
+  // bulk plan uses fewer than 32 lanes per pair they get their own launch with all 32 lanes and the fewest rows per
+  // lane, one stream per CTA, started first on the second CUDA stream.
+  const bool split_long = use16 && plan.npass == 1 && plan.g < 32 && db->n_long_streams > 0;
   K1SPlan plan_long = plan;
-  const bool split_long = use16 && use_s && plan.npass == 1 && plan.g < 32 && db->n_long_streams > 0;
   if (split_long) {
     int R = (int)((lq + 31) / 32); R += R & 1; if (R < 8) R = 8;
     plan_long = K1SPlan{32, 5, R, 1};
-    const size_t need = (size_t)32 * ((R + 3) / 4 + R / 2) * 32;
-    if (need > db->sprof2_cap) {
+  }
+  auto words_of = [](const K1SPlan& p) { return (size_t)p.npass * 32 * ((p.R + 3) / 4 + p.R / 2) * 32; };
+  if (use16) {
+    st.tile_rows = plan.R; st.lanes_per_pair = plan.g; st.passes = plan.npass;
+    if (words_of(plan) > db->sprof_cap) {
+      if (db->d_sprof) { cudaFree(db->d_sprof); db->d_sprof = nullptr; }
+      db->sprof_cap = words_of(plan) * 3 / 2;
+      CU(cudaMalloc((void**)&db->d_sprof, db->sprof_cap * sizeof(unsigned)));
+    }
+    if (split_long && words_of(plan_long) > db->sprof2_cap) {
       if (db->d_sprof2) { cudaFree(db->d_sprof2); db->d_sprof2 = nullptr; }
-      db->sprof2_cap = need * 2;
+      db->sprof2_cap = words_of(plan_long) * 2;
       CU(cudaMalloc((void**)&db->d_sprof2, db->sprof2_cap * sizeof(unsigned)));
     }
   }
-  if (use16 && !use_s) {
-    const size_t need = (size_t)ntiles * 32 * (((R / 4) | 1) + ((R / 2) | 1));
-    if (need > db->prof_cap) {
-      if (db->d_prof) { cudaFree(db->d_prof); db->d_prof = nullptr; }
-      db->prof_cap = need + need / 2;
-      CU(cudaMalloc((void**)&db->d_prof, db->prof_cap * sizeof(unsigned)));
-    }
-  }
 
-  // ---- timed region: first kernel -> last result resident ----
-  CU(cudaEventRecord(e[0], db->s_main));
-  CU(cudaMemsetAsync(db->d_counters, 0, 8 * sizeof(unsigned), db->s_main));
+  // ---- timed region: first kernel -> last result resident in HBM ----
+  CU(cudaEventRecord(e[0], sm));
+  CU(cudaMemsetAsync(db->d_counters, 0, 8 * sizeof(unsigned), sm));
   if (lq == 0 || db->n == 0) {
-    if (db->n) CU(cudaMemsetAsync(db->d_scores, 0, sizeof(int32_t) * (size_t)db->n, db->s_main));
-    CU(cudaEventRecord(e[1], db->s_main));
-    CU(cudaEventRecord(e[2], db->s_main));
-  } else {
-    swk::K3Params P3; memset(&P3, 0, sizeof(P3));
-    P3.plain = db->d_plain; P3.plain_off = db->d_plain_off; P3.query = db->d_query; P3.lq = (int)lq;
-    P3.table = db->d_table; P3.oe = oe; P3.ge = ge; P3.bnd = db->d_bnd3; P3.bnd_stride = db->bnd3_stride;
-    P3.order = db->d_order; P3.scores_file = db->d_scores; P3.one = 1u;
-    if (use16 && use_s) {
-      // systolic kernel over ALL targets (streams of paired targets), then 32-bit rescoring of saturated pairs
-      swk::K1SParams PS; memset(&PS, 0, sizeof(PS));
-      PS.scols = db->d_scols; PS.stream_off = db->d_stream_off; PS.stream_ncols = db->d_stream_ncols;
-      PS.stream_pair0 = db->d_stream_pair0;
-      PS.bnd = db->d_bnd_s; PS.bnd_stride = db->bnd_s_stride;
-      PS.BB = B * 0x10001u; PS.BBM = (B + (unsigned)(-oe)) * 0x10001u;
-      PS.OE2 = ((unsigned)oe & 0xffffu) * 0x10001u; PS.GE2 = ((unsigned)ge & 0xffffu) * 0x10001u;
-      const int fin_grid = (int)std::min<int64_t>((db->n_pairs + 255) / 256, 4096);
-      int r = SWGPU_OK;
-      const int64_t nls = split_long ? db->n_long_streams : 0, nlp = split_long ? db->n_long_pairs : 0;
-      if (split_long) {
-        CU(cudaEventRecord(e[3], db->s_main));
-        CU(cudaStreamWaitEvent(db->s_aux, e[3], 0));
-        swk::build_sprofile<<<32, 256, 0, db->s_aux>>>(db->d_query, (int)lq, db->d_table, plan_long.R, 32, 1, db->d_sprof2);
-        swk::K1SParams PL = PS;
-        PL.stream_begin = 0; PL.n_streams = (int)nls; PL.n_items = (int)nls; PL.prof = db->d_sprof2; PL.npass = 1;
-        PL.g = 32; PL.g_log2 = 5; PL.counter = db->d_counters + 1; PL.raw = db->d_raw_s;
-        PL.active_warps = 1;                                  // one long stream per CTA: spread them over the SMs
-        r = launch_k1s(db, PL, plan_long.R, false, db->s_aux, (int)std::min<int64_t>(nls, db->k1s_grid));
-        if (r) return r;
-        swk::k1s_finalize<<<std::max(1, (int)((nlp + 255) / 256)), 256, 0, db->s_aux>>>(
-            db->d_raw_s, 0, (long)nlp, 5, (long)db->n, B, 65535u - 129u, db->d_order, db->d_scores,
-            db->d_rescore_list, db->d_counters + 2);
-        CU(cudaGetLastError()); st.kernel_launches += 3;
-        CU(cudaEventRecord(e[4], db->s_aux));
-      }
-      swk::build_sprofile<<<std::min(2048, (int)((size_t)plan.npass * 24 * 1024 / 256) + 1), 256, 0, db->s_main>>>(
-          db->d_query, (int)lq, db->d_table, plan.R, plan.g, plan.npass, db->d_sprof);
-      CU(cudaGetLastError()); st.kernel_launches++;
-      const int per_warp = 32 / plan.g;
-      PS.stream_begin = (int)nls; PS.n_streams = (int)(db->n_streams - nls);
-      PS.n_items = (PS.n_streams + per_warp - 1) / per_warp;
-      PS.prof = db->d_sprof; PS.npass = plan.npass; PS.g = plan.g; PS.g_log2 = plan.g_log2;
-      PS.counter = db->d_counters + 0;
-      // the bulk's [pair][g] maxima start after the long launch's [pair][32] region
-      PS.raw = db->d_raw_s + (size_t)nlp * 32 - ((size_t)nlp << plan.g_log2);
-      if (PS.n_streams > 0) {
-        PS.active_warps = swk::K1S_WARPS;
-        r = launch_k1s(db, PS, plan.R, plan.npass > 1, db->s_main, db->k1s_grid); if (r) return r;
-        st.kernel_launches++;
-        swk::k1s_finalize<<<fin_grid, 256, 0, db->s_main>>>(
-            PS.raw, (long)nlp, (long)db->n_pairs, plan.g_log2, (long)db->n, B, 65535u - 129u, db->d_order, db->d_scores,
-            db->d_rescore_list, db->d_counters + 2);
-        CU(cudaGetLastError()); st.kernel_launches++;
-      }
-      if (split_long) CU(cudaStreamWaitEvent(db->s_main, e[4], 0));
-      CU(cudaEventRecord(e[1], db->s_main));
-      r = launch_rescore(db, P3, (int)lq, oe, ge, &st.kernel_launches); if (r) return r;
-      CU(cudaEventRecord(e[2], db->s_main));
-    } else if (use16) {
-      // long targets on the aux stream, concurrently with K1
-      CU(cudaEventRecord(e[3], db->s_main));
-      if (db->n_long > 0) {
-        CU(cudaStreamWaitEvent(db->s_aux, e[3], 0));
-        swk::K3Params PL = P3; PL.worklist = nullptr; PL.n_work = (int)db->n_long; PL.counter = db->d_counters + 1;
-        int r = launch_k3(db, db->s_aux, PL, (int)lq); if (r) return r;
-        st.kernel_launches++;
-        CU(cudaEventRecord(e[4], db->s_aux));
-      }
-      swk::build_profile<<<std::min(1024, (ntiles * 26 * 32 + 255) / 256 + 1), 256, 0, db->s_main>>>(
-          db->d_query, (int)lq, db->d_table, R, (R / 4) | 1, (R / 2) | 1, ntiles, db->d_prof);
-      CU(cudaGetLastError()); st.kernel_launches++;
-      swk::K1Params P1; memset(&P1, 0, sizeof(P1));
-      P1.cols = db->d_cols; P1.chunk_off = db->d_chunk_off; P1.chunk_cols = db->d_chunk_cols; P1.n_chunks = (int)db->n_chunks;
-      P1.prof = db->d_prof; P1.ntiles = ntiles; P1.bnd = db->d_bnd1; P1.bnd_stride = db->bnd1_stride;
-      P1.counter = db->d_counters + 0; P1.raw_out = db->d_raw;
-      P1.BB = B | (B << 16); P1.OE32 = (unsigned)(oe * 65537); P1.GE2 = ((unsigned)ge & 0xffffu) * 0x10001u; P1.one = 1u;
-      int r = SWGPU_OK;
-      switch (R) {
-        case 32: r = launch_k1<32>(db, P1); break;
-        case 28: r = launch_k1<28>(db, P1); break;
-        case 24: r = launch_k1<24>(db, P1); break;
-        case 20: r = launch_k1<20>(db, P1); break;
-        default: r = launch_k1<16>(db, P1); break;
-      }
-      if (r) return r;
-      st.kernel_launches++;
-      const long n_lanes = (long)db->n_chunks * 32;
-      swk::k1_finalize<<<(int)std::min<long>((n_lanes + 255) / 256, 2048), 256, 0, db->s_main>>>(
-          db->d_raw, n_lanes, (long)db->n_long, (long)db->n, B, 65535u - 129u, db->d_order, db->d_scores,
-          db->d_rescore_list, db->d_counters + 2);
-      CU(cudaGetLastError()); st.kernel_launches++;
-      CU(cudaEventRecord(e[1], db->s_main));
-      // 32-bit rescoring of saturated targets (count lives on the device)
-      r = launch_rescore(db, P3, (int)lq, oe, ge, &st.kernel_launches); if (r) return r;
-      if (db->n_long > 0) CU(cudaStreamWaitEvent(db->s_main, e[4], 0));
-      CU(cudaEventRecord(e[2], db->s_main));
-    } else {
-      swk::K3Params PA = P3; PA.worklist = nullptr; PA.n_work = (int)db->n; PA.counter = db->d_counters + 1;
-      int r = launch_k3(db, db->s_main, PA, (int)lq); if (r) return r;
-      st.kernel_launches++;
-      CU(cudaEventRecord(e[1], db->s_main));
-      CU(cudaEventRecord(e[2], db->s_main));
+    if (db->n) CU(cudaMemsetAsync(db->d_scores, 0, sizeof(int32_t) * (size_t)db->n, sm));
+    CU(cudaEventRecord(e[1], sm));
+  } else if (use16) {
+    swk::K1SParams PS; memset(&PS, 0, sizeof(PS));
+    PS.scols = db->d_scols; PS.stream_off = db->d_stream_off; PS.stream_ncols = db->d_stream_ncols;
+    PS.stream_pair0 = db->d_stream_pair0; PS.bnd = db->d_bnd_s; PS.bnd_stride = db->bnd_s_stride;
+    PS.BB = B * 0x10001u; PS.BBM = (B + (unsigned)(-oe)) * 0x10001u;
+    PS.OE2 = ((unsigned)oe & 0xffffu) * 0x10001u; PS.GE2 = ((unsigned)ge & 0xffffu) * 0x10001u;
+    const unsigned limit = 65535u - 129u;
+    const int64_t nls = split_long ? db->n_long_streams : 0, nlp = split_long ? db->n_long_pairs : 0;
+    int r;
+    if (split_long) {
+      CU(cudaEventRecord(e[3], sm));
+      CU(cudaStreamWaitEvent(sa, e[3], 0));
+      swk::build_sprofile<<<32, 256, 0, sa>>>(db->d_query, (int)lq, db->d_table, plan_long.R, 32, 1, db->d_sprof2);
+      swk::K1SParams PL = PS;
+      PL.stream_begin = 0; PL.n_streams = (int)nls; PL.n_items = (int)nls; PL.prof = db->d_sprof2; PL.npass = 1;
+      PL.g = 32; PL.g_log2 = 5; PL.counter = db->d_counters + 1; PL.raw = db->d_raw_s;
+      PL.active_warps = 1;                                     // one long stream per CTA: spread them over the SMs
+      if ((r = launch_k1s(db, PL, plan_long.R, false, sa, (int)std::min<int64_t>(nls, db->k1s_grid)))) return r;
+      swk::k1s_finalize<<<std::max(1, (int)((nlp + 255) / 256)), 256, 0, sa>>>(
+          db->d_raw_s, 0, (long)nlp, 5, (long)db->n, B, limit, db->d_order, db->d_plain_off, db->long_threshold,
+          db->d_scores, db->d_rescore_list, db->d_counters + 2);
+      CU(cudaGetLastError()); st.kernel_launches += 3;
+      CU(cudaEventRecord(e[4], sa));
     }
+    swk::build_sprofile<<<std::min(2048, (int)(words_of(plan) / 256) + 1), 256, 0, sm>>>(
+        db->d_query, (int)lq, db->d_table, plan.R, plan.g, plan.npass, db->d_sprof);
+    CU(cudaGetLastError()); st.kernel_launches++;
+    const int per_warp = 32 / plan.g;
+    PS.stream_begin = (int)nls; PS.n_streams = (int)(db->n_streams - nls);
+    PS.n_items = (PS.n_streams + per_warp - 1) / per_warp;
+    PS.prof = db->d_sprof; PS.npass = plan.npass; PS.g = plan.g; PS.g_log2 = plan.g_log2;
+    PS.counter = db->d_counters + 0; PS.active_warps = swk::K1S_WARPS;
+    // the bulk's [pair][g] maxima start after the long launch's [pair][32] region
+    PS.raw = db->d_raw_s + (size_t)nlp * 32 - ((size_t)nlp << plan.g_log2);
+    if (PS.n_streams > 0) {
+      if ((r = launch_k1s(db, PS, plan.R, plan.npass > 1, sm, db->k1s_grid))) return r;
+      swk::k1s_finalize<<<(int)std::min<int64_t>((db->n_pairs - nlp + 255) / 256, 4096), 256, 0, sm>>>(
+          PS.raw, (long)nlp, (long)db->n_pairs, plan.g_log2, (long)db->n, B, limit, db->d_order, db->d_plain_off,
+          db->long_threshold, db->d_scores, db->d_rescore_list, db->d_counters + 2);
+      CU(cudaGetLastError()); st.kernel_launches += 2;
+    }
+    if (split_long) CU(cudaStreamWaitEvent(sm, e[4], 0));
+    CU(cudaEventRecord(e[1], sm));
+    // 32-bit rescoring of the saturated (or forced) targets; the count lives on the device
+    if ((r = launch_32bit(db, db->d_rescore_list, db->d_counters + 2, 0, (int)lq, oe, ge, db->d_counters + 3,
+                          db->d_counters + 4, &st.kernel_launches))) return r;
+  } else {
+    CU(cudaEventRecord(e[1], sm));
+    int r;
+    if ((r = launch_32bit(db, nullptr, nullptr, (int)db->n, (int)lq, oe, ge, db->d_counters + 5, db->d_counters + 4,
+                          &st.kernel_launches))) return r;
   }
-  CU(cudaStreamSynchronize(db->s_main));
-  CU(cudaStreamSynchronize(db->s_aux));
+  CU(cudaEventRecord(e[2], sm));
+  CU(cudaStreamSynchronize(sm));
+  CU(cudaStreamSynchronize(sa));
   db->have_scores = true;
-  db->last_lq = lq;
-  db->last_oe = oe; db->last_ge = ge;
+  db->last_lq = lq; db->last_oe = oe; db->last_ge = ge;
 
   float ms = 0;
   CU(cudaEventElapsedTime(&ms, e[0], e[2])); st.ms_total = ms;
   CU(cudaEventElapsedTime(&ms, e[6], e[7])); st.ms_h2d = ms;
   st.cells = lq * db->n_residues;
   if (lq > 0 && db->n > 0) {
+    unsigned ctr[8] = {};
+    CU(cudaMemcpy(ctr, db->d_counters, sizeof(ctr), cudaMemcpyDeviceToHost));
+    if (ctr[6]) return fail(SWGPU_ECUDA, "32-bit wavefront kernel stalled (internal error)");
     if (use16) {
       CU(cudaEventElapsedTime(&ms, e[0], e[1])); st.ms_inter = ms;
       CU(cudaEventElapsedTime(&ms, e[1], e[2])); st.ms_rescore = ms;
-      const int64_t n_long = use_s ? 0 : db->n_long;
-      if (n_long > 0) { CU(cudaEventElapsedTime(&ms, e[3], e[4])); st.ms_intra = ms; }
-      st.n_long = n_long;
-      st.cells_intra = lq * db->h_len_sorted_prefix[n_long];
-      st.cells_inter = st.cells - st.cells_intra;
-      unsigned ctr[8] = {};
-      CU(cudaMemcpy(ctr, db->d_counters, sizeof(ctr), cudaMemcpyDeviceToHost));
-      if (ctr[6]) return fail(SWGPU_ECUDA, "32-bit wavefront rescoring stalled (internal error)");
-      const unsigned nres = ctr[2];
-      st.n_rescored = nres;
-      if (nres) {
-        std::vector<int> lst(nres);
-        CU(cudaMemcpy(lst.data(), db->d_rescore_list, sizeof(int) * nres, cudaMemcpyDeviceToHost));
+      if (split_long) { CU(cudaEventElapsedTime(&ms, e[3], e[4])); st.ms_intra = ms; st.n_long = 2 * db->n_long_pairs; }
+      st.cells_inter = st.cells;
+      st.n_rescored = ctr[2];
+      if (ctr[2]) {
+        std::vector<int> lst(ctr[2]);
+        CU(cudaMemcpy(lst.data(), db->d_rescore_list, sizeof(int) * ctr[2], cudaMemcpyDeviceToHost));
         int64_t res = 0;
         for (int s : lst) res += db->h_len_sorted_prefix[s + 1] - db->h_len_sorted_prefix[s];
         st.cells_rescore = lq * res;
       }
     } else {
-      st.ms_intra = st.ms_total; st.n_long = db->n; st.cells_intra = st.cells;
+      st.ms_rescore = st.ms_total; st.n_rescored = db->n; st.cells_rescore = st.cells;
     }
   }
   db->last_stats = st;
@@ -522,4 +418,3 @@ int swgpu_fill_batch16(int device, const int8_t* query, int64_t query_len, const
 }
 
 }  // extern "C"
-

@@ -25,49 +25,39 @@ inline int fail(int code, const char* fmt, ...) {
 struct swgpu_db {
   int device = 0;
   int sm_count = 0;
-  int64_t n = 0, n_residues = 0, n_long = 0, n_chunks = 0, entry_base = 0;
-  int32_t max_len = 0, max_chunk_cols = 0;
-  // device arrays (database, resident)
-  int8_t*   d_plain = nullptr;
-  int64_t*  d_plain_off = nullptr;
-  int64_t*  d_order = nullptr;
-  uint2*    d_cols = nullptr;
-  int64_t*  d_chunk_off = nullptr;
-  int32_t*  d_chunk_cols = nullptr;
-  // streams of paired targets (systolic kernel K1S)
-  uint16_t* d_scols = nullptr;
+  int64_t n = 0, n_residues = 0, entry_base = 0;
+  int32_t max_len = 0;
+  int32_t long_threshold = 0;          // > 0: targets longer than this always take the 32-bit kernels
+  // database, resident in HBM
+  int8_t*   d_plain = nullptr;         // residues, sorted order, back to back
+  int64_t*  d_plain_off = nullptr;     // n + 1
+  int64_t*  d_order = nullptr;         // sorted position -> file index
+  uint16_t* d_scols = nullptr;         // streams of paired targets (db_pack.h)
   int64_t*  d_stream_off = nullptr;
   int32_t*  d_stream_ncols = nullptr;
   int64_t*  d_stream_pair0 = nullptr;
   int64_t   n_pairs = 0, n_streams = 0;
   int32_t   max_stream_cols = 0;
-  unsigned* d_raw_s = nullptr;         // n_pairs * 32
   int64_t   n_long_streams = 0, n_long_pairs = 0;   // leading long streams get their own low-latency launch
-  unsigned* d_sprof2 = nullptr;  size_t sprof2_cap = 0;
-  uint2*    d_bnd_s = nullptr;  long long bnd_s_stride = 0;  int k1s_grid = 0;
-  unsigned* d_sprof = nullptr;  size_t sprof_cap = 0;
-  int       use_old_k1 = 0;
-  // device scratch (per search)
+  // per-search scratch
   int32_t*  d_scores = nullptr;        // file order
-  unsigned* d_raw = nullptr;           // n_chunks*32
+  unsigned* d_raw_s = nullptr;         // n_pairs * 32 packed running maxima
   int*      d_rescore_list = nullptr;  // up to n
-  unsigned* d_counters = nullptr;      // [0]=k1 queue, [1]=k3 long queue, [2]=rescore count, [3]=k3 rescore queue
-  uint2*    d_bnd1 = nullptr;  long long bnd1_stride = 0;  int k1_grid = 0;
-  int2*     d_bnd3 = nullptr;  long long bnd3_stride = 0;  int k3_grid = 0;
-  int8_t*   d_query = nullptr; int64_t query_cap = 0;
+  unsigned* d_counters = nullptr;      // [0] k1s queue, [1] k1s long queue, [2] rescore count, [3] k3 queue, [4] k3w queue,
+                                       // [5] k3 all-targets queue, [6] k3w error flag, [7] top-k error flag
+  uint2*    d_bnd_s = nullptr;  long long bnd_s_stride = 0;  int k1s_grid = 0;   // k1s multi-stripe carry rows
+  int2*     d_bnd3 = nullptr;   long long bnd3_stride = 0;   int k3_grid = 0;    // k3 / k3w carry rows
+  int8_t*   d_query = nullptr;  int64_t query_cap = 0;
   int8_t*   d_table = nullptr;
-  unsigned* d_prof = nullptr;  size_t prof_cap = 0;
+  unsigned* d_sprof = nullptr;  size_t sprof_cap = 0;     // k1s profile (bulk plan)
+  unsigned* d_sprof2 = nullptr; size_t sprof2_cap = 0;    // k1s profile (long-stream plan)
   int64_t   device_bytes = 0;
-  // host copies needed after packing
-  std::vector<int64_t> h_order;
-  std::vector<int64_t> h_len_sorted_prefix;   // plain_off (sorted)
+  std::vector<int64_t> h_len_sorted_prefix;               // plain_off on the host (statistics, top-k buffers)
   cudaStream_t s_main = nullptr, s_aux = nullptr;
   cudaEvent_t ev[8] = {};
-
   int64_t last_lq = 0;
   bool have_scores = false;
-  // gaps of the last search (top-k coordinates are recomputed against the last query / table)
-  int last_oe = 0, last_ge = 0;
+  int last_oe = 0, last_ge = 0;        // gaps of the last search (top-k coordinates are recomputed against it)
   // top-k scratch
   unsigned long long* d_keys = nullptr;  int* d_hit_sidx = nullptr;  void* d_sel = nullptr;  int topk_cap = 0;
   int4* d_coords = nullptr;

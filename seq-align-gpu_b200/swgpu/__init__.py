@@ -41,8 +41,7 @@ class Hit(C.Structure):
 
 
 class PackOpts(C.Structure):
-    _fields_ = [("long_threshold", C.c_int32), ("stream_cols", C.c_int32), ("use_chunk_kernel", C.c_int32),
-                ("reserved", C.c_int32 * 5)]
+    _fields_ = [("long_threshold", C.c_int32), ("stream_cols", C.c_int32), ("reserved", C.c_int32 * 6)]
 
 
 _lib = None
@@ -98,13 +97,13 @@ def _i8(a):
 class Database:
     """Packed, HBM-resident database on one GPU (swgpu_db_t)."""
 
-    def __init__(self, codes, offsets, device=0, entry_base=0, long_threshold=0, stream_cols=0, chunk_kernel=False):
+    def __init__(self, codes, offsets, device=0, entry_base=0, long_threshold=0, stream_cols=0):
         L = lib()
         self._codes, pc = _i8(codes)
         self._off = np.ascontiguousarray(offsets, dtype=np.int64)
         self.n = len(self._off) - 1
         h = C.c_void_p()
-        opts = PackOpts(long_threshold=long_threshold, stream_cols=stream_cols, use_chunk_kernel=int(chunk_kernel))
+        opts = PackOpts(long_threshold=long_threshold, stream_cols=stream_cols)
         _check(L.swgpu_db_create(C.byref(h), device, pc, self._off.ctypes.data_as(C.c_void_p), self.n, entry_base,
                                  C.byref(opts)))
         self._h = h

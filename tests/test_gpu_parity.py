@@ -31,7 +31,7 @@ def test_reference_golden_vectors(swgpu_mod, name):
     """Scores produced by the unmodified reference (tests/golden/make_golden.py)."""
     g = golden(f"ref16_{name}.npz")
     codes, off, q, tab = g["codes"], g["off"], g["query"], g["table"]
-    for long_thr in (0, 200):                       # default split, and a split that sends the top to K3
+    for long_thr in (0, 200):                       # 16-bit only, and targets > 200 aa re-scored by the 32-bit kernel
         db = swgpu_mod.Database(codes, off, long_threshold=long_thr)
         for lq in (1, 7, 33, 144, 360, 700):
             for go, ge in GAPS:
@@ -190,6 +190,25 @@ def test_config4_long_sequences_scaled(swgpu_mod, oracle, matrices):
     codes = np.concatenate(parts)
     got, st = check(swgpu_mod, oracle, q, codes, off, tab, -10, -1)
     assert got[1] > 65535 and st["n_rescored"] >= 1
+
+
+def test_32bit_kernels_on_everything(swgpu_mod, oracle, matrices):
+    """long_threshold=1 sends every target through the 32-bit kernels: k3_intra (< 4096 aa) and the
+    wavefront kernel k3w (>= 4096 aa, several groups of stripes for the 2 700-aa query)."""
+    from swgpu import synth
+    g = synth.rng(77)
+    lens = [9000, 6500, 4096, 4095, 5000] + list(synth.lognormal_lengths(g, 300))
+    parts = [synth.residues(g, int(L)) for L in lens]
+    q = synth.make_query(78, 2700)
+    parts[1][1000:3000] = q[300:2300]
+    off = np.zeros(len(parts) + 1, np.int64); np.cumsum([p.size for p in parts], out=off[1:])
+    codes = np.concatenate(parts)
+    for lq in (2700, 100, 129):
+        got, st = check(swgpu_mod, oracle, q[:lq], codes, off, matrices["BLOSUM45"], -12, -2, long_threshold=1)
+        assert st["n_rescored"] == len(parts)
+    # huge gap penalties: the 16-bit bias does not fit -> the 32-bit kernels score the whole database directly
+    got, st = check(swgpu_mod, oracle, q[:300], codes, off, matrices["BLOSUM62"], -20000, -1)
+    assert st["tile_rows"] == 0
 
 
 def test_resident_search_and_d2h(swgpu_mod, oracle, matrices):

@@ -71,15 +71,19 @@ WORKER = textwrap.dedent("""
     want = np.stack([allsc[oo], np.arange(2000)[oo]], axis=1)
     assert np.array_equal(merged, want), (rank, merged[:5], want[:5])
     dist.barrier(); dist.destroy_process_group()
-    print("rank", rank, "ok")
+    open(os.path.join(sys.argv[2], f"ok_{rank}"), "w").write("ok")
 """)
 
 
 def test_gloo_world2_gather_and_merge(tmp_path):
+    import socket
     w = tmp_path / "worker.py"
     w.write_text(WORKER)
+    with socket.socket() as sk:
+        sk.bind(("127.0.0.1", 0))
+        port = sk.getsockname()[1]
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
-                        "--master-addr", "127.0.0.1", "--master-port", "29611", str(w), ROOT],
+                        "--master-addr", "127.0.0.1", "--master-port", str(port), str(w), ROOT, str(tmp_path)],
                        capture_output=True, text=True, timeout=180, env={**os.environ, "OMP_NUM_THREADS": "1"})
     assert r.returncode == 0, r.stdout + r.stderr
-    assert "rank 0 ok" in r.stdout and "rank 1 ok" in r.stdout
+    assert (tmp_path / "ok_0").exists() and (tmp_path / "ok_1").exists()
