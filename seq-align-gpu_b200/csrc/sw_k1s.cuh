@@ -80,6 +80,9 @@ struct K1SParams {
 };
 
 constexpr int K1S_WARPS = 8;
+#ifndef K1S_R3CTA
+#define K1S_R3CTA 18                         // R up to this: three CTAs per SM (<= 85 registers per thread)
+#endif
 
 template <int R>
 constexpr size_t k1s_smem_bytes() {
@@ -90,7 +93,7 @@ constexpr size_t k1s_smem_bytes() {
 // MULTI = true : g == 32, several stripes; the CTA pulls 8 items at a time and reloads the
 //                shared profile between stripes.
 template <int R, bool MULTI>
-__global__ void __launch_bounds__(K1S_WARPS * 32, 2) k1s(const K1SParams P) {
+__global__ void __launch_bounds__(K1S_WARPS * 32, (R <= K1S_R3CTA ? 3 : 2)) k1s(const K1SParams P) {
   using S = SProf<R>;
   extern __shared__ __align__(16) unsigned smem_u32[];
   unsigned* prof_s = smem_u32;

@@ -7,6 +7,7 @@
 #include "sw_k1s.cuh"
 #include "sw_k3w.cuh"
 
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <vector>
@@ -108,7 +109,7 @@ int swgpu_db_create(swgpu_db_t** out, int device, const int8_t* codes, const int
     CU(cudaMemcpy(db->d_stream_ncols, pk.stream_ncols, sizeof(int32_t) * (size_t)pk.n_streams, cudaMemcpyHostToDevice));
     CU(cudaMemcpy(db->d_stream_pair0, pk.stream_pair0, sizeof(int64_t) * (size_t)pk.n_streams, cudaMemcpyHostToDevice));
     // persistent grids: k1s two CTAs of 8 warps per SM; k3 at most four CTAs of 4 warps per SM
-    db->k1s_grid = db->sm_count * 2;
+    db->k1s_grid = db->sm_count * 3;                          // upper bound of resident k1s CTAs (carry-row slots)
     db->bnd_s_stride = ((long long)std::max<int32_t>(pk.max_stream_cols, 64) + 63) & ~63ll;
     if ((r = dalloc(db, &db->d_bnd_s, (size_t)db->k1s_grid * swk::K1S_WARPS * (size_t)db->bnd_s_stride))) return r;
     db->k3_grid = db->sm_count * 4;
@@ -156,6 +157,14 @@ K1SPlan plan_k1s(int64_t lq, int64_t n_streams, int warp_slots) {
       if (best_cost < 0 || cost < best_cost) { best_cost = cost; best = K1SPlan{32, 5, R, np}; }
     }
   }
+  if (const char* ev = getenv("SWGPU_K1S_PLAN")) {               // "g,R": profiling override of the plan
+    int g = 0, R = 0;
+    if (sscanf(ev, "%d,%d", &g, &R) == 2 && (g == 8 || g == 16 || g == 32) && R >= 8 && R <= 32 && !(R & 1)) {
+      const int gl = g == 8 ? 3 : g == 16 ? 4 : 5;
+      const int np = (int)((lq + (int64_t)g * R - 1) / ((int64_t)g * R));
+      if (np == 1 || (g == 32 && (R == 16 || R == 20 || R >= 24))) best = K1SPlan{g, gl, R, np};
+    }
+  }
   return best;
 }
 
@@ -176,7 +185,7 @@ int launch_k1s(swgpu_db* db, const swk::K1SParams& P, int R, bool multi, cudaStr
 #define K1S_CASE(r) case r: return multi ? launch_k1s_t<r, true>(db, P, stream, grid) : launch_k1s_t<r, false>(db, P, stream, grid);
 #define K1S_CASE1(r) case r: return launch_k1s_t<r, false>(db, P, stream, grid);
   switch (R) {
-    K1S_CASE1(8) K1S_CASE1(10) K1S_CASE1(12) K1S_CASE1(14) K1S_CASE1(16) K1S_CASE1(18) K1S_CASE1(20) K1S_CASE1(22)
+    K1S_CASE1(8) K1S_CASE1(10) K1S_CASE1(12) K1S_CASE1(14) K1S_CASE(16) K1S_CASE1(18) K1S_CASE(20) K1S_CASE1(22)
     K1S_CASE(24) K1S_CASE(26) K1S_CASE(28) K1S_CASE(30) K1S_CASE(32)
     default: return fail(SWGPU_EINVAL, "no k1s instantiation for R=%d", R);
   }
@@ -311,7 +320,9 @@ int run_search(swgpu_db* db, const int8_t* query, int64_t lq, const int8_t* tabl
     // the bulk's [pair][g] maxima start after the long launch's [pair][32] region
     PS.raw = db->d_raw_s + (size_t)nlp * 32 - ((size_t)nlp << plan.g_log2);
     if (PS.n_streams > 0) {
-      if ((r = launch_k1s(db, PS, plan.R, plan.npass > 1, sm, db->k1s_grid))) return r;
+      int ctas = plan.R <= K1S_R3CTA ? 3 : 2;
+      if (const char* ev = getenv("SWGPU_K1S_CTAS")) ctas = std::max(1, std::min(ctas, atoi(ev)));   // A/B knob (profiling)
+      if ((r = launch_k1s(db, PS, plan.R, plan.npass > 1, sm, db->sm_count * ctas))) return r;
       swk::k1s_finalize<<<(int)std::min<int64_t>((db->n_pairs - nlp + 255) / 256, 4096), 256, 0, sm>>>(
           PS.raw, (long)nlp, (long)db->n_pairs, plan.g_log2, (long)db->n, B, limit, db->d_order, db->d_plain_off,
           db->long_threshold, db->d_scores, db->d_rescore_list, db->d_counters + 2);
