@@ -11,10 +11,12 @@ over the HBM-resident database = 41 752 x n_residues cell updates per GPU.  N > 
 rank holds its own 205 M-residue shard (the database shards by residue count, no data-path collective);
 after each step the per-rank top-k lists are merged with one small NCCL all_gather.
 
-value  = GCUPS, device-timed (CUDA events on the engine's stream: first kernel launch -> last result
-         resident in HBM), real unpadded cells of all ranks / max-over-ranks time.
-e2e    = same metric through the host-facing C-ABI call swgpu_search(): query + table in host memory,
-         H2D inside, kernels, D2H of all per-entry scores into host memory, host wall clock.
+value  = GCUPS, device-timed (CUDA events on the engine's streams: first kernel launch of the sweep -> last
+         top-k result of the sweep), real unpadded cells of all ranks / max-over-ranks time.  The sweep goes
+         through swgpu_search_many(): up to three queries in flight, so one query's tail overlaps the next.
+e2e    = same metric through the host-facing C-ABI call swgpu_search_many() with HOST buffers: queries + table
+         in host memory, H2D inside, kernels, D2H of all per-entry scores of every query into pinned host
+         memory, host wall clock.
 roofline = dominant kernel (K1, packed 16-bit inter-sequence) against the measured integer-ALU-pipe
          cell-update roofline (DESIGN.md "Roofline"); the HBM view is reported beside it.
 cpu_baseline = the reference's own AVX2/OpenMP kernel (oracle/_ref/libalign_ref.so, the unmodified
@@ -218,7 +220,6 @@ def main():
     n = len(off) - 1
     n_res = int(off[-1])
     cells_step = sum(len(q) for q in queries) * n_res
-    host_scores = np.empty(n, dtype=np.int32)
 
     def barrier():
         torch.cuda.synchronize()
@@ -233,19 +234,28 @@ def main():
         return gather_topk([[h["score"], h["entry"]] for h in hits_local], TOPK, dist, device="cuda" if dist is not None else None)
 
     def step_resident():
-        ms, launches, k1ms, k1cells, resc = 0.0, 0, 0.0, 0, 0
+        """The sweep through swgpu_search_many(): up to three queries in flight, scores stay in HBM, top-k with
+        coordinates per query; then the per-query merge (NCCL all_gather when N > 1)."""
+        _, hits, per, bs = db.search_many(queries, tab, GAP_OPEN, GAP_EXTEND, k=TOPK, want_scores=False)
+        for h in hits:
+            merge_topk(h)
+        return bs["ms_total"], bs["kernel_launches"], bs["n_rescored"]
+
+    def step_serial():
+        """Same sweep, one query at a time (nothing overlaps): the pass the per-kernel K1S time is taken from."""
+        ms, k1ms, k1cells = 0.0, 0.0, 0
         for q in queries:
             st = db.search_resident(q, tab, GAP_OPEN, GAP_EXTEND)
-            hits = db.topk(TOPK)
-            merge_topk(hits)
-            ms += st["ms_total"] + db.last_topk_ms; launches += st["kernel_launches"] + db.last_topk_launches
-            k1ms += st["ms_inter"]; k1cells += st["cells_inter"]; resc += st["n_rescored"]
-        return ms, launches, k1ms, k1cells, resc
+            db.topk(TOPK)
+            ms += st["ms_total"] + db.last_topk_ms
+            k1ms += st["ms_inter"]; k1cells += st["cells_inter"]
+        return ms, k1ms, k1cells
+
+    pinned = [torch.empty(n, dtype=torch.int32).pin_memory().numpy() for _ in queries]
 
     def step_e2e():
         t = time.perf_counter()
-        for q in queries:
-            db.search(q, tab, GAP_OPEN, GAP_EXTEND, out=host_scores)
+        db.search_many(queries, tab, GAP_OPEN, GAP_EXTEND, k=0, out=pinned)
         return time.perf_counter() - t
 
     for _ in range(a.warmup):
@@ -253,13 +263,21 @@ def main():
     barrier()
     sampler = ClockSampler(local); sampler.start(); time.sleep(0.25)
     tw0 = time.time()
-    dev_ms, launches, k1ms, k1cells, resc = 0.0, 0, 0.0, 0, 0
+    dev_ms, launches, resc = 0.0, 0, 0
     for _ in range(a.steps):
         r = step_resident()
-        dev_ms += r[0]; launches += r[1]; k1ms += r[2]; k1cells += r[3]; resc += r[4]
+        dev_ms += r[0]; launches += r[1]; resc += r[2]
     barrier()
     tw1 = time.time()
     clocks = sampler.stop(tw0, tw1)
+
+    # per-kernel time of the dominant kernel: the same K steps, serially (in the pipelined region above the
+    # event intervals of consecutive queries overlap, so they cannot be added up)
+    ser_ms, k1ms, k1cells = 0.0, 0.0, 0
+    for _ in range(a.steps):
+        r = step_serial()
+        ser_ms += r[0]; k1ms += r[1]; k1cells += r[2]
+    barrier()
 
     # e2e: host buffers in, host buffers out, wall clock
     step_e2e()
@@ -303,13 +321,17 @@ def main():
             "e2e": {"value": cells_all * a.steps / e2e_max / 1e9, "unit": "GCUPS",
                     "h2d_bytes_per_step": int(sum(len(q) + 1024 for q in queries)),
                     "d2h_bytes_per_step": int(len(queries) * 4 * n),
-                    "note": "swgpu_search(): host query/table in, all per-entry int32 scores out to host memory, host wall clock; "
-                            "database packed and HBM-resident (one-off cost in setup_s)"},
+                    "note": "swgpu_search_many(): host queries/table in, all per-entry int32 scores of every query out to pinned host "
+                            "memory, host wall clock; bytes are per rank; database packed and HBM-resident (one-off cost in setup_s)"},
             "roofline": {"bound": "int-alu", "kernel": "k1s", "achieved": k1_gcups, "peak": peak_gcups, "unit": "GCUPS",
                          "frac": k1_gcups / peak_gcups if peak_gcups else None,
                          "peak_how": f"{alu_rate:.3f} warp-inst/clk/SM {alu_src} x 32 lanes x {sms} SMs x {sm_max:.0f} MHz / 2.25 ALU-pipe "
                                      f"thread-instructions per cell",
-                         "sm_mhz_seen": sm_clk, "k1_ms_per_step": k1ms / a.steps, "k1_share_of_step": k1ms / dev_ms if dev_ms else None,
+                         "sm_mhz_seen": sm_clk, "k1_ms_per_step": k1ms / a.steps,
+                         "k1_share_of_step": k1ms / ser_ms if ser_ms else None,
+                         "k1_timing": "CUDA events around K1S in a serial pass of the same K steps right after the timed region "
+                                      "(one query at a time; in the pipelined region consecutive queries overlap)",
+                         "serial_ms_per_step": ser_ms / a.steps,
                          "traffic": None,
                          "hbm": {"achieved": hbm_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": hbm_gbs / hbm_peak, "peak_src": peak_src}},
             "cpu_baseline": cpu,

@@ -113,6 +113,33 @@ int swgpu_db_scores_d2h(swgpu_db_t *db, int32_t *scores);
  */
 int swgpu_topk(swgpu_db_t *db, int k, swgpu_hit_t *hits, int *n_hits);
 
+/*
+ * Many queries against the resident database: the many-to-many front end the reference's report names as
+ * the natural extension (it reads a single query, src/alignment_cmdline.c:369-380).  Up to three queries are
+ * in flight on separate CUDA streams and scratch buffers, so the latency-bound tail of one query (long
+ * targets, 32-bit rescoring, top-k selection and coordinates, score read-back) overlaps the bulk kernel of
+ * the next.  Results are identical to n_queries calls of swgpu_search() + swgpu_topk().
+ *   queries[q], query_lens[q]  host pointers
+ *   scores      NULL, or n_queries host pointers (each NULL or int32[n_targets], file order); pinned buffers are
+ *               written directly by the copy engine, pageable ones through an internal pinned staging buffer
+ *   k, hits, n_hits   k > 0: hits[q*k .. q*k+n_hits[q]) = top hits of query q with coordinates; k == 0: none
+ *   per_query   NULL or n_queries statistics (their ms_* include time spent queued behind other queries)
+ *   batch       NULL or totals; ms_total = first kernel of the batch -> last result of the batch in host memory
+ */
+typedef struct {
+    double  ms_total;
+    int64_t cells;
+    int64_t n_rescored;
+    int32_t kernel_launches;
+    int32_t slots;            /* queries kept in flight */
+    int32_t reserved[4];
+} swgpu_batch_stats_t;
+
+int swgpu_search_many(swgpu_db_t *db, int32_t n_queries, const int8_t *const *queries, const int64_t *query_lens,
+                      const int8_t *table, int gap_open, int gap_extend, int32_t *const *scores,
+                      int32_t k, swgpu_hit_t *hits, int32_t *n_hits,
+                      swgpu_stats_t *per_query, swgpu_batch_stats_t *batch);
+
 /* Statistics of the last search on this handle, with ms_topk / topk_launches of the last swgpu_topk(). */
 int swgpu_db_last_stats(const swgpu_db_t *db, swgpu_stats_t *out);
 

@@ -30,6 +30,42 @@ int dalloc(swgpu_db* db, T** p, size_t count) {
 
 }  // namespace
 
+namespace swi {
+
+int slot_prepare(swgpu_db* db, swgpu_slot& S) {
+  if (S.ready) return SWGPU_OK;
+  int lo = 0, hi = 0, r;
+  CU(cudaDeviceGetStreamPriorityRange(&lo, &hi));            // lo = least urgent, hi = most urgent (numerically smaller)
+  CU(cudaStreamCreateWithPriority(&S.s_main, cudaStreamNonBlocking, lo));
+  CU(cudaStreamCreateWithPriority(&S.s_aux, cudaStreamNonBlocking, hi));
+  for (auto& e : S.ev) CU(cudaEventCreate(&e));
+  if ((r = dalloc(db, &S.d_scores, (size_t)db->n))) return r;
+  if ((r = dalloc(db, &S.d_raw_s, (size_t)db->n_pairs * 32))) return r;
+  if ((r = dalloc(db, &S.d_rescore_list, (size_t)db->n))) return r;
+  if ((r = dalloc(db, &S.d_counters, 16))) return r;
+  if ((r = dalloc(db, &S.d_table, 1024))) return r;
+  if ((r = dalloc(db, &S.d_bnd_s, (size_t)db->k1s_grid * swk::K1S_WARPS * (size_t)db->bnd_s_stride))) return r;
+  if ((r = dalloc(db, &S.d_bnd3, (size_t)db->k3_grid * swk::K3_WARPS * (size_t)db->bnd3_stride))) return r;
+  CU(cudaMallocHost((void**)&S.h_ctr, 16 * sizeof(unsigned)));
+  S.ready = true;
+  return SWGPU_OK;
+}
+
+void slot_release(swgpu_slot& S) {
+  cudaFree(S.d_scores); cudaFree(S.d_raw_s); cudaFree(S.d_rescore_list); cudaFree(S.d_counters);
+  cudaFree(S.d_bnd_s); cudaFree(S.d_bnd3); cudaFree(S.d_query); cudaFree(S.d_table);
+  cudaFree(S.d_sprof); cudaFree(S.d_sprof2);
+  cudaFree(S.d_keys); cudaFree(S.d_hit_sidx); cudaFree(S.d_sel); cudaFree(S.d_coords); cudaFree(S.d_bnd_loc);
+  cudaFreeHost(S.h_ctr); cudaFreeHost(S.h_keys); cudaFreeHost(S.h_coords); cudaFreeHost(S.h_best); cudaFreeHost(S.h_sidx);
+  cudaFreeHost(S.h_scores);
+  for (auto& e : S.ev) if (e) cudaEventDestroy(e);
+  if (S.s_main) cudaStreamDestroy(S.s_main);
+  if (S.s_aux) cudaStreamDestroy(S.s_aux);
+  S = swgpu_slot();
+}
+
+}  // namespace swi
+
 extern "C" {
 
 int swgpu_device_count(void) {
@@ -44,15 +80,11 @@ const char* swgpu_version(void) { return "swgpu 0.2 (sm_100a)"; }
 void swgpu_db_destroy(swgpu_db_t* db) {
   if (!db) return;
   cudaSetDevice(db->device);
+  cudaDeviceSynchronize();
   cudaFree(db->d_plain); cudaFree(db->d_plain_off); cudaFree(db->d_order);
   cudaFree(db->d_scols); cudaFree(db->d_stream_off); cudaFree(db->d_stream_ncols); cudaFree(db->d_stream_pair0);
-  cudaFree(db->d_scores); cudaFree(db->d_raw_s); cudaFree(db->d_rescore_list); cudaFree(db->d_counters);
-  cudaFree(db->d_bnd_s); cudaFree(db->d_bnd3); cudaFree(db->d_query); cudaFree(db->d_table);
-  cudaFree(db->d_sprof); cudaFree(db->d_sprof2);
-  cudaFree(db->d_keys); cudaFree(db->d_hit_sidx); cudaFree(db->d_sel); cudaFree(db->d_coords); cudaFree(db->d_bnd_loc);
-  for (auto& e : db->ev) if (e) cudaEventDestroy(e);
-  if (db->s_main) cudaStreamDestroy(db->s_main);
-  if (db->s_aux) cudaStreamDestroy(db->s_aux);
+  for (auto& S : db->slots) swi::slot_release(S);
+  for (auto& e : db->ev_batch) if (e) cudaEventDestroy(e);
   delete db;
 }
 
@@ -85,9 +117,7 @@ int swgpu_db_create(swgpu_db_t** out, int device, const int8_t* codes, const int
     cudaDeviceProp prop;
     CU(cudaGetDeviceProperties(&prop, device));
     db->sm_count = prop.multiProcessorCount;
-    CU(cudaStreamCreateWithFlags(&db->s_main, cudaStreamNonBlocking));
-    CU(cudaStreamCreateWithFlags(&db->s_aux, cudaStreamNonBlocking));
-    for (auto& e : db->ev) CU(cudaEventCreate(&e));
+    for (auto& e : db->ev_batch) CU(cudaEventCreate(&e));
     int r;
     if ((r = dalloc(db, &db->d_plain, (size_t)pk.n_residues))) return r;
     if ((r = dalloc(db, &db->d_plain_off, (size_t)pk.n_targets + 1))) return r;
@@ -96,11 +126,6 @@ int swgpu_db_create(swgpu_db_t** out, int device, const int8_t* codes, const int
     if ((r = dalloc(db, &db->d_stream_off, (size_t)pk.n_streams + 1))) return r;
     if ((r = dalloc(db, &db->d_stream_ncols, (size_t)pk.n_streams))) return r;
     if ((r = dalloc(db, &db->d_stream_pair0, (size_t)pk.n_streams))) return r;
-    if ((r = dalloc(db, &db->d_scores, (size_t)pk.n_targets))) return r;
-    if ((r = dalloc(db, &db->d_raw_s, (size_t)pk.n_pairs * 32))) return r;
-    if ((r = dalloc(db, &db->d_rescore_list, (size_t)pk.n_targets))) return r;
-    if ((r = dalloc(db, &db->d_counters, 8))) return r;
-    if ((r = dalloc(db, &db->d_table, 1024))) return r;
     CU(cudaMemcpy(db->d_plain, pk.plain, (size_t)pk.n_residues, cudaMemcpyHostToDevice));
     CU(cudaMemcpy(db->d_plain_off, pk.plain_off, sizeof(int64_t) * ((size_t)pk.n_targets + 1), cudaMemcpyHostToDevice));
     CU(cudaMemcpy(db->d_order, pk.order, sizeof(int64_t) * (size_t)pk.n_targets, cudaMemcpyHostToDevice));
@@ -111,11 +136,9 @@ int swgpu_db_create(swgpu_db_t** out, int device, const int8_t* codes, const int
     // persistent grids: k1s two CTAs of 8 warps per SM; k3 at most four CTAs of 4 warps per SM
     db->k1s_grid = db->sm_count * 3;                          // upper bound of resident k1s CTAs (carry-row slots)
     db->bnd_s_stride = ((long long)std::max<int32_t>(pk.max_stream_cols, 64) + 63) & ~63ll;
-    if ((r = dalloc(db, &db->d_bnd_s, (size_t)db->k1s_grid * swk::K1S_WARPS * (size_t)db->bnd_s_stride))) return r;
     db->k3_grid = db->sm_count * 4;
     db->bnd3_stride = std::max<int32_t>(pk.max_len, 32);
-    if ((r = dalloc(db, &db->d_bnd3, (size_t)db->k3_grid * swk::K3_WARPS * (size_t)db->bnd3_stride))) return r;
-    return SWGPU_OK;
+    return swi::slot_prepare(db, db->slots[0]);
   };
   const int rc = body();
   swpack_free(&pk);
@@ -195,36 +218,31 @@ int launch_k1s(swgpu_db* db, const swk::K1SParams& P, int R, bool multi, cudaStr
 
 // 32-bit scoring of a work list (device-side count) or of all targets (list == nullptr): k3_intra (one warp per
 // target) takes the targets shorter than kWaveMinLen, the wavefront kernel k3w (one CTA per target) the rest.
-int launch_32bit(swgpu_db* db, const int* list, const unsigned* list_count, int n_all, int lq, int oe, int ge,
-                 unsigned* q_k3, unsigned* q_k3w, int* launches) {
+int launch_32bit(swgpu_db* db, swgpu_slot& S, cudaStream_t stream, const int* list, const unsigned* list_count,
+                 int n_all, int lq, int oe, int ge, unsigned* q_k3, unsigned* q_k3w, int* launches) {
   swk::K3Params P; memset(&P, 0, sizeof(P));
   P.worklist = list; P.work_count = list_count; P.n_work = n_all; P.counter = q_k3;
-  P.plain = db->d_plain; P.plain_off = db->d_plain_off; P.query = db->d_query; P.lq = lq; P.table = db->d_table;
-  P.oe = oe; P.ge = ge; P.bnd = db->d_bnd3; P.bnd_stride = db->bnd3_stride; P.order = db->d_order;
-  P.scores_file = db->d_scores; P.one = 1u; P.max_len = kWaveMinLen - 1;
-  if (lq <= 128) swk::k3_intra<4><<<db->k3_grid, swk::K3_WARPS * 32, 0, db->s_main>>>(P);
-  else           swk::k3_intra<8><<<db->k3_grid, swk::K3_WARPS * 32, 0, db->s_main>>>(P);
+  P.plain = db->d_plain; P.plain_off = db->d_plain_off; P.query = S.d_query; P.lq = lq; P.table = S.d_table;
+  P.oe = oe; P.ge = ge; P.bnd = S.d_bnd3; P.bnd_stride = db->bnd3_stride; P.order = db->d_order;
+  P.scores_file = S.d_scores; P.one = 1u; P.max_len = kWaveMinLen - 1;
+  if (lq <= 128) swk::k3_intra<4><<<db->k3_grid, swk::K3_WARPS * 32, 0, stream>>>(P);
+  else           swk::k3_intra<8><<<db->k3_grid, swk::K3_WARPS * 32, 0, stream>>>(P);
   CU(cudaGetLastError());
   ++*launches;
   if (db->max_len >= kWaveMinLen) {
     swk::K3WParams W; memset(&W, 0, sizeof(W));
     W.sidx_list = list; W.work_count = list_count; W.n_work = n_all; W.counter = q_k3w;
-    W.plain = db->d_plain; W.plain_off = db->d_plain_off; W.query = db->d_query; W.lq = lq; W.table = db->d_table;
-    W.oe = oe; W.ge = ge; W.bnd = db->d_bnd3; W.bnd_stride = db->bnd3_stride;
-    W.order = db->d_order; W.scores_file = db->d_scores; W.error_flag = db->d_counters + 6; W.min_len = kWaveMinLen;
-    swk::k3w<false><<<db->sm_count * 2, swk::K3W_WARPS * 32, 0, db->s_main>>>(W);   // after k3 on the same stream: d_bnd3 is shared
+    W.plain = db->d_plain; W.plain_off = db->d_plain_off; W.query = S.d_query; W.lq = lq; W.table = S.d_table;
+    W.oe = oe; W.ge = ge; W.bnd = S.d_bnd3; W.bnd_stride = db->bnd3_stride;
+    W.order = db->d_order; W.scores_file = S.d_scores; W.error_flag = S.d_counters + 6; W.min_len = kWaveMinLen;
+    swk::k3w<false><<<db->sm_count * 2, swk::K3W_WARPS * 32, 0, stream>>>(W);   // after k3 on the same stream: d_bnd3 is shared
     CU(cudaGetLastError());
     ++*launches;
   }
   return SWGPU_OK;
 }
 
-}  // namespace
-
-namespace {
-
-int run_search(swgpu_db* db, const int8_t* query, int64_t lq, const int8_t* table, int gap_open, int gap_extend,
-               swgpu_stats_t* stats) {
+int check_args(swgpu_db* db, const int8_t* query, int64_t lq, const int8_t* table, int gap_open, int gap_extend) {
   if (!db) return fail(SWGPU_EINVAL, "null database handle");
   if (lq < 0 || (lq > 0 && !query) || !table) return fail(SWGPU_EINVAL, "bad query/table argument");
   if (lq > 0x7fffffff) return fail(SWGPU_EINVAL, "query too long");
@@ -233,21 +251,30 @@ int run_search(swgpu_db* db, const int8_t* query, int64_t lq, const int8_t* tabl
     return fail(SWGPU_EINVAL, "positive gap scores are outside the supported (and the reference-equivalent) range");
   if (oe < -100000 || ge < -100000) return fail(SWGPU_EINVAL, "gap penalty out of range");
   for (int64_t i = 0; i < lq; ++i) if (query[i] < 0 || query[i] > 31) return fail(SWGPU_EINVAL, "query code outside 0..31");
-  CU(cudaSetDevice(db->device));
-  swgpu_stats_t st; memset(&st, 0, sizeof(st));
-  db->have_scores = false;
-  cudaEvent_t* e = db->ev;
-  cudaStream_t sm = db->s_main, sa = db->s_aux;
+  return SWGPU_OK;
+}
+
+// Queue one search on a slot.  Nothing here waits for the GPU: the bulk kernel goes to the slot's low-priority
+// stream, the long-stream launch and everything after the 16-bit pass (rescoring, later top-k and read-back) to its
+// high-priority stream.  The slot must be idle (collect_search() done for its previous search).
+int enqueue_search(swgpu_db* db, swgpu_slot& S, const int8_t* query, int64_t lq, const int8_t* table, int gap_open,
+                   int gap_extend) {
+  if (S.in_flight) return fail(SWGPU_EINVAL, "internal: slot busy");
+  const int oe = gap_open + gap_extend, ge = gap_extend;
+  swgpu_stats_t& st = S.st; memset(&st, 0, sizeof(st));
+  S.have_scores = false; S.topk_k = 0; S.user_scores = nullptr; S.scores_staged = false;
+  cudaEvent_t* e = S.ev;
+  cudaStream_t sm = S.s_main, sa = S.s_aux;
 
   // ---- uploads (query, table) ----
-  if (lq > db->query_cap) {
-    if (db->d_query) { cudaFree(db->d_query); db->d_query = nullptr; }
-    db->query_cap = std::max<int64_t>(lq, 1024);
-    CU(cudaMalloc((void**)&db->d_query, (size_t)db->query_cap));
+  if (lq > S.query_cap) {
+    if (S.d_query) { cudaFree(S.d_query); S.d_query = nullptr; }
+    S.query_cap = std::max<int64_t>(lq, 1024);
+    CU(cudaMalloc((void**)&S.d_query, (size_t)S.query_cap));
   }
   CU(cudaEventRecord(e[6], sm));
-  if (lq > 0) CU(cudaMemcpyAsync(db->d_query, query, (size_t)lq, cudaMemcpyHostToDevice, sm));
-  CU(cudaMemcpyAsync(db->d_table, table, 1024, cudaMemcpyHostToDevice, sm));
+  if (lq > 0) CU(cudaMemcpyAsync(S.d_query, query, (size_t)lq, cudaMemcpyHostToDevice, sm));
+  CU(cudaMemcpyAsync(S.d_table, table, 1024, cudaMemcpyHostToDevice, sm));
   CU(cudaEventRecord(e[7], sm));
 
   // ---- plan ----
@@ -257,7 +284,7 @@ int run_search(swgpu_db* db, const int8_t* query, int64_t lq, const int8_t* tabl
   const K1SPlan plan = plan_k1s(std::max<int64_t>(lq, 1), db->n_streams, db->k1s_grid * swk::K1S_WARPS);
   // Long streams (one target pair of thousands of columns) are latency-bound on their serial column chain: when the
   // bulk plan uses fewer than 32 lanes per pair they get their own launch with all 32 lanes and the fewest rows per
-  // lane, one stream per CTA, started first on the second CUDA stream.
+  // lane, one stream per CTA, on the high-priority CUDA stream.
   const bool split_long = use16 && plan.npass == 1 && plan.g < 32 && db->n_long_streams > 0;
   K1SPlan plan_long = plan;
   if (split_long) {
@@ -267,101 +294,146 @@ int run_search(swgpu_db* db, const int8_t* query, int64_t lq, const int8_t* tabl
   auto words_of = [](const K1SPlan& p) { return (size_t)p.npass * 32 * ((p.R + 3) / 4 + p.R / 2) * 32; };
   if (use16) {
     st.tile_rows = plan.R; st.lanes_per_pair = plan.g; st.passes = plan.npass;
-    if (words_of(plan) > db->sprof_cap) {
-      if (db->d_sprof) { cudaFree(db->d_sprof); db->d_sprof = nullptr; }
-      db->sprof_cap = words_of(plan) * 3 / 2;
-      CU(cudaMalloc((void**)&db->d_sprof, db->sprof_cap * sizeof(unsigned)));
+    if (words_of(plan) > S.sprof_cap) {
+      if (S.d_sprof) { cudaFree(S.d_sprof); S.d_sprof = nullptr; }
+      S.sprof_cap = words_of(plan) * 3 / 2;
+      CU(cudaMalloc((void**)&S.d_sprof, S.sprof_cap * sizeof(unsigned)));
     }
-    if (split_long && words_of(plan_long) > db->sprof2_cap) {
-      if (db->d_sprof2) { cudaFree(db->d_sprof2); db->d_sprof2 = nullptr; }
-      db->sprof2_cap = words_of(plan_long) * 2;
-      CU(cudaMalloc((void**)&db->d_sprof2, db->sprof2_cap * sizeof(unsigned)));
+    if (split_long && words_of(plan_long) > S.sprof2_cap) {
+      if (S.d_sprof2) { cudaFree(S.d_sprof2); S.d_sprof2 = nullptr; }
+      S.sprof2_cap = words_of(plan_long) * 2;
+      CU(cudaMalloc((void**)&S.d_sprof2, S.sprof2_cap * sizeof(unsigned)));
     }
   }
+  S.use16 = use16; S.split_long = split_long; S.lq = lq; S.oe = oe; S.ge = ge;
 
   // ---- timed region: first kernel -> last result resident in HBM ----
   CU(cudaEventRecord(e[0], sm));
-  CU(cudaMemsetAsync(db->d_counters, 0, 8 * sizeof(unsigned), sm));
+  CU(cudaMemsetAsync(S.d_counters, 0, 16 * sizeof(unsigned), sm));
+  int r;
   if (lq == 0 || db->n == 0) {
-    if (db->n) CU(cudaMemsetAsync(db->d_scores, 0, sizeof(int32_t) * (size_t)db->n, sm));
-    CU(cudaEventRecord(e[1], sm));
+    if (db->n) CU(cudaMemsetAsync(S.d_scores, 0, sizeof(int32_t) * (size_t)db->n, sm));
+    CU(cudaEventRecord(e[5], sm));
+    CU(cudaStreamWaitEvent(sa, e[5], 0));
+    CU(cudaEventRecord(e[1], sa));
   } else if (use16) {
     swk::K1SParams PS; memset(&PS, 0, sizeof(PS));
     PS.scols = db->d_scols; PS.stream_off = db->d_stream_off; PS.stream_ncols = db->d_stream_ncols;
-    PS.stream_pair0 = db->d_stream_pair0; PS.bnd = db->d_bnd_s; PS.bnd_stride = db->bnd_s_stride;
+    PS.stream_pair0 = db->d_stream_pair0; PS.bnd = S.d_bnd_s; PS.bnd_stride = db->bnd_s_stride;
     PS.BB = B * 0x10001u; PS.BBM = (B + (unsigned)(-oe)) * 0x10001u;
     PS.OE2 = ((unsigned)oe & 0xffffu) * 0x10001u; PS.GE2 = ((unsigned)ge & 0xffffu) * 0x10001u;
     const unsigned limit = 65535u - 129u;
     const int64_t nls = split_long ? db->n_long_streams : 0, nlp = split_long ? db->n_long_pairs : 0;
-    int r;
+    CU(cudaEventRecord(e[3], sm));
+    CU(cudaStreamWaitEvent(sa, e[3], 0));
     if (split_long) {
-      CU(cudaEventRecord(e[3], sm));
-      CU(cudaStreamWaitEvent(sa, e[3], 0));
-      swk::build_sprofile<<<32, 256, 0, sa>>>(db->d_query, (int)lq, db->d_table, plan_long.R, 32, 1, db->d_sprof2);
+      swk::build_sprofile<<<32, 256, 0, sa>>>(S.d_query, (int)lq, S.d_table, plan_long.R, 32, 1, S.d_sprof2);
       swk::K1SParams PL = PS;
-      PL.stream_begin = 0; PL.n_streams = (int)nls; PL.n_items = (int)nls; PL.prof = db->d_sprof2; PL.npass = 1;
-      PL.g = 32; PL.g_log2 = 5; PL.counter = db->d_counters + 1; PL.raw = db->d_raw_s;
+      PL.stream_begin = 0; PL.n_streams = (int)nls; PL.n_items = (int)nls; PL.prof = S.d_sprof2; PL.npass = 1;
+      PL.g = 32; PL.g_log2 = 5; PL.counter = S.d_counters + 1; PL.raw = S.d_raw_s;
       PL.active_warps = 1;                                     // one long stream per CTA: spread them over the SMs
       if ((r = launch_k1s(db, PL, plan_long.R, false, sa, (int)std::min<int64_t>(nls, db->k1s_grid)))) return r;
       swk::k1s_finalize<<<std::max(1, (int)((nlp + 255) / 256)), 256, 0, sa>>>(
-          db->d_raw_s, 0, (long)nlp, 5, (long)db->n, B, limit, db->d_order, db->d_plain_off, db->long_threshold,
-          db->d_scores, db->d_rescore_list, db->d_counters + 2);
+          S.d_raw_s, 0, (long)nlp, 5, (long)db->n, B, limit, db->d_order, db->d_plain_off, db->long_threshold,
+          S.d_scores, S.d_rescore_list, S.d_counters + 2);
       CU(cudaGetLastError()); st.kernel_launches += 3;
-      CU(cudaEventRecord(e[4], sa));
     }
+    CU(cudaEventRecord(e[4], sa));
     swk::build_sprofile<<<std::min(2048, (int)(words_of(plan) / 256) + 1), 256, 0, sm>>>(
-        db->d_query, (int)lq, db->d_table, plan.R, plan.g, plan.npass, db->d_sprof);
+        S.d_query, (int)lq, S.d_table, plan.R, plan.g, plan.npass, S.d_sprof);
     CU(cudaGetLastError()); st.kernel_launches++;
     const int per_warp = 32 / plan.g;
     PS.stream_begin = (int)nls; PS.n_streams = (int)(db->n_streams - nls);
     PS.n_items = (PS.n_streams + per_warp - 1) / per_warp;
-    PS.prof = db->d_sprof; PS.npass = plan.npass; PS.g = plan.g; PS.g_log2 = plan.g_log2;
-    PS.counter = db->d_counters + 0; PS.active_warps = swk::K1S_WARPS;
+    PS.prof = S.d_sprof; PS.npass = plan.npass; PS.g = plan.g; PS.g_log2 = plan.g_log2;
+    PS.counter = S.d_counters + 0; PS.active_warps = swk::K1S_WARPS;
     // the bulk's [pair][g] maxima start after the long launch's [pair][32] region
-    PS.raw = db->d_raw_s + (size_t)nlp * 32 - ((size_t)nlp << plan.g_log2);
+    PS.raw = S.d_raw_s + (size_t)nlp * 32 - ((size_t)nlp << plan.g_log2);
     if (PS.n_streams > 0) {
       int ctas = plan.R <= K1S_R3CTA ? 3 : 2;
       if (const char* ev = getenv("SWGPU_K1S_CTAS")) ctas = std::max(1, std::min(ctas, atoi(ev)));   // A/B knob (profiling)
       if ((r = launch_k1s(db, PS, plan.R, plan.npass > 1, sm, db->sm_count * ctas))) return r;
       swk::k1s_finalize<<<(int)std::min<int64_t>((db->n_pairs - nlp + 255) / 256, 4096), 256, 0, sm>>>(
           PS.raw, (long)nlp, (long)db->n_pairs, plan.g_log2, (long)db->n, B, limit, db->d_order, db->d_plain_off,
-          db->long_threshold, db->d_scores, db->d_rescore_list, db->d_counters + 2);
+          db->long_threshold, S.d_scores, S.d_rescore_list, S.d_counters + 2);
       CU(cudaGetLastError()); st.kernel_launches += 2;
     }
-    if (split_long) CU(cudaStreamWaitEvent(sm, e[4], 0));
-    CU(cudaEventRecord(e[1], sm));
+    CU(cudaEventRecord(e[5], sm));
+    CU(cudaStreamWaitEvent(sa, e[5], 0));
+    CU(cudaEventRecord(e[1], sa));
     // 32-bit rescoring of the saturated (or forced) targets; the count lives on the device
-    if ((r = launch_32bit(db, db->d_rescore_list, db->d_counters + 2, 0, (int)lq, oe, ge, db->d_counters + 3,
-                          db->d_counters + 4, &st.kernel_launches))) return r;
+    if ((r = launch_32bit(db, S, sa, S.d_rescore_list, S.d_counters + 2, 0, (int)lq, oe, ge, S.d_counters + 3,
+                          S.d_counters + 4, &st.kernel_launches))) return r;
   } else {
-    CU(cudaEventRecord(e[1], sm));
-    int r;
-    if ((r = launch_32bit(db, nullptr, nullptr, (int)db->n, (int)lq, oe, ge, db->d_counters + 5, db->d_counters + 4,
+    CU(cudaEventRecord(e[5], sm));
+    CU(cudaStreamWaitEvent(sa, e[5], 0));
+    CU(cudaEventRecord(e[1], sa));
+    if ((r = launch_32bit(db, S, sa, nullptr, nullptr, (int)db->n, (int)lq, oe, ge, S.d_counters + 5, S.d_counters + 4,
                           &st.kernel_launches))) return r;
   }
-  CU(cudaEventRecord(e[2], sm));
-  CU(cudaStreamSynchronize(sm));
-  CU(cudaStreamSynchronize(sa));
-  db->have_scores = true;
-  db->last_lq = lq; db->last_oe = oe; db->last_ge = ge;
+  CU(cudaEventRecord(e[2], sa));
+  S.in_flight = true;
+  return SWGPU_OK;
+}
 
+// Queue the read-back of a slot's results (counters always; all scores if the caller wants them) and the slot's
+// completion event.  `staged`: the caller's buffer may be pageable and the call must not block -> go through the
+// slot's pinned staging buffer, copied out in collect_search().
+int enqueue_readback(swgpu_db* db, swgpu_slot& S, int32_t* scores, bool staged) {
+  cudaStream_t sa = S.s_aux;
+  CU(cudaEventRecord(S.ev[10], sa));
+  CU(cudaMemcpyAsync(S.h_ctr, S.d_counters, 16 * sizeof(unsigned), cudaMemcpyDeviceToHost, sa));
+  if (scores && db->n) {
+    int32_t* dst = scores;
+    if (staged) {
+      cudaPointerAttributes at; memset(&at, 0, sizeof(at));
+      const bool pinned = cudaPointerGetAttributes(&at, scores) == cudaSuccess && at.type == cudaMemoryTypeHost;
+      cudaGetLastError();
+      if (!pinned) {
+        if (S.h_scores_cap < db->n) {
+          cudaFreeHost(S.h_scores); S.h_scores = nullptr;
+          CU(cudaMallocHost((void**)&S.h_scores, sizeof(int32_t) * (size_t)db->n));
+          S.h_scores_cap = db->n;
+        }
+        dst = S.h_scores; S.scores_staged = true;
+      }
+    }
+    S.user_scores = scores;
+    CU(cudaMemcpyAsync(dst, S.d_scores, sizeof(int32_t) * (size_t)db->n, cudaMemcpyDeviceToHost, sa));
+  }
+  CU(cudaEventRecord(S.ev[11], sa));
+  return SWGPU_OK;
+}
+
+// Wait for a slot's search (and top-k / read-back queued behind it) and fill in its statistics.
+int collect_search(swgpu_db* db, swgpu_slot& S, swgpu_stats_t* stats) {
+  if (!S.in_flight) return fail(SWGPU_EINVAL, "internal: slot idle");
+  cudaEvent_t* e = S.ev;
+  CU(cudaEventSynchronize(e[11]));
+  CU(cudaStreamSynchronize(S.s_main));
+  S.in_flight = false;
+  S.have_scores = true;
+  swgpu_stats_t& st = S.st;
+  const int64_t lq = S.lq;
   float ms = 0;
   CU(cudaEventElapsedTime(&ms, e[0], e[2])); st.ms_total = ms;
   CU(cudaEventElapsedTime(&ms, e[6], e[7])); st.ms_h2d = ms;
+  if (S.user_scores) { CU(cudaEventElapsedTime(&ms, e[10], e[11])); st.ms_d2h = ms; }
+  if (S.topk_k > 0) { CU(cudaEventElapsedTime(&ms, e[8], e[9])); st.ms_topk = ms; st.topk_launches = S.topk_launches; }
   st.cells = lq * db->n_residues;
+  if (S.scores_staged) memcpy(S.user_scores, S.h_scores, sizeof(int32_t) * (size_t)db->n);
   if (lq > 0 && db->n > 0) {
-    unsigned ctr[8] = {};
-    CU(cudaMemcpy(ctr, db->d_counters, sizeof(ctr), cudaMemcpyDeviceToHost));
+    const unsigned* ctr = S.h_ctr;
     if (ctr[6]) return fail(SWGPU_ECUDA, "32-bit wavefront kernel stalled (internal error)");
-    if (use16) {
+    if (S.use16) {
       CU(cudaEventElapsedTime(&ms, e[0], e[1])); st.ms_inter = ms;
       CU(cudaEventElapsedTime(&ms, e[1], e[2])); st.ms_rescore = ms;
-      if (split_long) { CU(cudaEventElapsedTime(&ms, e[3], e[4])); st.ms_intra = ms; st.n_long = 2 * db->n_long_pairs; }
+      if (S.split_long) { CU(cudaEventElapsedTime(&ms, e[3], e[4])); st.ms_intra = ms; st.n_long = 2 * db->n_long_pairs; }
       st.cells_inter = st.cells;
       st.n_rescored = ctr[2];
       if (ctr[2]) {
         std::vector<int> lst(ctr[2]);
-        CU(cudaMemcpy(lst.data(), db->d_rescore_list, sizeof(int) * ctr[2], cudaMemcpyDeviceToHost));
+        CU(cudaMemcpy(lst.data(), S.d_rescore_list, sizeof(int) * ctr[2], cudaMemcpyDeviceToHost));
         int64_t res = 0;
         for (int s : lst) res += db->h_len_sorted_prefix[s + 1] - db->h_len_sorted_prefix[s];
         st.cells_rescore = lq * res;
@@ -375,36 +447,89 @@ int run_search(swgpu_db* db, const int8_t* query, int64_t lq, const int8_t* tabl
   return SWGPU_OK;
 }
 
+int run_single(swgpu_db* db, const int8_t* query, int64_t lq, const int8_t* table, int gap_open, int gap_extend,
+               int32_t* scores, swgpu_stats_t* stats) {
+  int r = check_args(db, query, lq, table, gap_open, gap_extend);
+  if (r) return r;
+  CU(cudaSetDevice(db->device));
+  swgpu_slot& S = db->slots[0];
+  if ((r = enqueue_search(db, S, query, lq, table, gap_open, gap_extend))) { S.in_flight = false; return r; }
+  if ((r = enqueue_readback(db, S, scores, false))) { cudaDeviceSynchronize(); S.in_flight = false; return r; }
+  return collect_search(db, S, stats);
+}
+
 }  // namespace
 
 extern "C" {
 
 int swgpu_search_resident(swgpu_db_t* db, const int8_t* query, int64_t query_len, const int8_t* table,
                           int gap_open, int gap_extend, swgpu_stats_t* stats) {
-  return run_search(db, query, query_len, table, gap_open, gap_extend, stats);
+  return run_single(db, query, query_len, table, gap_open, gap_extend, nullptr, stats);
 }
 
 int swgpu_db_scores_d2h(swgpu_db_t* db, int32_t* scores) {
   if (!db || !scores) return fail(SWGPU_EINVAL, "bad argument");
-  if (!db->have_scores) return fail(SWGPU_EINVAL, "no search result resident");
+  swgpu_slot& S = db->slots[0];
+  if (!S.have_scores) return fail(SWGPU_EINVAL, "no search result resident");
   CU(cudaSetDevice(db->device));
-  if (db->n) CU(cudaMemcpy(scores, db->d_scores, sizeof(int32_t) * (size_t)db->n, cudaMemcpyDeviceToHost));
+  if (db->n) CU(cudaMemcpy(scores, S.d_scores, sizeof(int32_t) * (size_t)db->n, cudaMemcpyDeviceToHost));
   return SWGPU_OK;
 }
 
 int swgpu_search(swgpu_db_t* db, const int8_t* query, int64_t query_len, const int8_t* table,
                  int gap_open, int gap_extend, int32_t* scores, swgpu_stats_t* stats) {
   if (!scores && db && db->n) return fail(SWGPU_EINVAL, "null scores buffer");
-  swgpu_stats_t st;
-  int r = run_search(db, query, query_len, table, gap_open, gap_extend, &st);
-  if (r) return r;
-  CU(cudaEventRecord(db->ev[6], db->s_main));
-  if (db->n) CU(cudaMemcpyAsync(scores, db->d_scores, sizeof(int32_t) * (size_t)db->n, cudaMemcpyDeviceToHost, db->s_main));
-  CU(cudaEventRecord(db->ev[7], db->s_main));
-  CU(cudaStreamSynchronize(db->s_main));
-  float ms = 0; CU(cudaEventElapsedTime(&ms, db->ev[6], db->ev[7])); st.ms_d2h = ms;
-  db->last_stats = st;
-  if (stats) *stats = st;
+  return run_single(db, query, query_len, table, gap_open, gap_extend, scores, stats);
+}
+
+int swgpu_search_many(swgpu_db_t* db, int32_t n_queries, const int8_t* const* queries, const int64_t* query_lens,
+                      const int8_t* table, int gap_open, int gap_extend, int32_t* const* scores, int32_t k,
+                      swgpu_hit_t* hits, int32_t* n_hits, swgpu_stats_t* per_query, swgpu_batch_stats_t* batch) {
+  if (!db || n_queries < 0 || (n_queries > 0 && (!queries || !query_lens))) return fail(SWGPU_EINVAL, "swgpu_search_many: bad argument");
+  if (k < 0 || (k > 0 && (!hits || !n_hits))) return fail(SWGPU_EINVAL, "swgpu_search_many: bad top-k argument");
+  int r;
+  for (int q = 0; q < n_queries; ++q)
+    if ((r = check_args(db, queries[q], query_lens[q], table, gap_open, gap_extend))) return r;
+  CU(cudaSetDevice(db->device));
+  const int kk = (int)std::min<int64_t>(k, db->n);
+  const int n_slots = std::min<int>(SWGPU_SLOTS, std::max(1, n_queries));
+  for (int s = 0; s < n_slots; ++s) if ((r = swi::slot_prepare(db, db->slots[s]))) return r;
+  swgpu_batch_stats_t bs; memset(&bs, 0, sizeof(bs));
+  bs.slots = n_slots;
+  CU(cudaEventRecord(db->ev_batch[0], db->slots[0].s_main));
+  int rc = SWGPU_OK;
+  auto collect = [&](int q) -> int {
+    swgpu_slot& S = db->slots[q % n_slots];
+    swgpu_stats_t st;
+    int r2 = collect_search(db, S, &st);
+    if (r2) return r2;
+    if (kk > 0 && (r2 = swi::collect_topk(db, S, hits + (size_t)q * k, n_hits + q))) return r2;
+    else if (k > 0 && kk == 0) n_hits[q] = 0;
+    if (per_query) per_query[q] = st;
+    bs.cells += st.cells; bs.n_rescored += st.n_rescored; bs.kernel_launches += st.kernel_launches + st.topk_launches;
+    float ms = 0;
+    if (cudaEventElapsedTime(&ms, db->ev_batch[0], S.ev[11]) == cudaSuccess) bs.ms_total = std::max<double>(bs.ms_total, ms);
+    return SWGPU_OK;
+  };
+  int next_collect = 0;
+  for (int q = 0; q < n_queries && rc == SWGPU_OK; ++q) {
+    if (q >= n_slots) { rc = collect(next_collect++); if (rc) break; }
+    swgpu_slot& S = db->slots[q % n_slots];
+    if ((rc = enqueue_search(db, S, queries[q], query_lens[q], table, gap_open, gap_extend))) { S.in_flight = false; break; }
+    if (kk > 0 && (rc = swi::enqueue_topk(db, S, kk))) break;
+    if ((rc = enqueue_readback(db, S, scores ? scores[q] : nullptr, true))) break;
+  }
+  if (rc != SWGPU_OK) {                                     // drain whatever is queued, then report the first error
+    cudaDeviceSynchronize();
+    for (auto& S : db->slots) S.in_flight = false;
+    return rc;
+  }
+  for (; next_collect < n_queries; ++next_collect) if ((rc = collect(next_collect))) {
+    cudaDeviceSynchronize();
+    for (auto& S : db->slots) S.in_flight = false;
+    return rc;
+  }
+  if (batch) *batch = bs;
   return SWGPU_OK;
 }
 

@@ -22,6 +22,45 @@ inline int fail(int code, const char* fmt, ...) {
   return swi::fail(e_ == cudaErrorNoDevice || e_ == cudaErrorInsufficientDriver ? SWGPU_ENODEV : SWGPU_ECUDA, \
               "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); } while (0)
 
+constexpr int SWGPU_SLOTS = 3;        // query slots: up to 3 searches of one batch are in flight (swgpu_search_many)
+
+// Everything one search writes: scratch in HBM, streams, events, pinned read-back staging.  Slot 0 serves the
+// single-query entry points; swgpu_search_many() rotates queries over all slots so that the tail of one query
+// (long streams, finalize, rescoring, top-k) overlaps the bulk kernel of the next.
+struct swgpu_slot {
+  bool ready = false;                  // buffers allocated
+  int32_t*  d_scores = nullptr;        // file order
+  unsigned* d_raw_s = nullptr;         // n_pairs * 32 packed running maxima
+  int*      d_rescore_list = nullptr;  // up to n
+  unsigned* d_counters = nullptr;      // [0] k1s queue, [1] k1s long queue, [2] rescore count, [3] k3 queue, [4] k3w queue,
+                                       // [5] k3 all-targets queue, [6] k3w error flag, [7] top-k error flag,
+                                       // [8] top-k coordinate queue phase 0, [9] phase 1
+  uint2*    d_bnd_s = nullptr;         // k1s multi-stripe carry rows
+  int2*     d_bnd3 = nullptr;          // k3 / k3w carry rows
+  int8_t*   d_query = nullptr;  int64_t query_cap = 0;
+  int8_t*   d_table = nullptr;
+  unsigned* d_sprof = nullptr;  size_t sprof_cap = 0;     // k1s profile (bulk plan)
+  unsigned* d_sprof2 = nullptr; size_t sprof2_cap = 0;    // k1s profile (long-stream plan)
+  cudaStream_t s_main = nullptr;       // bulk K1S (low priority)
+  cudaStream_t s_aux = nullptr;        // long-stream K1S, then rescoring / top-k / read-back (high priority)
+  cudaEvent_t ev[12] = {};             // 0 start, 1 16-bit done, 2 scores final, 3 fork, 4 long done, 5 bulk done,
+                                       // 6/7 h2d, 8/9 top-k, 10 d2h start, 11 everything done (slot reusable)
+  // top-k scratch
+  unsigned long long* d_keys = nullptr;  int* d_hit_sidx = nullptr;  void* d_sel = nullptr;  int topk_cap = 0;
+  int4* d_coords = nullptr;
+  int2* d_bnd_loc = nullptr;  long long bnd_loc_stride = 0;  int loc_slots = 0;
+  // pinned host staging for asynchronous read-back
+  unsigned* h_ctr = nullptr;                                // 16 counters
+  unsigned long long* h_keys = nullptr;  int4* h_coords = nullptr;  int* h_best = nullptr;  int* h_sidx = nullptr;  int h_cap = 0;
+  int32_t* h_scores = nullptr;  int64_t h_scores_cap = 0;   // staging when the caller's score buffer is pageable
+  // host-side state of the search in flight / last finished
+  bool in_flight = false, have_scores = false, use16 = false, split_long = false;
+  int64_t lq = 0;  int oe = 0, ge = 0;
+  int topk_k = 0, topk_launches = 0;
+  int32_t* user_scores = nullptr;  bool scores_staged = false;
+  swgpu_stats_t st = {};
+};
+
 struct swgpu_db {
   int device = 0;
   int sm_count = 0;
@@ -39,28 +78,18 @@ struct swgpu_db {
   int64_t   n_pairs = 0, n_streams = 0;
   int32_t   max_stream_cols = 0;
   int64_t   n_long_streams = 0, n_long_pairs = 0;   // leading long streams get their own low-latency launch
-  // per-search scratch
-  int32_t*  d_scores = nullptr;        // file order
-  unsigned* d_raw_s = nullptr;         // n_pairs * 32 packed running maxima
-  int*      d_rescore_list = nullptr;  // up to n
-  unsigned* d_counters = nullptr;      // [0] k1s queue, [1] k1s long queue, [2] rescore count, [3] k3 queue, [4] k3w queue,
-                                       // [5] k3 all-targets queue, [6] k3w error flag, [7] top-k error flag
-  uint2*    d_bnd_s = nullptr;  long long bnd_s_stride = 0;  int k1s_grid = 0;   // k1s multi-stripe carry rows
-  int2*     d_bnd3 = nullptr;   long long bnd3_stride = 0;   int k3_grid = 0;    // k3 / k3w carry rows
-  int8_t*   d_query = nullptr;  int64_t query_cap = 0;
-  int8_t*   d_table = nullptr;
-  unsigned* d_sprof = nullptr;  size_t sprof_cap = 0;     // k1s profile (bulk plan)
-  unsigned* d_sprof2 = nullptr; size_t sprof2_cap = 0;    // k1s profile (long-stream plan)
+  long long bnd_s_stride = 0;  int k1s_grid = 0;    // k1s multi-stripe carry rows: per warp slot
+  long long bnd3_stride = 0;   int k3_grid = 0;     // k3 / k3w carry rows
   int64_t   device_bytes = 0;
-  std::vector<int64_t> h_len_sorted_prefix;               // plain_off on the host (statistics, top-k buffers)
-  cudaStream_t s_main = nullptr, s_aux = nullptr;
-  cudaEvent_t ev[8] = {};
-  int64_t last_lq = 0;
-  bool have_scores = false;
-  int last_oe = 0, last_ge = 0;        // gaps of the last search (top-k coordinates are recomputed against it)
-  // top-k scratch
-  unsigned long long* d_keys = nullptr;  int* d_hit_sidx = nullptr;  void* d_sel = nullptr;  int topk_cap = 0;
-  int4* d_coords = nullptr;
-  int2* d_bnd_loc = nullptr;  long long bnd_loc_stride = 0;  int loc_slots = 0;
+  std::vector<int64_t> h_len_sorted_prefix;         // plain_off on the host (statistics)
+  swgpu_slot slots[SWGPU_SLOTS];
+  cudaEvent_t ev_batch[1] = {};                     // start of the current swgpu_search_many() batch
   swgpu_stats_t last_stats = {};
 };
+
+namespace swi {
+int slot_prepare(swgpu_db* db, swgpu_slot& S);                        // allocate a slot's buffers on first use
+void slot_release(swgpu_slot& S);
+int enqueue_topk(swgpu_db* db, swgpu_slot& S, int k);                  // no host synchronisation
+int collect_topk(swgpu_db* db, swgpu_slot& S, swgpu_hit_t* hits, int* n_hits);   // after S.ev[11] has completed
+}  // namespace swi

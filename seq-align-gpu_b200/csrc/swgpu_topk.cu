@@ -11,8 +11,9 @@
 // Selection: an 8-pass MSB-first radix select (8 bits per pass) over 64-bit keys
 // (score << 32 | ~entry) finds the k-th largest key exactly; a compaction pass collects the k keys
 // >= it together with their position in the length-sorted database; a rank sort orders them.
-// Coordinates: one warp per hit runs the 32-bit systolic recurrence of K3 (sw_kernels.cuh) twice,
-// tracking the first maximum.
+// Coordinates: the wavefront kernel k3w<TRACK> (sw_k3w.cuh) runs the 32-bit recurrence twice per hit,
+// tracking the first maximum; hits are pulled from a device-side queue, so nothing returns to the host
+// between selection and coordinates (swgpu_search_many keeps several queries in flight).
 #include "swgpu_internal.h"
 #include "sw_kernels.cuh"
 #include "sw_k3w.cuh"
@@ -101,97 +102,131 @@ __global__ void topk_ranksort(const unsigned long long* __restrict__ keys, const
 
 using swi::fail;
 
+namespace swk {
+__global__ void topk_init(SelState* st, unsigned k) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) { st->prefix = 0ull; st->k_rem = k; st->n_out = 0u; }
+}
+}  // namespace swk
+
+namespace swi {
+
+// Queue selection + coordinate passes + read-back of the k hits on the slot's high-priority stream, behind the
+// search queued on it.  No host synchronisation (buffers grow on first use only); 1 <= k <= min(65536, n).
+int enqueue_topk(swgpu_db* db, swgpu_slot& S, int k) {
+  cudaStream_t st = S.s_aux;
+  if (k > S.topk_cap) {
+    cudaFree(S.d_keys); cudaFree(S.d_hit_sidx); cudaFree(S.d_coords);
+    S.d_keys = nullptr; S.d_hit_sidx = nullptr; S.d_coords = nullptr; S.topk_cap = 0;
+    const int cap = std::max(k, 128);
+    CU(cudaMalloc((void**)&S.d_keys, sizeof(unsigned long long) * 2 * (size_t)cap));
+    CU(cudaMalloc((void**)&S.d_hit_sidx, sizeof(int) * 3 * (size_t)cap));       // unsorted, sorted, best_out
+    CU(cudaMalloc((void**)&S.d_coords, sizeof(int4) * (size_t)cap));
+    S.topk_cap = cap;
+  }
+  if (k > S.h_cap) {
+    cudaFreeHost(S.h_keys); cudaFreeHost(S.h_coords); cudaFreeHost(S.h_best); cudaFreeHost(S.h_sidx);
+    S.h_keys = nullptr; S.h_coords = nullptr; S.h_best = nullptr; S.h_sidx = nullptr; S.h_cap = 0;
+    const int cap = std::max(k, 128);
+    CU(cudaMallocHost((void**)&S.h_keys, sizeof(unsigned long long) * (size_t)cap));
+    CU(cudaMallocHost((void**)&S.h_coords, sizeof(int4) * (size_t)cap));
+    CU(cudaMallocHost((void**)&S.h_best, sizeof(int) * (size_t)cap));
+    CU(cudaMallocHost((void**)&S.h_sidx, sizeof(int) * (size_t)cap));
+    S.h_cap = cap;
+  }
+  if (!S.d_sel) CU(cudaMalloc(&S.d_sel, sizeof(swk::SelState)));
+  // coordinate passes: a queue of k hits over at most 2 CTAs per SM, one linear-space carry row per CTA
+  const int loc_ctas = std::min(k, db->sm_count * 2);
+  const long long need = std::max<long long>(db->max_len, 32);
+  if (need > S.bnd_loc_stride || loc_ctas > S.loc_slots) {
+    cudaFree(S.d_bnd_loc); S.d_bnd_loc = nullptr;
+    S.bnd_loc_stride = std::max(need, S.bnd_loc_stride); S.loc_slots = std::max(loc_ctas, S.loc_slots);
+    CU(cudaMalloc((void**)&S.d_bnd_loc, sizeof(int2) * (size_t)S.bnd_loc_stride * (size_t)S.loc_slots));
+  }
+  swk::SelState* sel = (swk::SelState*)S.d_sel;
+  const int cap = S.topk_cap;
+  unsigned long long* keys_u = S.d_keys; unsigned long long* keys_s = S.d_keys + cap;
+  int* sidx_u = S.d_hit_sidx; int* sidx_s = S.d_hit_sidx + cap; int* best_out = S.d_hit_sidx + 2 * cap;
+
+  int launches = 0;
+  CU(cudaEventRecord(S.ev[8], st));
+  CU(cudaMemsetAsync(sel, 0, sizeof(swk::SelState), st));
+  CU(cudaMemsetAsync(S.d_counters + 7, 0, 3 * sizeof(unsigned), st));
+  swk::topk_init<<<1, 32, 0, st>>>(sel, (unsigned)k);
+  const int grid = (int)std::min<int64_t>((db->n + 255) / 256, (int64_t)db->sm_count * 8);
+  for (int pass = 0; pass < 8; ++pass) {
+    swk::topk_hist<<<grid, 256, 0, st>>>(S.d_scores, db->d_order, (long)db->n, pass, sel);
+    swk::topk_pick<<<1, 32, 0, st>>>(pass, sel);
+    launches += 2;
+  }
+  swk::topk_compact<<<grid, 256, 0, st>>>(S.d_scores, db->d_order, (long)db->n, sel, keys_u, sidx_u, k);
+  swk::topk_ranksort<<<(k + 255) / 256, 256, 0, st>>>(keys_u, sidx_u, k, keys_s, sidx_s);
+  launches += 3;
+  CU(cudaGetLastError());
+  if (S.lq > 0) {
+    // coordinates of the k hits against the query of this slot's search (hits with score 0 come out as -1)
+    swk::K3WParams P; memset(&P, 0, sizeof(P));
+    P.sidx_list = sidx_s; P.n_work = k; P.plain = db->d_plain; P.plain_off = db->d_plain_off; P.query = S.d_query;
+    P.lq = (int)S.lq; P.table = S.d_table; P.oe = S.oe; P.ge = S.ge; P.bnd = S.d_bnd_loc;
+    P.bnd_stride = S.bnd_loc_stride; P.coords = S.d_coords; P.best_out = best_out;
+    P.error_flag = S.d_counters + 7;
+    P.phase = 0; P.counter = S.d_counters + 8; swk::k3w<true><<<loc_ctas, swk::K3W_WARPS * 32, 0, st>>>(P);
+    P.phase = 1; P.counter = S.d_counters + 9; swk::k3w<true><<<loc_ctas, swk::K3W_WARPS * 32, 0, st>>>(P);
+    launches += 2;
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(S.h_coords, S.d_coords, sizeof(int4) * k, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(S.h_best, best_out, sizeof(int) * k, cudaMemcpyDeviceToHost, st));
+  }
+  CU(cudaMemcpyAsync(S.h_keys, keys_s, sizeof(unsigned long long) * k, cudaMemcpyDeviceToHost, st));
+  CU(cudaMemcpyAsync(S.h_sidx, sidx_s, sizeof(int) * k, cudaMemcpyDeviceToHost, st));
+  CU(cudaEventRecord(S.ev[9], st));
+  S.topk_k = k; S.topk_launches = launches;
+  return SWGPU_OK;
+}
+
+// Decode the hits of a finished slot (its completion event has been waited for; S.h_ctr holds the counters).
+int collect_topk(swgpu_db* db, swgpu_slot& S, swgpu_hit_t* hits, int* n_hits) {
+  const int k = S.topk_k;
+  if (n_hits) *n_hits = 0;
+  if (S.h_ctr[7]) return fail(SWGPU_ECUDA, "swgpu_topk: coordinate pipeline stalled (internal error)");
+  for (int i = 0; i < k; ++i) {
+    swgpu_hit_t& h = hits[i];
+    const unsigned long long key = S.h_keys[i];
+    h.score = (int32_t)(key >> 32);
+    h.entry = db->entry_base + (int64_t)(0xffffffffu - (unsigned)(key & 0xffffffffu));
+    if (S.lq > 0 && h.score > 0) {
+      const int4 c = S.h_coords[i];
+      h.q_start = c.x; h.q_end = c.y; h.t_start = c.z; h.t_end = c.w;
+      if (S.h_best[i] != h.score)
+        return fail(SWGPU_ECUDA, "swgpu_topk: coordinate pass found score %d for a hit scored %d (internal error)",
+                    S.h_best[i], h.score);
+    } else {
+      h.q_start = h.q_end = h.t_start = h.t_end = -1;         // hits with score 0 have no coordinates
+    }
+  }
+  if (n_hits) *n_hits = k;
+  return SWGPU_OK;
+}
+
+}  // namespace swi
+
 extern "C" int swgpu_topk(swgpu_db_t* db, int k, swgpu_hit_t* hits, int* n_hits) {
   if (n_hits) *n_hits = 0;
   if (!db || k < 0 || (k > 0 && !hits)) return fail(SWGPU_EINVAL, "swgpu_topk: bad argument");
-  if (!db->have_scores) return fail(SWGPU_EINVAL, "swgpu_topk: no search result resident");
+  swgpu_slot& S = db->slots[0];
+  if (!S.have_scores || S.in_flight) return fail(SWGPU_EINVAL, "swgpu_topk: no search result resident");
   if (k > 65536) return fail(SWGPU_EINVAL, "swgpu_topk: k > 65536 not supported");
   k = (int)std::min<int64_t>(k, db->n);
   db->last_stats.ms_topk = 0; db->last_stats.topk_launches = 0;
   if (k == 0) return SWGPU_OK;
   CU(cudaSetDevice(db->device));
-  cudaStream_t st = db->s_main;
-  if (k > db->topk_cap) {
-    cudaFree(db->d_keys); cudaFree(db->d_hit_sidx); cudaFree(db->d_coords); cudaFree(db->d_bnd_loc);
-    db->d_keys = nullptr; db->d_hit_sidx = nullptr; db->d_coords = nullptr; db->d_bnd_loc = nullptr; db->topk_cap = 0;
-    const int cap = std::max(k, 128);
-    CU(cudaMalloc((void**)&db->d_keys, sizeof(unsigned long long) * 2 * (size_t)cap));
-    CU(cudaMalloc((void**)&db->d_hit_sidx, sizeof(int) * 3 * (size_t)cap));       // unsorted, sorted, best_out
-    CU(cudaMalloc((void**)&db->d_coords, sizeof(int4) * (size_t)cap));
-    db->topk_cap = cap;
-  }
-  if (!db->d_sel) CU(cudaMalloc(&db->d_sel, sizeof(swk::SelState)));
-  swk::SelState* sel = (swk::SelState*)db->d_sel;
-  const int cap = db->topk_cap;
-  unsigned long long* keys_u = db->d_keys; unsigned long long* keys_s = db->d_keys + cap;
-  int* sidx_u = db->d_hit_sidx; int* sidx_s = db->d_hit_sidx + cap; int* best_out = db->d_hit_sidx + 2 * cap;
-
-  int launches = 0;
-  CU(cudaEventRecord(db->ev[4], st));
-  swk::SelState init; memset(&init, 0, sizeof(init)); init.k_rem = (unsigned)k;
-  CU(cudaMemcpyAsync(sel, &init, sizeof(init), cudaMemcpyHostToDevice, st));   // pageable source: copied before return
-  const int grid = (int)std::min<int64_t>((db->n + 255) / 256, (int64_t)db->sm_count * 8);
-  for (int pass = 0; pass < 8; ++pass) {
-    swk::topk_hist<<<grid, 256, 0, st>>>(db->d_scores, db->d_order, (long)db->n, pass, sel);
-    swk::topk_pick<<<1, 32, 0, st>>>(pass, sel);
-    launches += 2;
-  }
-  swk::topk_compact<<<grid, 256, 0, st>>>(db->d_scores, db->d_order, (long)db->n, sel, keys_u, sidx_u, k);
-  swk::topk_ranksort<<<(k + 255) / 256, 256, 0, st>>>(keys_u, sidx_u, k, keys_s, sidx_s);
-  launches += 2;
-  CU(cudaGetLastError());
-
-  // coordinates of the k hits against the query of the last search
-  std::vector<unsigned long long> hk(k);
-  std::vector<int> hs(k);
-  CU(cudaMemcpyAsync(hk.data(), keys_s, sizeof(unsigned long long) * k, cudaMemcpyDeviceToHost, st));
-  CU(cudaMemcpyAsync(hs.data(), sidx_s, sizeof(int) * k, cudaMemcpyDeviceToHost, st));
-  CU(cudaStreamSynchronize(st));
-  std::vector<int4> hc(k, make_int4(-1, -1, -1, -1));
-  std::vector<int> hb(k, 0);
-  unsigned loc_err = 0;
-  const int lq = (int)db->last_lq;
-  int n_pos = 0;
-  while (n_pos < k && (hk[n_pos] >> 32) != 0) ++n_pos;          // hits with score 0 have no coordinates
-  if (lq > 0 && n_pos > 0) {
-    // linear-space carry buffer: one row of (H, V) per hit, as long as the longest hit target
-    long long need = 32;
-    for (int i = 0; i < n_pos; ++i)
-      need = std::max<long long>(need, db->h_len_sorted_prefix[hs[i] + 1] - db->h_len_sorted_prefix[hs[i]]);
-    if (need > db->bnd_loc_stride || n_pos > db->loc_slots) {
-      cudaFree(db->d_bnd_loc); db->d_bnd_loc = nullptr;
-      db->bnd_loc_stride = std::max(need, db->bnd_loc_stride); db->loc_slots = std::max(n_pos, db->loc_slots);
-      CU(cudaMalloc((void**)&db->d_bnd_loc, sizeof(int2) * (size_t)db->bnd_loc_stride * (size_t)db->loc_slots));
-    }
-    swk::K3WParams P; memset(&P, 0, sizeof(P));
-    P.sidx_list = sidx_s; P.n_work = n_pos; P.plain = db->d_plain; P.plain_off = db->d_plain_off; P.query = db->d_query;
-    P.lq = lq; P.table = db->d_table; P.oe = db->last_oe; P.ge = db->last_ge; P.bnd = db->d_bnd_loc;
-    P.bnd_stride = db->bnd_loc_stride; P.coords = db->d_coords; P.best_out = best_out;
-    P.error_flag = db->d_counters + 7;
-    CU(cudaMemsetAsync(db->d_counters + 7, 0, sizeof(unsigned), st));
-    P.phase = 0; swk::k3w<true><<<n_pos, swk::K3W_WARPS * 32, 0, st>>>(P);
-    P.phase = 1; swk::k3w<true><<<n_pos, swk::K3W_WARPS * 32, 0, st>>>(P);
-    launches += 2;
-    CU(cudaGetLastError());
-    CU(cudaMemcpyAsync(&loc_err, db->d_counters + 7, sizeof(unsigned), cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(hc.data(), db->d_coords, sizeof(int4) * n_pos, cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(hb.data(), best_out, sizeof(int) * n_pos, cudaMemcpyDeviceToHost, st));
-  }
-  CU(cudaEventRecord(db->ev[5], st));
-  CU(cudaStreamSynchronize(st));
-  float ms = 0; CU(cudaEventElapsedTime(&ms, db->ev[4], db->ev[5]));
-  db->last_stats.ms_topk = ms; db->last_stats.topk_launches = launches;
-  if (loc_err) return fail(SWGPU_ECUDA, "swgpu_topk: coordinate pipeline stalled (internal error)");
-  for (int i = 0; i < k; ++i) {
-    swgpu_hit_t& h = hits[i];
-    h.score = (int32_t)(hk[i] >> 32);
-    h.entry = db->entry_base + (int64_t)(0xffffffffu - (unsigned)(hk[i] & 0xffffffffu));
-    h.q_start = hc[i].x; h.q_end = hc[i].y; h.t_start = hc[i].z; h.t_end = hc[i].w;
-    if (i < n_pos && lq > 0 && hb[i] != h.score)
-      return fail(SWGPU_ECUDA, "swgpu_topk: coordinate pass found score %d for a hit scored %d (internal error)", hb[i], h.score);
-  }
-  if (n_hits) *n_hits = k;
-  return SWGPU_OK;
+  int r = swi::enqueue_topk(db, S, k);
+  if (r) { cudaDeviceSynchronize(); return r; }
+  CU(cudaMemcpyAsync(S.h_ctr, S.d_counters, 16 * sizeof(unsigned), cudaMemcpyDeviceToHost, S.s_aux));
+  CU(cudaStreamSynchronize(S.s_aux));
+  float ms = 0; CU(cudaEventElapsedTime(&ms, S.ev[8], S.ev[9]));
+  S.st.ms_topk = ms; S.st.topk_launches = S.topk_launches;
+  db->last_stats.ms_topk = ms; db->last_stats.topk_launches = S.topk_launches;
+  return swi::collect_topk(db, S, hits, n_hits);
 }
 
 extern "C" int swgpu_db_last_stats(const swgpu_db_t* db, swgpu_stats_t* out) {

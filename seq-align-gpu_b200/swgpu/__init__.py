@@ -40,6 +40,14 @@ class Hit(C.Structure):
                 ("t_start", C.c_int32), ("t_end", C.c_int32), ("entry", C.c_int64)]
 
 
+class BatchStats(C.Structure):
+    _fields_ = [("ms_total", C.c_double), ("cells", C.c_int64), ("n_rescored", C.c_int64),
+                ("kernel_launches", C.c_int32), ("slots", C.c_int32), ("reserved", C.c_int32 * 4)]
+
+    def as_dict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_ if k != "reserved"}
+
+
 class PackOpts(C.Structure):
     _fields_ = [("long_threshold", C.c_int32), ("stream_cols", C.c_int32), ("reserved", C.c_int32 * 6)]
 
@@ -75,6 +83,9 @@ def lib():
     L.swgpu_db_scores_d2h.argtypes = [C.c_void_p, C.c_void_p]
     L.swgpu_topk.restype = C.c_int
     L.swgpu_topk.argtypes = [C.c_void_p, C.c_int, P(Hit), P(C.c_int)]
+    L.swgpu_search_many.restype = C.c_int
+    L.swgpu_search_many.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
+                                    C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, P(BatchStats)]
     L.swgpu_db_last_stats.restype = C.c_int
     L.swgpu_db_last_stats.argtypes = [C.c_void_p, P(Stats)]
     L.swgpu_fill_batch16.restype = C.c_int
@@ -136,6 +147,31 @@ class Database:
         st = Stats()
         _check(lib().swgpu_search_resident(self._h, pq, q.size, pt, int(gap_open), int(gap_extend), C.byref(st)))
         return st.as_dict()
+
+    def search_many(self, queries, table, gap_open, gap_extend, k=0, want_scores=True, out=None):
+        """swgpu_search_many(): several queries in flight.  Returns (scores [nq][n] or None, hits per query,
+        per-query stats, batch stats).  `out`: optional list of int32[n] host arrays (pinned ones are written
+        directly by the copy engine)."""
+        nq = len(queries)
+        qs = [np.ascontiguousarray(q, dtype=np.int8) for q in queries]
+        qptr = (C.c_void_p * max(nq, 1))(*[q.ctypes.data for q in qs])
+        qlen = np.array([q.size for q in qs], dtype=np.int64)
+        t, pt = _i8(np.asarray(table).reshape(-1))
+        assert t.size == 1024
+        scores, sptr = None, None
+        if want_scores:
+            scores = out if out is not None else [np.empty(self.n, dtype=np.int32) for _ in range(nq)]
+            sptr = (C.c_void_p * max(nq, 1))(*[a.ctypes.data for a in scores])
+        hits = (Hit * max(nq * k, 1))()
+        nh = np.zeros(max(nq, 1), dtype=np.int32)
+        per = (Stats * max(nq, 1))()
+        bs = BatchStats()
+        _check(lib().swgpu_search_many(self._h, nq, qptr, qlen.ctypes.data_as(C.c_void_p), pt, int(gap_open),
+                                       int(gap_extend), sptr, int(k), hits if k else None,
+                                       nh.ctypes.data_as(C.c_void_p) if k else None, per, C.byref(bs)))
+        out_hits = [[dict(score=h.score, q_start=h.q_start, q_end=h.q_end, t_start=h.t_start, t_end=h.t_end,
+                          entry=h.entry) for h in hits[q * k: q * k + int(nh[q])]] for q in range(nq)] if k else None
+        return scores, out_hits, [per[q].as_dict() for q in range(nq)], bs.as_dict()
 
     def scores(self):
         s = np.empty(self.n, dtype=np.int32)
