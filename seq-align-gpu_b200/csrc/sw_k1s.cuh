@@ -89,11 +89,15 @@ constexpr size_t k1s_smem_bytes() {
   return (size_t)SProf<R>::WORDS * 4 + (size_t)K1S_WARPS * (128 * 2 + 32 * 8) + 16;
 }
 
+// LANES = lanes per target pair (g), a compile-time constant (shuffle widths, ring masks and the block period fold into
+// immediates: measured 5-7 % over a run-time g).
 // MULTI = false: the whole query fits one stripe; warps pull items independently.
 // MULTI = true : g == 32, several stripes; the CTA pulls 8 items at a time and reloads the
 //                shared profile between stripes.
-template <int R, bool MULTI>
+template <int R, int LANES, bool MULTI>
 __global__ void __launch_bounds__(K1S_WARPS * 32, (R <= K1S_R3CTA ? 3 : 2)) k1s(const K1SParams P) {
+  static_assert(LANES == 8 || LANES == 16 || LANES == 32, "lanes per pair");
+  static_assert(!MULTI || LANES == 32, "multi-stripe mode uses all 32 lanes");
   using S = SProf<R>;
   extern __shared__ __align__(16) unsigned smem_u32[];
   unsigned* prof_s = smem_u32;
@@ -102,9 +106,9 @@ __global__ void __launch_bounds__(K1S_WARPS * 32, (R <= K1S_R3CTA ? 3 : 2)) k1s(
   uint2* ring2 = reinterpret_cast<uint2*>(reinterpret_cast<unsigned short*>(smem_u32 + S::WORDS) + K1S_WARPS * 128) + warp * 32;
   __shared__ unsigned cta_item;
 
-  const int g = MULTI ? 32 : P.g, g_log2 = MULTI ? 5 : P.g_log2;
+  constexpr int g = LANES, g_log2 = (LANES == 8 ? 3 : LANES == 16 ? 4 : 5);
   const int lane_g = lane & (g - 1), grp = lane >> g_log2, per_warp = 32 >> g_log2;
-  const int rmask = 4 * g - 1;                       // ring of 4g columns per group (g-step blocks, generous slack)
+  constexpr int rmask = 4 * g - 1;                       // ring of 4g columns per group (g-step blocks, generous slack)
   unsigned short* gring = ring + grp * (4 * g);
   const unsigned BB = P.BB, BBM = P.BBM, OE2 = P.OE2, GE2 = P.GE2;
   const unsigned pa_lane = (unsigned)__cvta_generic_to_shared(prof_s) + lane * 4;

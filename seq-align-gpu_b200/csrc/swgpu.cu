@@ -158,6 +158,12 @@ int64_t swgpu_db_device_bytes(const swgpu_db_t* db) { return db ? db->device_byt
 // ------------------------------------------------------------------------------------------
 namespace {
 
+// Instantiated kernels: every even R in 8..32 for g = 8, 16, 32; multi-stripe (g = 32) with R in {16, 20, 24..32}.
+bool k1s_has_plan(int g, int R, bool multi) {
+  if (R < 8 || R > 32 || (R & 1) || (g != 8 && g != 16 && g != 32)) return false;
+  return !multi || (g == 32 && (R == 16 || R == 20 || R >= 24));
+}
+
 // K1S plan: lanes per target pair (g), query rows per lane (R), stripes (npass).
 // Cost model: padded rows x (cell work + per-step overhead / R); few work items -> prefer more lanes per pair.
 struct K1SPlan { int g, g_log2, R, npass; };
@@ -185,35 +191,47 @@ K1SPlan plan_k1s(int64_t lq, int64_t n_streams, int warp_slots) {
     if (sscanf(ev, "%d,%d", &g, &R) == 2 && (g == 8 || g == 16 || g == 32) && R >= 8 && R <= 32 && !(R & 1)) {
       const int gl = g == 8 ? 3 : g == 16 ? 4 : 5;
       const int np = (int)((lq + (int64_t)g * R - 1) / ((int64_t)g * R));
-      if (np == 1 || (g == 32 && (R == 16 || R == 20 || R >= 24))) best = K1SPlan{g, gl, R, np};
+      if (k1s_has_plan(g, R, np > 1)) best = K1SPlan{g, gl, R, np};
     }
   }
   return best;
 }
 
-template <int R, bool MULTI>
+template <int R, int G, bool MULTI>
 int launch_k1s_t(swgpu_db* db, const swk::K1SParams& P, cudaStream_t stream, int grid) {
   const size_t smem = swk::k1s_smem_bytes<R>();
   static thread_local bool attr_done[16] = {};
   if (!attr_done[db->device & 15]) {
-    CU(cudaFuncSetAttribute(swk::k1s<R, MULTI>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CU(cudaFuncSetAttribute(swk::k1s<R, G, MULTI>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attr_done[db->device & 15] = true;
   }
-  swk::k1s<R, MULTI><<<grid, swk::K1S_WARPS * 32, smem, stream>>>(P);
+  swk::k1s<R, G, MULTI><<<grid, swk::K1S_WARPS * 32, smem, stream>>>(P);
   CU(cudaGetLastError());
   return SWGPU_OK;
 }
 
-int launch_k1s(swgpu_db* db, const swk::K1SParams& P, int R, bool multi, cudaStream_t stream, int grid) {
-#define K1S_CASE(r) case r: return multi ? launch_k1s_t<r, true>(db, P, stream, grid) : launch_k1s_t<r, false>(db, P, stream, grid);
-#define K1S_CASE1(r) case r: return launch_k1s_t<r, false>(db, P, stream, grid);
+template <int G>
+int launch_k1s_g(swgpu_db* db, const swk::K1SParams& P, int R, cudaStream_t stream, int grid) {
+#define K1S_CASE(r) case r: return launch_k1s_t<r, G, false>(db, P, stream, grid);
   switch (R) {
-    K1S_CASE1(8) K1S_CASE1(10) K1S_CASE1(12) K1S_CASE1(14) K1S_CASE(16) K1S_CASE1(18) K1S_CASE(20) K1S_CASE1(22)
+    K1S_CASE(8) K1S_CASE(10) K1S_CASE(12) K1S_CASE(14) K1S_CASE(16) K1S_CASE(18) K1S_CASE(20) K1S_CASE(22)
     K1S_CASE(24) K1S_CASE(26) K1S_CASE(28) K1S_CASE(30) K1S_CASE(32)
-    default: return fail(SWGPU_EINVAL, "no k1s instantiation for R=%d", R);
+    default: return fail(SWGPU_EINVAL, "no k1s instantiation for g=%d R=%d", G, R);
   }
 #undef K1S_CASE
-#undef K1S_CASE1
+}
+
+int launch_k1s(swgpu_db* db, const swk::K1SParams& P, int g, int R, bool multi, cudaStream_t stream, int grid) {
+  if (!k1s_has_plan(g, R, multi)) return fail(SWGPU_EINVAL, "no k1s instantiation for g=%d R=%d multi=%d", g, R, (int)multi);
+  if (multi) {
+#define K1S_CASEM(r) case r: return launch_k1s_t<r, 32, true>(db, P, stream, grid);
+    switch (R) { K1S_CASEM(16) K1S_CASEM(20) K1S_CASEM(24) K1S_CASEM(26) K1S_CASEM(28) K1S_CASEM(30) K1S_CASEM(32) default: break; }
+#undef K1S_CASEM
+    return fail(SWGPU_EINVAL, "no multi-stripe k1s instantiation for R=%d", R);
+  }
+  if (g == 8) return launch_k1s_g<8>(db, P, R, stream, grid);
+  if (g == 16) return launch_k1s_g<16>(db, P, R, stream, grid);
+  return launch_k1s_g<32>(db, P, R, stream, grid);
 }
 
 // 32-bit scoring of a work list (device-side count) or of all targets (list == nullptr): k3_intra (one warp per
@@ -332,7 +350,7 @@ int enqueue_search(swgpu_db* db, swgpu_slot& S, const int8_t* query, int64_t lq,
       PL.stream_begin = 0; PL.n_streams = (int)nls; PL.n_items = (int)nls; PL.prof = S.d_sprof2; PL.npass = 1;
       PL.g = 32; PL.g_log2 = 5; PL.counter = S.d_counters + 1; PL.raw = S.d_raw_s;
       PL.active_warps = 1;                                     // one long stream per CTA: spread them over the SMs
-      if ((r = launch_k1s(db, PL, plan_long.R, false, sa, (int)std::min<int64_t>(nls, db->k1s_grid)))) return r;
+      if ((r = launch_k1s(db, PL, 32, plan_long.R, false, sa, (int)std::min<int64_t>(nls, db->k1s_grid)))) return r;
       swk::k1s_finalize<<<std::max(1, (int)((nlp + 255) / 256)), 256, 0, sa>>>(
           S.d_raw_s, 0, (long)nlp, 5, (long)db->n, B, limit, db->d_order, db->d_plain_off, db->long_threshold,
           S.d_scores, S.d_rescore_list, S.d_counters + 2);
@@ -352,7 +370,7 @@ int enqueue_search(swgpu_db* db, swgpu_slot& S, const int8_t* query, int64_t lq,
     if (PS.n_streams > 0) {
       int ctas = plan.R <= K1S_R3CTA ? 3 : 2;
       if (const char* ev = getenv("SWGPU_K1S_CTAS")) ctas = std::max(1, std::min(ctas, atoi(ev)));   // A/B knob (profiling)
-      if ((r = launch_k1s(db, PS, plan.R, plan.npass > 1, sm, db->sm_count * ctas))) return r;
+      if ((r = launch_k1s(db, PS, plan.g, plan.R, plan.npass > 1, sm, db->sm_count * ctas))) return r;
       swk::k1s_finalize<<<(int)std::min<int64_t>((db->n_pairs - nlp + 255) / 256, 4096), 256, 0, sm>>>(
           PS.raw, (long)nlp, (long)db->n_pairs, plan.g_log2, (long)db->n, B, limit, db->d_order, db->d_plain_off,
           db->long_threshold, S.d_scores, S.d_rescore_list, S.d_counters + 2);
