@@ -216,30 +216,39 @@ typedef struct {
     int device;
     const int8_t *codes; const int64_t *off; int64_t n;   /* this shard */
     const int64_t *entry;                                 /* shard index -> file index (NULL = identity) */
-    const int8_t *query; int64_t lq; const scoring_t *sc;
-    int32_t *scores_file;                                 /* shared output, file order */
-    int topk; swgpu_hit_t *hits; int n_hits;
+    int nq; const int8_t *const *queries; const int64_t *qlens; const scoring_t *sc;
+    int32_t **scores_file;                                /* [nq] shared outputs, file order (NULL in top-k mode) */
+    int topk; swgpu_hit_t *hits; int32_t *n_hits;         /* [nq * topk], [nq] */
     double ms; int rc; char err[512];
 } shard_job_t;
 
+/* one GPU: pack this shard, then all queries through swgpu_search_many() (up to three in flight) */
 static void *shard_run(void *arg)
 {
     shard_job_t *j = (shard_job_t *)arg;
     swgpu_db_t *db = NULL;
     j->rc = swgpu_db_create(&db, j->device, j->codes, j->off, j->n, 0, NULL);
     if (j->rc == SWGPU_OK) {
-        int32_t *tmp = (int32_t *)malloc(sizeof(int32_t) * (size_t)(j->n ? j->n : 1));
-        swgpu_stats_t st;
-        j->rc = swgpu_search(db, j->query, j->lq, &j->sc->swap_scores[0][0], j->sc->gap_open, j->sc->gap_extend, tmp, &st);
-        if (j->rc == SWGPU_OK) {
-            j->ms = st.ms_total;
-            for (int64_t i = 0; i < j->n; i++) j->scores_file[j->entry ? j->entry[i] : i] = tmp[i];
-            if (j->topk > 0) {
-                j->rc = swgpu_topk(db, j->topk, j->hits, &j->n_hits);
-                for (int h = 0; h < j->n_hits && j->entry; h++) j->hits[h].entry = j->entry[j->hits[h].entry];
-            }
+        const size_t n1 = (size_t)(j->n ? j->n : 1);
+        int32_t **tmp = NULL;
+        if (j->scores_file) {
+            tmp = (int32_t **)calloc((size_t)j->nq, sizeof(*tmp));
+            for (int q = 0; q < j->nq; q++) tmp[q] = j->entry ? (int32_t *)malloc(sizeof(int32_t) * n1) : j->scores_file[q];
         }
-        free(tmp);
+        swgpu_batch_stats_t bs;
+        j->rc = swgpu_search_many(db, j->nq, j->queries, j->qlens, &j->sc->swap_scores[0][0], j->sc->gap_open,
+                                  j->sc->gap_extend, tmp, j->topk, j->hits, j->n_hits, NULL, &bs);
+        if (j->rc == SWGPU_OK) {
+            j->ms = bs.ms_total;
+            for (int q = 0; q < j->nq && tmp && j->entry; q++)
+                for (int64_t i = 0; i < j->n; i++) j->scores_file[q][j->entry[i]] = tmp[q][i];
+            for (int q = 0; q < j->nq && j->topk > 0 && j->entry; q++)
+                for (int h = 0; h < j->n_hits[q]; h++) {
+                    swgpu_hit_t *hit = &j->hits[(size_t)q * (size_t)j->topk + (size_t)h];
+                    hit->entry = j->entry[hit->entry];
+                }
+        }
+        if (tmp) { for (int q = 0; q < j->nq; q++) if (j->entry) free(tmp[q]); free(tmp); }
     }
     if (j->rc != SWGPU_OK) snprintf(j->err, sizeof(j->err), "%s", swgpu_last_error());
     swgpu_db_destroy(db);
@@ -253,8 +262,16 @@ static int hit_cmp(const void *a, const void *b)
     return x->entry < y->entry ? -1 : (x->entry > y->entry);
 }
 
+static int i64_cmp(const void *a, const void *b)
+{
+    const int64_t x = *(const int64_t *)a, y = *(const int64_t *)b;
+    return x < y ? -1 : (x > y);
+}
+
 /* length-balanced sharding: deal the targets, longest first, round-robin over the GPUs, so every
- * shard gets the same length mix and (to within one target per round) the same residue count */
+ * shard gets the same length mix and (to within one target per round) the same residue count.
+ * Inside a shard the targets stay in ascending file order: the engine's tie-break (score desc,
+ * shard-local entry asc) is then the global rule and the merged top-k does not depend on the GPU count. */
 static void make_shards(const dbmem_t *d, int g, int8_t **codes, int64_t **off, int64_t **entry, int64_t *cnt)
 {
     const size_t n = d->n;
@@ -274,11 +291,12 @@ static void make_shards(const dbmem_t *d, int g, int8_t **codes, int64_t **off, 
         off[s] = (int64_t *)malloc(sizeof(int64_t) * (size_t)(m + 1));
         entry[s] = (int64_t *)malloc(sizeof(int64_t) * (size_t)(m ? m : 1));
         int64_t k = 0; off[s][0] = 0;
-        for (size_t r = (size_t)s; r < n; r += (size_t)g, k++) {
-            const int64_t t = order[r], l = d->off[t + 1] - d->off[t];
+        for (size_t r = (size_t)s; r < n; r += (size_t)g, k++) entry[s][k] = order[r];
+        qsort(entry[s], (size_t)m, sizeof(int64_t), i64_cmp);
+        for (k = 0; k < m; k++) {
+            const int64_t t = entry[s][k], l = d->off[t + 1] - d->off[t];
             memcpy(codes[s] + off[s][k], d->codes + d->off[t], (size_t)l);
             off[s][k + 1] = off[s][k] + l;
-            entry[s][k] = t;
         }
     }
     free(order);
@@ -292,18 +310,36 @@ void align_from_query_and_db(const char *query_path, const char *db_path, scorin
     swfa_reader_t *df = swfa_open(db_path, use_zlib);
     if (!df) { fprintf(stderr, "Error: couldn't open database file %s\n", db_path); fflush(stderr); swfa_close(qf); return; }
 
-    swfa_record_t q = {0}, rec = {0};
-    if (swfa_read(qf, &q) <= 0 || q.seq_len == 0) {
+    /* The reference aligns the FIRST record of the query file only (src/alignment_cmdline.c:369-380).  With
+     * SWGPU_ALL_QUERIES=1 every record is a query (many-to-many): the listing below is repeated per query. */
+    const char *eq = getenv("SWGPU_ALL_QUERIES");
+    const int all_queries = eq && atoi(eq) > 0;
+    swfa_record_t *qrec = NULL; int nq = 0, qcap = 0;
+    for (;;) {
+        swfa_record_t r = {0};
+        const int got = swfa_read(qf, &r);
+        if (got <= 0 || r.seq_len == 0) { swfa_record_free(&r); break; }
+        if (nq == qcap) { qcap = qcap ? qcap * 2 : 4; qrec = (swfa_record_t *)realloc(qrec, (size_t)qcap * sizeof(*qrec)); }
+        qrec[nq++] = r;
+        if (!all_queries) break;
+    }
+    if (nq == 0) {
         fprintf(stderr, "Error: Query file %s is empty or invalid\n", query_path); fflush(stderr);
-        swfa_close(qf); swfa_close(df); swfa_record_free(&q); return;
+        swfa_close(qf); swfa_close(df); free(qrec); return;
     }
     /* query encode; letters whose diagonal the matrix never defined become 'X' (src/alignment_cmdline.c:388-396) */
-    int8_t *qi = (int8_t *)malloc(q.seq_len);
-    for (size_t i = 0; i < q.seq_len; i++) {
-        qi[i] = letters_to_index(q.seq[i]);
-        if (!get_swap_bit(scoring, qi[i], qi[i])) qi[i] = letters_to_index('X');
+    int8_t **qi = (int8_t **)calloc((size_t)nq, sizeof(*qi));
+    int64_t *qlen = (int64_t *)calloc((size_t)nq, sizeof(int64_t));
+    for (int k = 0; k < nq; k++) {
+        qlen[k] = (int64_t)qrec[k].seq_len;
+        qi[k] = (int8_t *)malloc(qrec[k].seq_len);
+        for (size_t i = 0; i < qrec[k].seq_len; i++) {
+            qi[k][i] = letters_to_index(qrec[k].seq[i]);
+            if (!get_swap_bit(scoring, qi[k][i], qi[k][i])) qi[k][i] = letters_to_index('X');
+        }
     }
 
+    swfa_record_t rec = {0};
     dbmem_t d; memset(&d, 0, sizeof(d));
     int st;
     while ((st = swfa_read(df, &rec)) > 0) db_push(&d, &rec);
@@ -321,7 +357,11 @@ void align_from_query_and_db(const char *query_path, const char *db_path, scorin
     const char *ek = getenv("SWGPU_TOPK");
     if (ek && atoi(ek) > 0) topk = atoi(ek);
 
-    int32_t *scores = (int32_t *)calloc(d.n ? d.n : 1, sizeof(int32_t));
+    int32_t **scores = NULL;
+    if (!topk) {
+        scores = (int32_t **)calloc((size_t)nq, sizeof(*scores));
+        for (int k = 0; k < nq; k++) scores[k] = (int32_t *)calloc(d.n ? d.n : 1, sizeof(int32_t));
+    }
     shard_job_t *jobs = (shard_job_t *)calloc((size_t)g, sizeof(shard_job_t));
     int8_t **sc_codes = (int8_t **)calloc((size_t)g, sizeof(*sc_codes));
     int64_t **sc_off = (int64_t **)calloc((size_t)g, sizeof(*sc_off)), **sc_entry = (int64_t **)calloc((size_t)g, sizeof(*sc_entry));
@@ -330,8 +370,11 @@ void align_from_query_and_db(const char *query_path, const char *db_path, scorin
     pthread_t *th = (pthread_t *)calloc((size_t)g, sizeof(pthread_t));
     for (int s = 0; s < g; s++) {
         shard_job_t *j = &jobs[s];
-        j->device = s; j->query = qi; j->lq = (int64_t)q.seq_len; j->sc = scoring; j->scores_file = scores;
-        j->topk = topk; j->hits = topk ? (swgpu_hit_t *)calloc((size_t)topk, sizeof(swgpu_hit_t)) : NULL;
+        j->device = s; j->nq = nq; j->queries = (const int8_t *const *)qi; j->qlens = qlen; j->sc = scoring;
+        j->scores_file = scores;
+        j->topk = topk;
+        j->hits = topk ? (swgpu_hit_t *)calloc((size_t)topk * (size_t)nq, sizeof(swgpu_hit_t)) : NULL;
+        j->n_hits = topk ? (int32_t *)calloc((size_t)nq, sizeof(int32_t)) : NULL;
         if (g > 1) { j->codes = sc_codes[s]; j->off = sc_off[s]; j->n = sc_cnt[s]; j->entry = sc_entry[s]; }
         else { j->codes = d.codes; j->off = d.off; j->n = (int64_t)d.n; j->entry = NULL; }
         if (g > 1) pthread_create(&th[s], NULL, shard_run, j); else shard_run(j);
@@ -344,43 +387,50 @@ void align_from_query_and_db(const char *query_path, const char *db_path, scorin
     }
 
     /* ---- hand-off: the reference's callback over groups of 16 entries in file order (:511-512) ---- */
-    if (topk > 0) {
-        swgpu_hit_t *all = (swgpu_hit_t *)calloc((size_t)topk * (size_t)g, sizeof(swgpu_hit_t));
-        int m = 0;
-        for (int s = 0; s < g; s++) for (int h = 0; h < jobs[s].n_hits; h++) all[m++] = jobs[s].hits[h];
-        qsort(all, (size_t)m, sizeof(swgpu_hit_t), hit_cmp);       /* score desc, entry asc: independent of the GPU count */
-        if (m > topk) m = topk;
-        for (int h = 0; h < m; h++)
-            printf("Hit #%d: entry %lld score %d query [%d..%d] target [%d..%d] %s\n", h, (long long)all[h].entry, all[h].score,
-                   all[h].q_start, all[h].q_end, all[h].t_start, all[h].t_end, d.names[all[h].entry]);
-        free(all);
-    } else {
-        aligner_t view; aligner_init(&view);
-        score_t s16[16]; int32_t s32[16];
-        view.scoring = scoring; view.seq_a_indexes = qi; view.seq_a_str = q.seq; view.seq_a_fasta = q.name;
-        view.score_width = q.seq_len + 1; view.max_scores = s16; view.max_scores32 = s32;
-        for (size_t first = 0; first < d.n; first += 16) {
-            const size_t lanes = d.n - first < 16 ? d.n - first : 16;
-            view.vector_size = lanes;
-            view.seq_b_str_batch = d.seqs + first; view.seq_b_fasta_batch = d.names + first;
-            size_t maxlen = 0;
-            for (size_t l = 0; l < lanes; l++) {
-                s32[l] = scores[first + l];
-                s16[l] = (score_t)(s32[l] > 32767 ? 32767 : s32[l]);
-                const size_t len = (size_t)(d.off[first + l + 1] - d.off[first + l]);
-                if (len > maxlen) maxlen = len;
+    for (int k = 0; k < nq; k++) {
+        if (topk > 0) {
+            swgpu_hit_t *all = (swgpu_hit_t *)calloc((size_t)topk * (size_t)g, sizeof(swgpu_hit_t));
+            int m = 0;
+            for (int s = 0; s < g; s++)
+                for (int h = 0; h < jobs[s].n_hits[k]; h++) all[m++] = jobs[s].hits[(size_t)k * (size_t)topk + (size_t)h];
+            qsort(all, (size_t)m, sizeof(swgpu_hit_t), hit_cmp);   /* score desc, entry asc: independent of the GPU count */
+            if (m > topk) m = topk;
+            if (all_queries) printf("Query #%d: %s\n", k, qrec[k].name);
+            for (int h = 0; h < m; h++)
+                printf("Hit #%d: entry %lld score %d query [%d..%d] target [%d..%d] %s\n", h, (long long)all[h].entry, all[h].score,
+                       all[h].q_start, all[h].q_end, all[h].t_start, all[h].t_end, d.names[all[h].entry]);
+            free(all);
+        } else {
+            aligner_t view; aligner_init(&view);
+            score_t s16[16]; int32_t s32[16];
+            view.scoring = scoring; view.seq_a_indexes = qi[k]; view.seq_a_str = qrec[k].seq; view.seq_a_fasta = qrec[k].name;
+            view.score_width = qrec[k].seq_len + 1; view.max_scores = s16; view.max_scores32 = s32;
+            for (size_t first = 0; first < d.n; first += 16) {
+                const size_t lanes = d.n - first < 16 ? d.n - first : 16;
+                view.vector_size = lanes;
+                view.seq_b_str_batch = d.seqs + first; view.seq_b_fasta_batch = d.names + first;
+                size_t maxlen = 0;
+                for (size_t l = 0; l < lanes; l++) {
+                    s32[l] = scores[k][first + l];
+                    s16[l] = (score_t)(s32[l] > 32767 ? 32767 : s32[l]);
+                    const size_t len = (size_t)(d.off[first + l + 1] - d.off[first + l]);
+                    if (len > maxlen) maxlen = len;
+                }
+                view.score_height = maxlen + 1;
+                print_alignment(&view, first);
             }
-            view.score_height = maxlen + 1;
-            print_alignment(&view, first);
         }
     }
     printf("Total Time: %f\n", total_ms * 1e-3);
     printf("Total Entries: %lu\n", (unsigned long)d.n);
 
-    for (int s = 0; s < g; s++) { free(jobs[s].hits); free(sc_codes[s]); free(sc_off[s]); free(sc_entry[s]); }
-    free(jobs); free(sc_codes); free(sc_off); free(sc_entry); free(sc_cnt); free(th); free(scores);
+    for (int s = 0; s < g; s++) { free(jobs[s].hits); free(jobs[s].n_hits); free(sc_codes[s]); free(sc_off[s]); free(sc_entry[s]); }
+    free(jobs); free(sc_codes); free(sc_off); free(sc_entry); free(sc_cnt); free(th);
+    for (int k = 0; k < nq && scores; k++) free(scores[k]);
+    free(scores);
     for (size_t i = 0; i < d.n; i++) { free(d.names[i]); free(d.seqs[i]); }
     free(d.names); free(d.seqs); free(d.codes); free(d.off);
-    free(qi); swfa_record_free(&q); swfa_record_free(&rec);
+    for (int k = 0; k < nq; k++) { free(qi[k]); swfa_record_free(&qrec[k]); }
+    free(qi); free(qlen); free(qrec); swfa_record_free(&rec);
     swfa_close(qf); swfa_close(df);
 }

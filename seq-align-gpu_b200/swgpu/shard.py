@@ -12,11 +12,13 @@ import numpy as np
 def deal_shards(offsets, world):
     """Deal targets, longest first, round-robin over `world` ranks.  Returns a list of int64 arrays of
     file-order entry indices; every rank gets the same length mix and (within one target per round) the
-    same residue count.  Same rule as make_shards() in host/alignment_cmdline.c."""
+    same residue count.  Inside a shard the entries stay in ascending file order, so the engine's tie-break
+    (score desc, shard-local entry asc) is the global rule and the merged top-k is independent of `world`.
+    Same rule as make_shards() in host/alignment_cmdline.c."""
     offsets = np.asarray(offsets, dtype=np.int64)
     lens = offsets[1:] - offsets[:-1]
     order = np.argsort(-lens, kind="stable")
-    return [order[r::world].copy() for r in range(world)]
+    return [np.sort(order[r::world]) for r in range(world)]
 
 
 def take_shard(codes, offsets, entries):

@@ -176,3 +176,42 @@ def test_cli_unsorted_db_partial_batch_gzip_and_topk(tmp_path, oracle, matrices)
     assert len(hits) == 3 and int(hits[0][1]) == 20 and int(hits[0][2]) == int(want.max())
     s, c = oracle.end_start(qq, codes[off[20]:off[21]], matrices["PAM250"], -10, -1)
     assert tuple(int(x) for x in hits[0][3:]) == c
+
+
+@pytest.mark.gpu
+def test_cli_many_queries(tmp_path, oracle, matrices):
+    """Many-to-many front end: SWGPU_ALL_QUERIES=1 aligns every record of the query file; by
+    default only the first one is used, like the reference (src/alignment_cmdline.c:369-380)."""
+    from swgpu import synth
+    g = synth.rng(15)
+    lens = g.integers(1, 300, size=53)
+    off = np.zeros(54, np.int64); np.cumsum(lens, out=off[1:])
+    codes = synth.residues(g, off[-1])
+    qlens = [80, 1, 300, 33, 150]
+    qoff = np.zeros(len(qlens) + 1, np.int64); np.cumsum(qlens, out=qoff[1:])
+    qcodes = synth.residues(g, qoff[-1])
+    codes[off[7]:off[7] + 60] = qcodes[qoff[2] + 20: qoff[2] + 80]
+    synth.to_fasta(str(tmp_path / "db.fa"), codes, off)
+    synth.to_fasta(str(tmp_path / "q.fa"), qcodes, qoff, prefix="query")
+    tab = matrices["BLOSUM62"]
+    args = ["--substitution_matrix", os.path.join(SCORING, "BLOSUM62.txt"), "--gapopen", "-10", "--gapextend", "-1",
+            "--files", str(tmp_path / "q.fa"), str(tmp_path / "db.fa")]
+    pat = r"Entry\s+#(\d+):\s*score:\s*([+-]?\d+)"
+    r = run(args)
+    assert r.returncode == 0, r.stderr
+    got = [int(m.group(2)) for m in re.finditer(pat, r.stdout)]
+    assert got == list(oracle.search32(qcodes[:80], codes, off, tab, -10, -1))
+    r = run(args, env={**os.environ, "SWGPU_ALL_QUERIES": "1"})
+    assert r.returncode == 0, r.stderr
+    got = [int(m.group(2)) for m in re.finditer(pat, r.stdout)]
+    want = []
+    for k in range(len(qlens)):
+        want += list(oracle.search32(qcodes[qoff[k]:qoff[k + 1]], codes, off, tab, -10, -1))
+    assert got == want and r.stdout.count("Total Entries: 53") == 1
+    r = run(args, env={**os.environ, "SWGPU_ALL_QUERIES": "1", "SWGPU_TOPK": "2"})
+    assert r.returncode == 0, r.stderr
+    blocks = r.stdout.split("Query #")[1:]
+    assert len(blocks) == len(qlens)
+    top = re.findall(r"Hit #0: entry (\d+) score (\d+)", blocks[2])
+    s2 = oracle.search32(qcodes[qoff[2]:qoff[3]], codes, off, tab, -10, -1)
+    assert top and int(top[0][0]) == 7 and int(top[0][1]) == int(s2.max())
