@@ -1,0 +1,266 @@
+// sw_k3x.cuh -- K3X: 32-bit intra-sequence WAVEFRONT kernel, one WARP per stripe of query rows, any number of
+// warps (from any CTA) on the same target at the same time.
+//
+// Same recurrence as k3_intra (sw_kernels.cuh; reference src/alignment.c:117-176).  A single (query, target)
+// pair is a chain of Lt dependent column steps per stripe of query rows; a 35 213 x 35 213 pair has 276 stripes
+// of 128 rows.  Here every stripe is a work item of its own:
+//   * items = (target, stripe), enumerated target-major / stripe-ascending and pulled from one atomic queue, so
+//     the producer of an item's input row always has a smaller item index: it is already running (or done) when
+//     the consumer starts -- no deadlock whatever the number of resident warps;
+//   * stripe s-1 -> stripe s: the bottom row (H, V per column) goes through a full-length row in global memory
+//     (two rows per target slot, ping-pong by stripe parity) and a 64-bit progress word per (slot, stripe),
+//     published with st.release.gpu every 32 columns and polled with ld.acquire.gpu by lane 0 of the consumer;
+//   * target slots (rows, progress words, per-stripe results) are reused round-robin: a warp starts an item of
+//     target t only after target t - K3X_SLOTS has completed (done counter per slot);
+//   * the last warp to finish a target reduces the per-stripe results and writes the target's output.
+// Inside a warp the scheme is k3_intra's: lane l owns 4 rows, the target streams through the lanes by
+// __shfl_up_sync.  The cell update is the latency-optimised form: with Hx = max(0, t, G) (independent of V)
+//   V' = max(V + ge, Hx + oe)     -- the only row-to-row dependency, one VIADDMNMX
+//   H  = max(Hx, V)                 G' = max(G + ge, H + oe)
+// Used for (a) the coordinate passes of top-k (TRACK: first maximum in the reference's scan order)
+// and (b) 32-bit rescoring of long targets.
+#pragma once
+#include "sw_kernels.cuh"
+
+namespace swk {
+
+constexpr int K3X_WARPS = 8;
+constexpr int K3X_R = 4;                       // rows per lane: 128 rows per stripe
+constexpr int K3X_SLOTS = 128;                 // targets in flight
+constexpr unsigned K3X_SPIN_LIMIT = 1u << 24;  // polls (with back-off) before the error flag is raised instead of hanging
+
+struct K3XParams {
+  const int*      sidx_list;    // targets (sorted positions); nullptr -> target index itself
+  int             n_targets;
+  const unsigned* work_count;   // if non-null the target count is read from the device
+  unsigned*       counter;      // item queue
+  const int8_t*   plain;
+  const int64_t*  plain_off;
+  const int8_t*   query;
+  int             lq;
+  int             nstripes_max; // ceil(lq / 128)
+  const int8_t*   table;
+  int             oe, ge;
+  int2*           rows;         // [K3X_SLOTS][2][row_stride] (H, V)
+  long long       row_stride;
+  unsigned long long* progress; // [K3X_SLOTS][nstripes_max]: (target + 1) << 32 | columns published
+  unsigned*       done;         // [K3X_SLOTS]: items finished on this slot since the launch
+  int4*           partial;      // [K3X_SLOTS][nstripes_max]: (best, j, i, -) per stripe
+  const int64_t*  order;        // !TRACK: scores_file[order[sidx]] = score
+  int32_t*        scores_file;
+  int4*           coords;       // TRACK: per target (q_start, q_end, t_start, t_end)
+  int*            best_out;     // TRACK phase 0: score found
+  int             phase;        // TRACK: 0 = forward (end cell), 1 = reversed prefixes (start cell)
+  unsigned*       error_flag;
+  int             min_len;      // !TRACK: targets shorter than this are left to k3_intra
+};
+
+__device__ __forceinline__ unsigned long long ld_acquire_u64(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_u64(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.release.gpu.global.u64 [%0], %1;" :: "l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned ld_acquire_u32(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+__device__ __forceinline__ bool k3x_better(int s, int j, int i, int bs, int bj, int bi) {
+  return s > bs || (s == bs && (j < bj || (j == bj && i < bi)));
+}
+
+template <bool TRACK>
+__global__ void __launch_bounds__(K3X_WARPS * 32) k3x(const K3XParams P) {
+  constexpr int R3 = K3X_R;
+  __shared__ int8_t tab[32 * 32];
+  __shared__ unsigned pl_all[K3X_WARPS][32 * 32];          // [code][lane], one int8x4 word (R3 == 4)
+  static_assert(R3 == 4, "profile layout assumes 4 rows per lane");
+  for (int i = threadIdx.x; i < 1024; i += blockDim.x) tab[i] = P.table[i];
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  unsigned* pl = pl_all[warp];
+  const unsigned pl_addr = (unsigned)__cvta_generic_to_shared(pl) + lane * 4;
+  const int n_targets = P.work_count ? (int)*P.work_count : P.n_targets;
+  const long long n_items = (long long)n_targets * P.nstripes_max;
+  const int oe = P.oe, ge = P.ge;
+
+  for (;;) {
+    long long item = 0;
+    if (lane == 0) item = (long long)atomicAdd(P.counter, 1u);
+    item = __shfl_sync(0xffffffffu, item, 0);
+    if (item >= n_items) break;
+    const int t = (int)(item / P.nstripes_max), stripe = (int)(item - (long long)t * P.nstripes_max);
+    const int slot = t % K3X_SLOTS, gen = t / K3X_SLOTS;
+    // the slot's previous user (target t - K3X_SLOTS) must be completely done before its rows are touched
+    if (gen > 0) {
+      if (lane == 0) {
+        const unsigned need = (unsigned)gen * (unsigned)P.nstripes_max;
+        unsigned spins = 0;
+        while (ld_acquire_u32(P.done + slot) < need) {
+          __nanosleep(200);
+          if (++spins > K3X_SPIN_LIMIT) { atomicExch(P.error_flag, 1u); break; }
+        }
+      }
+      __syncwarp();
+    }
+    const int sidx = P.sidx_list ? P.sidx_list[t] : t;
+    const int8_t* tp = P.plain + P.plain_off[sidx];
+    int lt = (int)(P.plain_off[sidx + 1] - P.plain_off[sidx]);
+    int lq = P.lq;
+    const int8_t* qp = P.query;
+    int qstep = 1, tstep = 1;
+    bool skip = false;
+    if (TRACK && P.phase == 1) {
+      const int4 c = P.coords[t];
+      if (c.y < 0) skip = true;
+      else { lq = c.y + 1; lt = c.w + 1; qp += c.y; tp += c.w; qstep = -1; tstep = -1; }
+    }
+    if (!TRACK && lt < P.min_len) skip = true;             // this target belongs to k3_intra
+    const int nstripes = skip ? 0 : (lq + 32 * R3 - 1) / (32 * R3);
+    int best = 0, bj = 0x7fffffff, bi = 0x7fffffff;
+
+    if (stripe < nstripes) {
+      const int row0 = stripe * 32 * R3 + lane * R3;
+      __syncwarp();
+      for (int c = 0; c < 32; ++c) {
+        unsigned word = 0;
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+          const int i = row0 + b;
+          const int s = (c == 0 || i >= lq) ? -128 : (int)tab[(qp[(long)i * qstep] & 31) * 32 + c];
+          word |= (unsigned)(s & 0xff) << (8 * b);
+        }
+        pl[c * 32 + lane] = word;
+      }
+      __syncwarp();
+      const bool has_in = stripe > 0, has_out = stripe + 1 < nstripes;
+      const int2* row_in = P.rows + ((size_t)slot * 2 + ((stripe + 1) & 1)) * (size_t)P.row_stride;
+      int2* row_out = P.rows + ((size_t)slot * 2 + (stripe & 1)) * (size_t)P.row_stride;
+      const unsigned long long* prog_in = P.progress + (size_t)slot * P.nstripes_max + (stripe - 1);
+      unsigned long long* prog_out = P.progress + (size_t)slot * P.nstripes_max + stripe;
+      const unsigned long long tag = (unsigned long long)(t + 1) << 32;
+      int H[R3], G[R3];
+#pragma unroll
+      for (int k = 0; k < R3; ++k) { H[k] = 0; G[k] = 0; }
+      int diag_in = 0, out_h = 0, out_v = 0, my_code = 0;
+      int pre_code = 0, pre_h = 0, pre_v = 0;
+      const int nsteps = lt + 31;
+      for (int s = 0; s < nsteps; ++s) {
+        if ((s & 31) == 0) {
+          const int j = s + lane;
+          if (has_in && s < lt) {                          // wait until the stripe above has published columns [s, s+32)
+            if (lane == 0) {
+              const unsigned long long need = tag | (unsigned long long)min(s + 32, lt);
+              unsigned spins = 0;
+              for (;;) {
+                const unsigned long long v = ld_acquire_u64(prog_in);
+                if ((v >> 32) == (tag >> 32) && v >= need) break;
+                __nanosleep(100);
+                if (++spins > K3X_SPIN_LIMIT) { atomicExch(P.error_flag, 1u); break; }
+              }
+            }
+            __syncwarp();
+          }
+          int2 b = make_int2(0, 0);
+          if (has_in && j < lt) b = __ldcg(&row_in[j]);
+          pre_h = b.x; pre_v = b.y;
+          pre_code = (j < lt) ? (int)tp[(long)j * tstep] : 0;
+        }
+        int code = __shfl_up_sync(0xffffffffu, my_code, 1);
+        int h_up = __shfl_up_sync(0xffffffffu, out_h, 1);
+        int v_in = __shfl_up_sync(0xffffffffu, out_v, 1);
+        const int c0 = __shfl_sync(0xffffffffu, pre_code, s & 31);
+        const int h0 = __shfl_sync(0xffffffffu, pre_h, s & 31);
+        const int v0 = __shfl_sync(0xffffffffu, pre_v, s & 31);
+        if (lane == 0) { code = c0; h_up = h0; v_in = v0; }
+        my_code = code;
+        const int j = s - lane;
+        if (j >= 0 && j < lt) {
+          int d = diag_in;
+          diag_in = h_up;
+          int V = v_in;
+          const unsigned w0 = lds32(pl_addr + (code & 31) * 128);
+          int colbest = 0, colk = 0;
+#pragma unroll
+          for (int k = 0; k < R3; ++k) {
+            const int tt = (int)add_byte(w0, 1u << (8 * k), (unsigned)d);
+            const int hx = __vimax3_s32_relu(tt, G[k], 0);   // max(0, t, G): independent of V
+            const int h = max(hx, V);
+            V = __viaddmax_s32(V, ge, hx + oe);              // the row-to-row chain: one op
+            d = H[k];
+            H[k] = h;
+            G[k] = __viaddmax_s32(G[k], ge, h + oe);
+            if (TRACK) { if (h > colbest) { colbest = h; colk = k; } } else best = max(best, h);
+          }
+          if (TRACK && k3x_better(colbest, j, row0 + colk, best, bj, bi)) { best = colbest; bj = j; bi = row0 + colk; }
+          out_h = H[R3 - 1];
+          out_v = V;
+          if (lane == 31 && has_out) {
+            row_out[j] = make_int2(out_h, out_v);
+            if ((j & 31) == 31 || j == lt - 1) st_release_u64(prog_out, tag | (unsigned long long)(j + 1));
+          }
+        }
+      }
+      // this stripe's candidate
+      if (TRACK) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+          const int s2 = __shfl_xor_sync(0xffffffffu, best, o);
+          const int j2 = __shfl_xor_sync(0xffffffffu, bj, o);
+          const int i2 = __shfl_xor_sync(0xffffffffu, bi, o);
+          if (k3x_better(s2, j2, i2, best, bj, bi)) { best = s2; bj = j2; bi = i2; }
+        }
+      } else {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) best = max(best, __shfl_xor_sync(0xffffffffu, best, o));
+      }
+      if (lane == 0) P.partial[(size_t)slot * P.nstripes_max + stripe] = make_int4(best, bj, bi, 0);
+    }
+
+    // completion: the last item of this target reduces the per-stripe candidates and writes the result
+    unsigned fin = 0;
+    if (lane == 0) {
+      __threadfence();
+      fin = atomicAdd(P.done + slot, 1u) + 1u;
+      __threadfence();
+    }
+    fin = __shfl_sync(0xffffffffu, fin, 0);
+    if (fin == (unsigned)(gen + 1) * (unsigned)P.nstripes_max) {
+      int rb = 0, rj = 0x7fffffff, ri = 0x7fffffff;
+      for (int s = lane; s < nstripes; s += 32) {
+        const int4 c = __ldcg(&P.partial[(size_t)slot * P.nstripes_max + s]);
+        if (TRACK ? k3x_better(c.x, c.y, c.z, rb, rj, ri) : c.x > rb) { rb = c.x; rj = c.y; ri = c.z; }
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        const int s2 = __shfl_xor_sync(0xffffffffu, rb, o);
+        const int j2 = __shfl_xor_sync(0xffffffffu, rj, o);
+        const int i2 = __shfl_xor_sync(0xffffffffu, ri, o);
+        if (TRACK ? k3x_better(s2, j2, i2, rb, rj, ri) : s2 > rb) { rb = s2; rj = j2; ri = i2; }
+      }
+      if (lane == 0) {
+        if (TRACK) {
+          int4 c = P.coords[t];
+          if (P.phase == 0) {
+            if (rb > 0) { c.y = ri; c.w = rj; } else { c = make_int4(-1, -1, -1, -1); }
+            P.best_out[t] = rb;
+            P.coords[t] = c;
+          } else if (!skip) {
+            c.x = c.y - ri; c.z = c.w - rj;
+            P.coords[t] = c;
+          } else {
+            P.coords[t] = make_int4(-1, -1, -1, -1);
+          }
+        } else if (!skip) {
+          P.scores_file[P.order[sidx]] = rb;
+        }
+      }
+    }
+  }
+}
+
+}  // namespace swk

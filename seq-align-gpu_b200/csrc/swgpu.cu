@@ -1,11 +1,11 @@
 // swgpu.cu -- implementation of the C-ABI in include/swgpu.h: database handle, search orchestration.
 // Thin extern "C" layer over the kernels in sw_k1s.cuh (16-bit systolic), sw_kernels.cuh (K3, 32-bit)
-// and sw_k3w.cuh (32-bit wavefront).  No CPU fallback: every compute entry point needs a CUDA device.
+// and sw_k3x.cuh (32-bit wavefront).  No CPU fallback: every compute entry point needs a CUDA device.
 #include "swgpu_internal.h"
 #include "db_pack.h"
 #include "sw_kernels.cuh"
 #include "sw_k1s.cuh"
-#include "sw_k3w.cuh"
+#include "sw_k3x.cuh"
 
 #include <cstdio>
 #include <cstdlib>
@@ -18,7 +18,7 @@ namespace {
 using swi::fail;
 
 constexpr int kDefaultStreamCols = 1536;
-constexpr int kWaveMinLen = 4096;          // 32-bit path: targets at least this long take k3w (one CTA each)
+constexpr int kWaveMinLen = 4096;          // 32-bit path: targets at least this long take k3x (one warp per 128-row stripe)
 
 template <typename T>
 int dalloc(swgpu_db* db, T** p, size_t count) {
@@ -46,8 +46,31 @@ int slot_prepare(swgpu_db* db, swgpu_slot& S) {
   if ((r = dalloc(db, &S.d_table, 1024))) return r;
   if ((r = dalloc(db, &S.d_bnd_s, (size_t)db->k1s_grid * swk::K1S_WARPS * (size_t)db->bnd_s_stride))) return r;
   if ((r = dalloc(db, &S.d_bnd3, (size_t)db->k3_grid * swk::K3_WARPS * (size_t)db->bnd3_stride))) return r;
+  if (db->max_len >= kWaveMinLen) {
+    if ((r = dalloc(db, &S.d_x_rows, (size_t)swk::K3X_SLOTS * 2 * (size_t)db->x_row_stride))) return r;
+    if ((r = dalloc(db, &S.d_x_done, (size_t)swk::K3X_SLOTS))) return r;
+  }
   CU(cudaMallocHost((void**)&S.h_ctr, 16 * sizeof(unsigned)));
   S.ready = true;
+  return SWGPU_OK;
+}
+
+// k3x slot state for a query of lq rows: progress words and per-stripe partial results grow with the query;
+// progress and done counters are zeroed on `stream` before every k3x launch.
+int k3x_prepare(swgpu_db* db, swgpu_slot& S, int lq, cudaStream_t stream) {
+  const int ns = std::max(1, (lq + 127) / 128);
+  if (!S.d_x_rows) {                                       // top-k coordinates on a database without long targets
+    CU(cudaMalloc((void**)&S.d_x_rows, sizeof(int2) * (size_t)swk::K3X_SLOTS * 2 * (size_t)db->x_row_stride));
+    CU(cudaMalloc((void**)&S.d_x_done, sizeof(unsigned) * swk::K3X_SLOTS));
+  }
+  if (ns > S.x_stripes_cap) {
+    cudaFree(S.d_x_progress); cudaFree(S.d_x_partial); S.d_x_progress = nullptr; S.d_x_partial = nullptr;
+    S.x_stripes_cap = ns + ns / 2;
+    CU(cudaMalloc((void**)&S.d_x_progress, sizeof(unsigned long long) * (size_t)swk::K3X_SLOTS * S.x_stripes_cap));
+    CU(cudaMalloc((void**)&S.d_x_partial, sizeof(int4) * (size_t)swk::K3X_SLOTS * S.x_stripes_cap));
+  }
+  CU(cudaMemsetAsync(S.d_x_progress, 0, sizeof(unsigned long long) * (size_t)swk::K3X_SLOTS * ns, stream));
+  CU(cudaMemsetAsync(S.d_x_done, 0, sizeof(unsigned) * swk::K3X_SLOTS, stream));
   return SWGPU_OK;
 }
 
@@ -55,7 +78,8 @@ void slot_release(swgpu_slot& S) {
   cudaFree(S.d_scores); cudaFree(S.d_raw_s); cudaFree(S.d_rescore_list); cudaFree(S.d_counters);
   cudaFree(S.d_bnd_s); cudaFree(S.d_bnd3); cudaFree(S.d_query); cudaFree(S.d_table);
   cudaFree(S.d_sprof); cudaFree(S.d_sprof2);
-  cudaFree(S.d_keys); cudaFree(S.d_hit_sidx); cudaFree(S.d_sel); cudaFree(S.d_coords); cudaFree(S.d_bnd_loc);
+  cudaFree(S.d_keys); cudaFree(S.d_hit_sidx); cudaFree(S.d_sel); cudaFree(S.d_coords);
+  cudaFree(S.d_x_rows); cudaFree(S.d_x_progress); cudaFree(S.d_x_partial); cudaFree(S.d_x_done);
   cudaFreeHost(S.h_ctr); cudaFreeHost(S.h_keys); cudaFreeHost(S.h_coords); cudaFreeHost(S.h_best); cudaFreeHost(S.h_sidx);
   cudaFreeHost(S.h_scores);
   for (auto& e : S.ev) if (e) cudaEventDestroy(e);
@@ -137,7 +161,8 @@ int swgpu_db_create(swgpu_db_t** out, int device, const int8_t* codes, const int
     db->k1s_grid = db->sm_count * 3;                          // upper bound of resident k1s CTAs (carry-row slots)
     db->bnd_s_stride = ((long long)std::max<int32_t>(pk.max_stream_cols, 64) + 63) & ~63ll;
     db->k3_grid = db->sm_count * 4;
-    db->bnd3_stride = std::max<int32_t>(pk.max_len, 32);
+    db->bnd3_stride = std::max<int32_t>(std::min<int32_t>(pk.max_len, kWaveMinLen), 32);   // k3_intra takes targets < kWaveMinLen
+    db->x_row_stride = ((long long)std::max<int32_t>(pk.max_len, 32) + 31) & ~31ll;
     return swi::slot_prepare(db, db->slots[0]);
   };
   const int rc = body();
@@ -235,7 +260,7 @@ int launch_k1s(swgpu_db* db, const swk::K1SParams& P, int g, int R, bool multi, 
 }
 
 // 32-bit scoring of a work list (device-side count) or of all targets (list == nullptr): k3_intra (one warp per
-// target) takes the targets shorter than kWaveMinLen, the wavefront kernel k3w (one CTA per target) the rest.
+// target) takes the targets shorter than kWaveMinLen, the wavefront kernel k3x (one warp per stripe, many warps per target) the rest.
 int launch_32bit(swgpu_db* db, swgpu_slot& S, cudaStream_t stream, const int* list, const unsigned* list_count,
                  int n_all, int lq, int oe, int ge, unsigned* q_k3, unsigned* q_k3w, int* launches) {
   swk::K3Params P; memset(&P, 0, sizeof(P));
@@ -248,12 +273,16 @@ int launch_32bit(swgpu_db* db, swgpu_slot& S, cudaStream_t stream, const int* li
   CU(cudaGetLastError());
   ++*launches;
   if (db->max_len >= kWaveMinLen) {
-    swk::K3WParams W; memset(&W, 0, sizeof(W));
-    W.sidx_list = list; W.work_count = list_count; W.n_work = n_all; W.counter = q_k3w;
-    W.plain = db->d_plain; W.plain_off = db->d_plain_off; W.query = S.d_query; W.lq = lq; W.table = S.d_table;
-    W.oe = oe; W.ge = ge; W.bnd = S.d_bnd3; W.bnd_stride = db->bnd3_stride;
+    int r = swi::k3x_prepare(db, S, lq, stream);
+    if (r) return r;
+    swk::K3XParams W; memset(&W, 0, sizeof(W));
+    W.sidx_list = list; W.work_count = list_count; W.n_targets = n_all; W.counter = q_k3w;
+    W.plain = db->d_plain; W.plain_off = db->d_plain_off; W.query = S.d_query; W.lq = lq; W.nstripes_max = (lq + 127) / 128;
+    W.table = S.d_table; W.oe = oe; W.ge = ge; W.rows = S.d_x_rows; W.row_stride = db->x_row_stride;
+    W.progress = S.d_x_progress; W.done = S.d_x_done; W.partial = S.d_x_partial;
     W.order = db->d_order; W.scores_file = S.d_scores; W.error_flag = S.d_counters + 6; W.min_len = kWaveMinLen;
-    swk::k3w<false><<<db->sm_count * 2, swk::K3W_WARPS * 32, 0, stream>>>(W);   // after k3 on the same stream: d_bnd3 is shared
+    if ((double)db->n * W.nstripes_max >= 4.0e9) return fail(SWGPU_EINVAL, "query too long for this database size (32-bit path)");
+    swk::k3x<false><<<db->sm_count * 2, swk::K3X_WARPS * 32, 0, stream>>>(W);
     CU(cudaGetLastError());
     ++*launches;
   }

@@ -32,11 +32,15 @@ struct swgpu_slot {
   int32_t*  d_scores = nullptr;        // file order
   unsigned* d_raw_s = nullptr;         // n_pairs * 32 packed running maxima
   int*      d_rescore_list = nullptr;  // up to n
-  unsigned* d_counters = nullptr;      // [0] k1s queue, [1] k1s long queue, [2] rescore count, [3] k3 queue, [4] k3w queue,
-                                       // [5] k3 all-targets queue, [6] k3w error flag, [7] top-k error flag,
+  unsigned* d_counters = nullptr;      // [0] k1s queue, [1] k1s long queue, [2] rescore count, [3] k3 queue, [4] k3x queue,
+                                       // [5] k3 all-targets queue, [6] k3x error flag, [7] top-k error flag,
                                        // [8] top-k coordinate queue phase 0, [9] phase 1
   uint2*    d_bnd_s = nullptr;         // k1s multi-stripe carry rows
-  int2*     d_bnd3 = nullptr;          // k3 / k3w carry rows
+  int2*     d_bnd3 = nullptr;          // k3_intra carry rows
+  // k3x (32-bit wavefront over many warps): target slots
+  int2*     d_x_rows = nullptr;        // [K3X_SLOTS][2][x_row_stride]
+  unsigned long long* d_x_progress = nullptr;  int4* d_x_partial = nullptr;  int x_stripes_cap = 0;   // [K3X_SLOTS][x_stripes_cap]
+  unsigned* d_x_done = nullptr;        // [K3X_SLOTS]
   int8_t*   d_query = nullptr;  int64_t query_cap = 0;
   int8_t*   d_table = nullptr;
   unsigned* d_sprof = nullptr;  size_t sprof_cap = 0;     // k1s profile (bulk plan)
@@ -48,7 +52,6 @@ struct swgpu_slot {
   // top-k scratch
   unsigned long long* d_keys = nullptr;  int* d_hit_sidx = nullptr;  void* d_sel = nullptr;  int topk_cap = 0;
   int4* d_coords = nullptr;
-  int2* d_bnd_loc = nullptr;  long long bnd_loc_stride = 0;  int loc_slots = 0;
   // pinned host staging for asynchronous read-back
   unsigned* h_ctr = nullptr;                                // 16 counters
   unsigned long long* h_keys = nullptr;  int4* h_coords = nullptr;  int* h_best = nullptr;  int* h_sidx = nullptr;  int h_cap = 0;
@@ -79,7 +82,8 @@ struct swgpu_db {
   int32_t   max_stream_cols = 0;
   int64_t   n_long_streams = 0, n_long_pairs = 0;   // leading long streams get their own low-latency launch
   long long bnd_s_stride = 0;  int k1s_grid = 0;    // k1s multi-stripe carry rows: per warp slot
-  long long bnd3_stride = 0;   int k3_grid = 0;     // k3 / k3w carry rows
+  long long bnd3_stride = 0;   int k3_grid = 0;     // k3_intra carry rows
+  long long x_row_stride = 0;                       // k3x rows: longest target, rounded up
   int64_t   device_bytes = 0;
   std::vector<int64_t> h_len_sorted_prefix;         // plain_off on the host (statistics)
   swgpu_slot slots[SWGPU_SLOTS];
@@ -90,6 +94,7 @@ struct swgpu_db {
 namespace swi {
 int slot_prepare(swgpu_db* db, swgpu_slot& S);                        // allocate a slot's buffers on first use
 void slot_release(swgpu_slot& S);
+int k3x_prepare(swgpu_db* db, swgpu_slot& S, int lq, cudaStream_t stream);   // (re)allocate + zero the k3x slot state
 int enqueue_topk(swgpu_db* db, swgpu_slot& S, int k);                  // no host synchronisation
 int collect_topk(swgpu_db* db, swgpu_slot& S, swgpu_hit_t* hits, int* n_hits);   // after S.ev[11] has completed
 }  // namespace swi

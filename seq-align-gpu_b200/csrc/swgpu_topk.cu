@@ -11,12 +11,12 @@
 // Selection: an 8-pass MSB-first radix select (8 bits per pass) over 64-bit keys
 // (score << 32 | ~entry) finds the k-th largest key exactly; a compaction pass collects the k keys
 // >= it together with their position in the length-sorted database; a rank sort orders them.
-// Coordinates: the wavefront kernel k3w<TRACK> (sw_k3w.cuh) runs the 32-bit recurrence twice per hit,
-// tracking the first maximum; hits are pulled from a device-side queue, so nothing returns to the host
+// Coordinates: the wavefront kernel k3x<TRACK> (sw_k3x.cuh) runs the 32-bit recurrence twice per hit,
+// tracking the first maximum; (hit, stripe) items are pulled from a device-side queue, so nothing returns to the host
 // between selection and coordinates (swgpu_search_many keeps several queries in flight).
 #include "swgpu_internal.h"
 #include "sw_kernels.cuh"
-#include "sw_k3w.cuh"
+#include "sw_k3x.cuh"
 
 #include <algorithm>
 #include <cstring>
@@ -95,8 +95,8 @@ __global__ void topk_ranksort(const unsigned long long* __restrict__ keys, const
   if (i < k) { keys_out[rank] = mine; sidx_out[rank] = sidx[i]; }
 }
 
-// Coordinates: the wavefront kernel k3w<TRACK> (sw_k3w.cuh), one CTA per hit; phase 0 = forward (end cell),
-// phase 1 = the reversed prefixes (start cell).
+// Coordinates: the wavefront kernel k3x<TRACK> (sw_k3x.cuh), one warp per 128-row stripe of a hit; phase 0 =
+// forward (end cell), phase 1 = the reversed prefixes (start cell).
 
 }  // namespace swk
 
@@ -134,14 +134,6 @@ int enqueue_topk(swgpu_db* db, swgpu_slot& S, int k) {
     S.h_cap = cap;
   }
   if (!S.d_sel) CU(cudaMalloc(&S.d_sel, sizeof(swk::SelState)));
-  // coordinate passes: a queue of k hits over at most 2 CTAs per SM, one linear-space carry row per CTA
-  const int loc_ctas = std::min(k, db->sm_count * 2);
-  const long long need = std::max<long long>(db->max_len, 32);
-  if (need > S.bnd_loc_stride || loc_ctas > S.loc_slots) {
-    cudaFree(S.d_bnd_loc); S.d_bnd_loc = nullptr;
-    S.bnd_loc_stride = std::max(need, S.bnd_loc_stride); S.loc_slots = std::max(loc_ctas, S.loc_slots);
-    CU(cudaMalloc((void**)&S.d_bnd_loc, sizeof(int2) * (size_t)S.bnd_loc_stride * (size_t)S.loc_slots));
-  }
   swk::SelState* sel = (swk::SelState*)S.d_sel;
   const int cap = S.topk_cap;
   unsigned long long* keys_u = S.d_keys; unsigned long long* keys_s = S.d_keys + cap;
@@ -164,13 +156,19 @@ int enqueue_topk(swgpu_db* db, swgpu_slot& S, int k) {
   CU(cudaGetLastError());
   if (S.lq > 0) {
     // coordinates of the k hits against the query of this slot's search (hits with score 0 come out as -1)
-    swk::K3WParams P; memset(&P, 0, sizeof(P));
-    P.sidx_list = sidx_s; P.n_work = k; P.plain = db->d_plain; P.plain_off = db->d_plain_off; P.query = S.d_query;
-    P.lq = (int)S.lq; P.table = S.d_table; P.oe = S.oe; P.ge = S.ge; P.bnd = S.d_bnd_loc;
-    P.bnd_stride = S.bnd_loc_stride; P.coords = S.d_coords; P.best_out = best_out;
+    swk::K3XParams P; memset(&P, 0, sizeof(P));
+    P.sidx_list = sidx_s; P.n_targets = k; P.plain = db->d_plain; P.plain_off = db->d_plain_off; P.query = S.d_query;
+    P.lq = (int)S.lq; P.nstripes_max = ((int)S.lq + 127) / 128; P.table = S.d_table; P.oe = S.oe; P.ge = S.ge;
+    P.rows = S.d_x_rows; P.row_stride = db->x_row_stride; P.coords = S.d_coords; P.best_out = best_out;
     P.error_flag = S.d_counters + 7;
-    P.phase = 0; P.counter = S.d_counters + 8; swk::k3w<true><<<loc_ctas, swk::K3W_WARPS * 32, 0, st>>>(P);
-    P.phase = 1; P.counter = S.d_counters + 9; swk::k3w<true><<<loc_ctas, swk::K3W_WARPS * 32, 0, st>>>(P);
+    const int grid = std::min(db->sm_count * 2, std::max(1, (k * P.nstripes_max + swk::K3X_WARPS - 1) / swk::K3X_WARPS));
+    for (int phase = 0; phase < 2; ++phase) {
+      int r = swi::k3x_prepare(db, S, (int)S.lq, st);
+      if (r) return r;
+      P.progress = S.d_x_progress; P.done = S.d_x_done; P.partial = S.d_x_partial; P.rows = S.d_x_rows;
+      P.phase = phase; P.counter = S.d_counters + 8 + phase;
+      swk::k3x<true><<<grid, swk::K3X_WARPS * 32, 0, st>>>(P);
+    }
     launches += 2;
     CU(cudaGetLastError());
     CU(cudaMemcpyAsync(S.h_coords, S.d_coords, sizeof(int4) * k, cudaMemcpyDeviceToHost, st));

@@ -7,6 +7,8 @@
 #include "alignment_cmdline.h"
 #include "alignment_scoring_load.h"
 #include "fasta_reader.h"
+#include "db_loader.h"
+#include <time.h>
 #include "swgpu.h"
 
 #include <limits.h>
@@ -182,37 +184,6 @@ cmdline_t *cmdline_new(int argc, char **argv, scoring_t *scoring, enum SeqAlignC
 /* ---------------------------------------------------------------- one-to-many driver */
 
 typedef struct {
-    char **names, **seqs;          /* per entry, file order (seqs kept only for --printseq callers) */
-    int8_t *codes; int64_t *off;   /* encoded residues back to back + prefix offsets */
-    size_t n, cap; size_t res_cap;
-} dbmem_t;
-
-static void db_push(dbmem_t *d, const swfa_record_t *rec)
-{
-    if (d->n == d->cap) {
-        d->cap = d->cap ? d->cap * 2 : 4096;
-        d->names = (char **)realloc(d->names, d->cap * sizeof(char *));
-        d->seqs = (char **)realloc(d->seqs, d->cap * sizeof(char *));
-        d->off = (int64_t *)realloc(d->off, (d->cap + 1) * sizeof(int64_t));
-        if (!d->names || !d->seqs || !d->off) { fprintf(stderr, "Error: out of memory\n"); exit(EXIT_FAILURE); }
-        if (d->n == 0) d->off[0] = 0;
-    }
-    const size_t base = (size_t)d->off[d->n];
-    if (base + rec->seq_len > d->res_cap) {
-        d->res_cap = d->res_cap ? d->res_cap * 2 : (1u << 20);
-        while (base + rec->seq_len > d->res_cap) d->res_cap *= 2;
-        d->codes = (int8_t *)realloc(d->codes, d->res_cap);
-        if (!d->codes) { fprintf(stderr, "Error: out of memory\n"); exit(EXIT_FAILURE); }
-    }
-    /* same encoding, same failure mode (stdout message + exit(1)) as src/alignment_cmdline.c:444-446 */
-    for (size_t i = 0; i < rec->seq_len; i++) d->codes[base + i] = letters_to_index(rec->seq[i]);
-    d->names[d->n] = strdup(rec->name);
-    d->seqs[d->n] = strdup(rec->seq);
-    d->off[d->n + 1] = (int64_t)(base + rec->seq_len);
-    d->n++;
-}
-
-typedef struct {
     int device;
     const int8_t *codes; const int64_t *off; int64_t n;   /* this shard */
     const int64_t *entry;                                 /* shard index -> file index (NULL = identity) */
@@ -272,9 +243,9 @@ static int i64_cmp(const void *a, const void *b)
  * shard gets the same length mix and (to within one target per round) the same residue count.
  * Inside a shard the targets stay in ascending file order: the engine's tie-break (score desc,
  * shard-local entry asc) is then the global rule and the merged top-k does not depend on the GPU count. */
-static void make_shards(const dbmem_t *d, int g, int8_t **codes, int64_t **off, int64_t **entry, int64_t *cnt)
+static void make_shards(const swdb_t *d, int g, int8_t **codes, int64_t **off, int64_t **entry, int64_t *cnt)
 {
-    const size_t n = d->n;
+    const size_t n = (size_t)d->n;
     int64_t maxlen = 0;
     for (size_t t = 0; t < n; t++) { const int64_t l = d->off[t + 1] - d->off[t]; if (l > maxlen) maxlen = l; }
     int64_t *bucket = (int64_t *)calloc((size_t)maxlen + 2, sizeof(int64_t));
@@ -307,9 +278,6 @@ void align_from_query_and_db(const char *query_path, const char *db_path, scorin
 {
     swfa_reader_t *qf = swfa_open(query_path, use_zlib);
     if (!qf) { fprintf(stderr, "Error: couldn't open query file %s\n", query_path); fflush(stderr); return; }
-    swfa_reader_t *df = swfa_open(db_path, use_zlib);
-    if (!df) { fprintf(stderr, "Error: couldn't open database file %s\n", db_path); fflush(stderr); swfa_close(qf); return; }
-
     /* The reference aligns the FIRST record of the query file only (src/alignment_cmdline.c:369-380).  With
      * SWGPU_ALL_QUERIES=1 every record is a query (many-to-many): the listing below is repeated per query. */
     const char *eq = getenv("SWGPU_ALL_QUERIES");
@@ -325,7 +293,7 @@ void align_from_query_and_db(const char *query_path, const char *db_path, scorin
     }
     if (nq == 0) {
         fprintf(stderr, "Error: Query file %s is empty or invalid\n", query_path); fflush(stderr);
-        swfa_close(qf); swfa_close(df); free(qrec); return;
+        swfa_close(qf); free(qrec); return;
     }
     /* query encode; letters whose diagonal the matrix never defined become 'X' (src/alignment_cmdline.c:388-396) */
     int8_t **qi = (int8_t **)calloc((size_t)nq, sizeof(*qi));
@@ -339,11 +307,32 @@ void align_from_query_and_db(const char *query_path, const char *db_path, scorin
         }
     }
 
-    swfa_record_t rec = {0};
-    dbmem_t d; memset(&d, 0, sizeof(d));
-    int st;
-    while ((st = swfa_read(df, &rec)) > 0) db_push(&d, &rec);
-    if (d.n == 0) { d.off = (int64_t *)calloc(1, sizeof(int64_t)); }
+    /* ---- database: packed cache if asked for and valid, else parse (parallel for plain FASTA files) ---- */
+    swdb_t d; memset(&d, 0, sizeof(d));
+    const char *ec = getenv("SWGPU_DB_CACHE"), *ev = getenv("SWGPU_VERBOSE"), *et = getenv("SWGPU_PARSE_THREADS");
+    char cache_path[4096] = "";
+    if (ec && *ec && strcmp(ec, "0") != 0 && strcmp(db_path, "-") != 0) {
+        if (!strcmp(ec, "1")) snprintf(cache_path, sizeof(cache_path), "%s.swdb", db_path);
+        else snprintf(cache_path, sizeof(cache_path), "%s", ec);
+    }
+    struct timespec t0, t1;
+    clock_gettime(CLOCK_MONOTONIC, &t0);
+    int loaded = 0;
+    if (cache_path[0] && swdb_cache_open(cache_path, db_path, &d) == 0) loaded = 1;
+    if (!loaded) {
+        if (swdb_load(db_path, use_zlib, et ? atoi(et) : 0, &d) != 0) {
+            fprintf(stderr, "Error: couldn't open database file %s\n", db_path); fflush(stderr);
+            for (int k = 0; k < nq; k++) { free(qi[k]); swfa_record_free(&qrec[k]); }
+            free(qi); free(qlen); free(qrec); swfa_close(qf); return;
+        }
+        if (cache_path[0] && swdb_cache_write(cache_path, &d, db_path) != 0)
+            fprintf(stderr, "Warning: could not write database cache %s\n", cache_path);
+    }
+    clock_gettime(CLOCK_MONOTONIC, &t1);
+    if (ev && atoi(ev) > 0)
+        fprintf(stderr, "swgpu: database %s: %lld entries, %lld residues, loaded in %.3f s (%s)\n", db_path, (long long)d.n,
+                (long long)d.n_residues, (double)(t1.tv_sec - t0.tv_sec) + 1e-9 * (double)(t1.tv_nsec - t0.tv_nsec),
+                d.from_cache ? "packed cache, mmap" : d.threads_used > 1 ? "parallel FASTA parser" : "streaming reader");
 
     /* ---- GPU search (the reference's timed `omp parallel for`, src/alignment_cmdline.c:503-509) ---- */
     int ndev = swgpu_device_count();
@@ -352,7 +341,7 @@ void align_from_query_and_db(const char *query_path, const char *db_path, scorin
     const char *eg = getenv("SWGPU_GPUS");
     if (eg && atoi(eg) > 0) g = atoi(eg);
     if (g > ndev) g = ndev;
-    if ((size_t)g > d.n) g = d.n ? (int)d.n : 1;
+    if ((int64_t)g > d.n) g = d.n ? (int)d.n : 1;
     int topk = 0;
     const char *ek = getenv("SWGPU_TOPK");
     if (ek && atoi(ek) > 0) topk = atoi(ek);
@@ -360,7 +349,7 @@ void align_from_query_and_db(const char *query_path, const char *db_path, scorin
     int32_t **scores = NULL;
     if (!topk) {
         scores = (int32_t **)calloc((size_t)nq, sizeof(*scores));
-        for (int k = 0; k < nq; k++) scores[k] = (int32_t *)calloc(d.n ? d.n : 1, sizeof(int32_t));
+        for (int k = 0; k < nq; k++) scores[k] = (int32_t *)calloc(d.n ? (size_t)d.n : 1, sizeof(int32_t));
     }
     shard_job_t *jobs = (shard_job_t *)calloc((size_t)g, sizeof(shard_job_t));
     int8_t **sc_codes = (int8_t **)calloc((size_t)g, sizeof(*sc_codes));
@@ -398,27 +387,39 @@ void align_from_query_and_db(const char *query_path, const char *db_path, scorin
             if (all_queries) printf("Query #%d: %s\n", k, qrec[k].name);
             for (int h = 0; h < m; h++)
                 printf("Hit #%d: entry %lld score %d query [%d..%d] target [%d..%d] %s\n", h, (long long)all[h].entry, all[h].score,
-                       all[h].q_start, all[h].q_end, all[h].t_start, all[h].t_end, d.names[all[h].entry]);
+                       all[h].q_start, all[h].q_end, all[h].t_start, all[h].t_end, d.names + d.name_off[all[h].entry]);
             free(all);
         } else {
             aligner_t view; aligner_init(&view);
             score_t s16[16]; int32_t s32[16];
             view.scoring = scoring; view.seq_a_indexes = qi[k]; view.seq_a_str = qrec[k].seq; view.seq_a_fasta = qrec[k].name;
             view.score_width = qrec[k].seq_len + 1; view.max_scores = s16; view.max_scores32 = s32;
-            for (size_t first = 0; first < d.n; first += 16) {
-                const size_t lanes = d.n - first < 16 ? d.n - first : 16;
+            char *b_str[16], *b_name[16];
+            char *strbuf = NULL; size_t strcap = 0;
+            view.seq_b_str_batch = b_str; view.seq_b_fasta_batch = b_name;
+            for (size_t first = 0; first < (size_t)d.n; first += 16) {
+                const size_t lanes = (size_t)d.n - first < 16 ? (size_t)d.n - first : 16;
                 view.vector_size = lanes;
-                view.seq_b_str_batch = d.seqs + first; view.seq_b_fasta_batch = d.names + first;
-                size_t maxlen = 0;
+                /* the 16 sequences as NUL-terminated strings: the file's own text, or (database from a packed
+                 * cache) the residue codes decoded to upper-case letters */
+                const size_t need = (size_t)(d.off[first + lanes] - d.off[first]) + lanes;
+                if (need > strcap) { strcap = need * 2; strbuf = (char *)realloc(strbuf, strcap); if (!strbuf) { fprintf(stderr, "Error: out of memory\n"); exit(EXIT_FAILURE); } }
+                size_t maxlen = 0, w = 0;
                 for (size_t l = 0; l < lanes; l++) {
                     s32[l] = scores[k][first + l];
                     s16[l] = (score_t)(s32[l] > 32767 ? 32767 : s32[l]);
                     const size_t len = (size_t)(d.off[first + l + 1] - d.off[first + l]);
                     if (len > maxlen) maxlen = len;
+                    b_name[l] = d.names + d.name_off[first + l];
+                    b_str[l] = strbuf + w;
+                    if (d.text) memcpy(strbuf + w, d.text + d.off[first + l], len);
+                    else for (size_t i = 0; i < len; i++) strbuf[w + i] = index_to_letters(d.codes[d.off[first + l] + (int64_t)i]);
+                    strbuf[w + len] = 0; w += len + 1;
                 }
                 view.score_height = maxlen + 1;
                 print_alignment(&view, first);
             }
+            free(strbuf);
         }
     }
     printf("Total Time: %f\n", total_ms * 1e-3);
@@ -428,9 +429,8 @@ void align_from_query_and_db(const char *query_path, const char *db_path, scorin
     free(jobs); free(sc_codes); free(sc_off); free(sc_entry); free(sc_cnt); free(th);
     for (int k = 0; k < nq && scores; k++) free(scores[k]);
     free(scores);
-    for (size_t i = 0; i < d.n; i++) { free(d.names[i]); free(d.seqs[i]); }
-    free(d.names); free(d.seqs); free(d.codes); free(d.off);
+    swdb_free(&d);
     for (int k = 0; k < nq; k++) { free(qi[k]); swfa_record_free(&qrec[k]); }
-    free(qi); free(qlen); free(qrec); swfa_record_free(&rec);
-    swfa_close(qf); swfa_close(df);
+    free(qi); free(qlen); free(qrec);
+    swfa_close(qf);
 }

@@ -56,6 +56,25 @@ def config2(n=570000, total=205_000_000):
     return make_db(43, n, lo=2, hi=35213, total=total, force_max=35213)
 
 
+def config4(n=1024, lq=35213):
+    """C4: seed 45; titin-length query; 16 targets at 35 213 aa, 48 log-uniform in [8 k, 35 k],
+    the rest C1-distributed; target 1 is a 90 %-identity copy of the query (overflows 16 bits).
+    Returns (query, codes, offsets), targets sorted longest first."""
+    g = rng(45)
+    q = make_query(4500, lq)
+    lens = [35213] * 16 + [int(x) for x in np.exp(g.uniform(np.log(8000), np.log(35000), size=48))]
+    lens += [int(x) for x in lognormal_lengths(g, max(n - len(lens), 0))]
+    lens = sorted(lens[:n], reverse=True)
+    parts = [residues(g, L) for L in lens]
+    cp = q[:lens[1]].copy()
+    mut = g.random(cp.size) < 0.10
+    cp[mut] = residues(g, int(mut.sum()))
+    parts[1] = cp
+    off = np.zeros(len(parts) + 1, dtype=np.int64)
+    np.cumsum([p.size for p in parts], out=off[1:])
+    return q, np.concatenate(parts), off
+
+
 def to_fasta(path, codes, off, prefix="sp"):
     letters = np.frombuffer(b"?ABCDEFGHIJKLMNOPQRSTUVWXYZ????*", dtype=np.uint8)
     txt = letters[np.asarray(codes, dtype=np.int64)]

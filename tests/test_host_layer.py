@@ -215,3 +215,24 @@ def test_cli_many_queries(tmp_path, oracle, matrices):
     top = re.findall(r"Hit #0: entry (\d+) score (\d+)", blocks[2])
     s2 = oracle.search32(qcodes[qoff[2]:qoff[3]], codes, off, tab, -10, -1)
     assert top and int(top[0][0]) == 7 and int(top[0][1]) == int(s2.max())
+
+
+@pytest.mark.gpu
+def test_cli_packed_db_cache(tmp_path):
+    """SWGPU_DB_CACHE=1 writes <db>.swdb on the first run and mmaps it on the next; the listing
+    (with --printseq, so names and sequences come from the cache too) is byte-identical."""
+    g, q, d = _write_cli_inputs(tmp_path)
+    args = ["--substitution_matrix", os.path.join(SCORING, "BLOSUM62.txt"), "--gapopen", "-10", "--gapextend", "-1",
+            "--printfasta", "--printseq", "--files", str(q), str(d)]
+    env = {**os.environ, "SWGPU_DB_CACHE": "1", "SWGPU_VERBOSE": "1"}
+    r0 = run(args)
+    r1 = run(args, env=env)
+    assert r1.returncode == 0 and os.path.exists(str(d) + ".swdb") and "packed cache" not in r1.stderr
+    r2 = run(args, env=env)
+    assert r2.returncode == 0 and "packed cache, mmap" in r2.stderr
+    assert _normalise(r0.stdout, tmp_path) == _normalise(r1.stdout, tmp_path) == _normalise(r2.stdout, tmp_path)
+    # touching the source invalidates the cache
+    os.utime(d, ns=(0, 10**18))
+    r3 = run(args, env=env)
+    assert r3.returncode == 0 and "packed cache" not in r3.stderr
+    assert _normalise(r3.stdout, tmp_path) == _normalise(r0.stdout, tmp_path)
