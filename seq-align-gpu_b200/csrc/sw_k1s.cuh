@@ -77,7 +77,28 @@ struct K1SParams {
   unsigned*       counter;      // work queue head
   unsigned*       raw;          // [pair][g] packed biased running maxima
   unsigned        BB, BBM, OE2, GE2;   // bias, bias - oe, packed oe, packed ge (u16 x 2)
+  // multi-pass only -- X items: the first n_x_streams streams (the long ones) are cut into (8 streams, ONE stripe)
+  // items, so the stripes of a titin-length pair run at the same time on different CTAs instead of one after the
+  // other on one warp.  Stripe p-1 -> stripe p through x_bnd (two full-length rows per stream, ping-pong by stripe
+  // parity) and one progress word per (stream, stripe): st.release.gpu by the producer's lane 31 every 32 columns,
+  // ld.acquire.gpu by the consumer's lane 0.  Items are ordered (group, stripe) ascending, so a producer always has
+  // the smaller item index and is already running when its consumer starts.
+  int             n_x_streams;
+  uint2*          x_bnd;        // per X stream two rows of its own length, at 2 * stream_off[stream]
+  unsigned*       x_progress;   // [n_x_streams][npass], zeroed per search
+  unsigned*       x_raw;        // [pair][npass][32] running maxima of the X pairs (one slot set per stripe)
+  unsigned*       error_flag;
 };
+
+__device__ __forceinline__ unsigned k1s_ld_acquire(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void k1s_st_release(unsigned* p, unsigned v) {
+  asm volatile("st.release.gpu.global.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
+}
+constexpr unsigned K1S_SPIN_LIMIT = 1u << 24;
 
 constexpr int K1S_WARPS = 8;
 #ifndef K1S_R3CTA
@@ -128,16 +149,23 @@ __global__ void __launch_bounds__(K1S_WARPS * 32, (R <= K1S_R3CTA ? 3 : 2)) k1s(
       __syncthreads();
       if (threadIdx.x == 0) cta_item = atomicAdd(P.counter, 1u);
       __syncthreads();
-      if ((long)cta_item * K1S_WARPS >= P.n_items) break;
-      item = (int)cta_item * K1S_WARPS + warp;
+      if (cta_item >= (unsigned)P.n_items) break;
+      item = (int)cta_item;
     } else {
       item = 0;
       if (lane == 0) item = (int)atomicAdd(P.counter, 1u);
       item = __shfl_sync(0xffffffffu, item, 0);
       if (item >= P.n_items) break;
     }
-    const long st_local = (long)item * per_warp + grp;
-    const bool valid = item < P.n_items && st_local < P.n_streams;
+    // MULTI: P.n_items counts CTA items: first the X items (8 long streams x one stripe), then 8 streams x all stripes
+    const int n_x_items = MULTI ? ((P.n_x_streams + K1S_WARPS - 1) / K1S_WARPS) * P.npass : 0;
+    const bool x_item = MULTI && item < n_x_items;
+    const int x_pass = x_item ? item % P.npass : 0;
+    long st_local;
+    if (!MULTI) st_local = (long)item * per_warp + grp;
+    else if (x_item) st_local = (long)(item / P.npass) * K1S_WARPS + warp;
+    else st_local = (long)P.n_x_streams + (long)(item - n_x_items) * K1S_WARPS + warp;
+    const bool valid = x_item ? st_local < P.n_x_streams : st_local < P.n_streams;
     const long st = P.stream_begin + st_local;
     const int ncols = valid ? P.stream_ncols[st] : 0;
     const long pair0 = valid ? (long)P.stream_pair0[st] : 0;
@@ -147,9 +175,35 @@ __global__ void __launch_bounds__(K1S_WARPS * 32, (R <= K1S_R3CTA ? 3 : 2)) k1s(
     for (int o = 16; o > 0; o >>= 1) maxcols = max(maxcols, __shfl_xor_sync(0xffffffffu, maxcols, o));
     const int nsteps = maxcols > 0 ? maxcols + g - 1 : 0;
 
-    for (int pass = 0; pass < (MULTI ? P.npass : 1); ++pass) {
+    const int pass_begin = x_item ? x_pass : 0, pass_end = x_item ? x_pass + 1 : (MULTI ? P.npass : 1);
+    for (int pass = pass_begin; pass < pass_end; ++pass) {
       if (MULTI) { __syncthreads(); load_profile(pass); __syncthreads(); }
       const bool first = (pass == 0), last = !MULTI || (pass == P.npass - 1);
+      // hand-over rows: own per-warp row (all stripes on this warp), or the stream's ping-pong rows (X item)
+      const uint2* bnd_in = bnd;
+      uint2* bnd_out = bnd;
+      const unsigned* prog_in = nullptr;
+      unsigned* prog_out = nullptr;
+      if (MULTI && x_item && valid) {
+        uint2* rows = P.x_bnd + 2 * (size_t)P.stream_off[st];      // two rows of ncols columns per stream
+        bnd_in = rows + (size_t)((pass + 1) & 1) * (size_t)ncols;
+        bnd_out = rows + (size_t)(pass & 1) * (size_t)ncols;
+        if (!first) prog_in = P.x_progress + (size_t)st_local * P.npass + (pass - 1);
+        if (!last) prog_out = P.x_progress + (size_t)st_local * P.npass + pass;
+      }
+      auto wait_cols = [&](int upto) {                 // X item: the stripe above has published columns [0, upto)
+        if (prog_in) {
+          if (lane == 0) {
+            const unsigned need = (unsigned)min(upto, ncols);
+            unsigned spins = 0;
+            while (k1s_ld_acquire(prog_in) < need) {
+              __nanosleep(100);
+              if (++spins > K1S_SPIN_LIMIT) { atomicExch(P.error_flag, 1u); break; }
+            }
+          }
+          __syncwarp();
+        }
+      };
       unsigned H[R], G[R];
 #pragma unroll
       for (int k = 0; k < R; ++k) { H[k] = BB; G[k] = BBM; }
@@ -159,13 +213,20 @@ __global__ void __launch_bounds__(K1S_WARPS * 32, (R <= K1S_R3CTA ? 3 : 2)) k1s(
       for (int i = lane; i < 128; i += 32) ring[i] = 0;
       unsigned pre = (lane_g < ncols) ? (unsigned)cp[lane_g] : 0u;
       uint2 pre_b = make_uint2(BB, BBM);
-      if (MULTI && !first && lane < ncols) pre_b = bnd[lane];
+      if (MULTI && !first) {
+        wait_cols(32);
+        if (lane < ncols) pre_b = __ldcg(&bnd_in[lane]);
+      }
       __syncwarp();
 
       auto flush = [&]() {
         if (pair_idx >= pair0) {
-          unsigned* slot = P.raw + ((size_t)pair_idx << g_log2) + lane_g;
-          *slot = (MULTI && !first) ? __vmaxu2(*slot, best) : best;
+          if (MULTI && x_item) {
+            P.x_raw[(((size_t)pair_idx * P.npass + pass) << 5) + lane] = best;
+          } else {
+            unsigned* slot = P.raw + ((size_t)pair_idx << g_log2) + lane_g;
+            *slot = (MULTI && !first) ? __vmaxu2(*slot, best) : best;
+          }
         }
       };
 
@@ -178,7 +239,11 @@ __global__ void __launch_bounds__(K1S_WARPS * 32, (R <= K1S_R3CTA ? 3 : 2)) k1s(
           if (MULTI) {
             ring2[lane] = pre_b;
             pre_b = make_uint2(BB, BBM);
-            if (!first && c < ncols) pre_b = bnd[c];
+            if (prog_out && lane == 31 && s > 31) k1s_st_release(prog_out, (unsigned)min(s - 31, ncols));
+            if (!first) {
+              wait_cols(s + 2 * g);
+              if (c < ncols) pre_b = __ldcg(&bnd_in[c]);
+            }
           }
           __syncwarp();
         }
@@ -229,27 +294,27 @@ __global__ void __launch_bounds__(K1S_WARPS * 32, (R <= K1S_R3CTA ? 3 : 2)) k1s(
         out_v = V;
         if (MULTI && !last && lane == 31) {
           const int j = s - 31;
-          if (j >= 0 && j < ncols) bnd[j] = make_uint2(out_h, out_v);
+          if (j >= 0 && j < ncols) bnd_out[j] = make_uint2(out_h, out_v);
         }
       }
+      if (MULTI && prog_out && lane == 31) k1s_st_release(prog_out, (unsigned)ncols);
       flush();
     }
   }
 }
 
-// reduce the g per-lane maxima of every pair, un-bias, detect saturation, scatter to file order.
+// reduce the `slots` per-lane (and, for X pairs, per-stripe) maxima of every pair, un-bias, detect saturation, scatter to file order.
 // A pair whose either half reached `limit` sends BOTH members to the 32-bit list (a carry out of the low
 // half would have corrupted the high half); long_thr > 0 also sends every target longer than that.
-static __global__ void k1s_finalize(const unsigned* __restrict__ raw, long pair_begin, long n_pairs, int g_log2, long n_sorted,
+static __global__ void k1s_finalize(const unsigned* __restrict__ raw, long pair_begin, long n_pairs, int slots, long n_sorted,
                                     unsigned B, unsigned limit, const int64_t* __restrict__ order,
                                     const int64_t* __restrict__ plain_off, int long_thr,
                                     int32_t* __restrict__ scores_file, int* __restrict__ rescore_list,
                                     unsigned* __restrict__ rescore_count) {
-  const int g = 1 << g_log2;
   for (long p = pair_begin + blockIdx.x * (long)blockDim.x + threadIdx.x; p < n_pairs; p += (long)gridDim.x * blockDim.x) {
-    const unsigned* r = raw + ((size_t)p << g_log2);
+    const unsigned* r = raw + (size_t)p * (size_t)slots;
     unsigned m = r[0];
-    for (int i = 1; i < g; ++i) m = __vmaxu2(m, r[i]);
+    for (int i = 1; i < slots; ++i) m = __vmaxu2(m, r[i]);
     const unsigned lo = m & 0xffffu, hi = m >> 16;
     const bool sat = (lo >= limit) || (hi >= limit);
 #pragma unroll

@@ -79,6 +79,7 @@ void slot_release(swgpu_slot& S) {
   cudaFree(S.d_bnd_s); cudaFree(S.d_bnd3); cudaFree(S.d_query); cudaFree(S.d_table);
   cudaFree(S.d_sprof); cudaFree(S.d_sprof2);
   cudaFree(S.d_keys); cudaFree(S.d_hit_sidx); cudaFree(S.d_sel); cudaFree(S.d_coords);
+  cudaFree(S.d_xs_bnd); cudaFree(S.d_xs_progress); cudaFree(S.d_xs_raw);
   cudaFree(S.d_x_rows); cudaFree(S.d_x_progress); cudaFree(S.d_x_partial); cudaFree(S.d_x_done);
   cudaFreeHost(S.h_ctr); cudaFreeHost(S.h_keys); cudaFreeHost(S.h_coords); cudaFreeHost(S.h_best); cudaFreeHost(S.h_sidx);
   cudaFreeHost(S.h_scores);
@@ -136,6 +137,8 @@ int swgpu_db_create(swgpu_db_t** out, int device, const int8_t* codes, const int
   db->h_len_sorted_prefix.assign(pk.plain_off, pk.plain_off + pk.n_targets + 1);
   db->n_pairs = pk.n_pairs; db->n_streams = pk.n_streams; db->max_stream_cols = pk.max_stream_cols;
   db->n_long_streams = pk.n_long_streams; db->n_long_pairs = pk.n_long_pairs;
+  db->scols_len = (int64_t)pk.scols_len;
+  db->long_cols = pk.n_long_streams < pk.n_streams ? pk.stream_off[pk.n_long_streams] : (int64_t)pk.scols_len;
 
   auto body = [&]() -> int {
     cudaDeviceProp prop;
@@ -381,7 +384,7 @@ int enqueue_search(swgpu_db* db, swgpu_slot& S, const int8_t* query, int64_t lq,
       PL.active_warps = 1;                                     // one long stream per CTA: spread them over the SMs
       if ((r = launch_k1s(db, PL, 32, plan_long.R, false, sa, (int)std::min<int64_t>(nls, db->k1s_grid)))) return r;
       swk::k1s_finalize<<<std::max(1, (int)((nlp + 255) / 256)), 256, 0, sa>>>(
-          S.d_raw_s, 0, (long)nlp, 5, (long)db->n, B, limit, db->d_order, db->d_plain_off, db->long_threshold,
+          S.d_raw_s, 0, (long)nlp, 32, (long)db->n, B, limit, db->d_order, db->d_plain_off, db->long_threshold,
           S.d_scores, S.d_rescore_list, S.d_counters + 2);
       CU(cudaGetLastError()); st.kernel_launches += 3;
     }
@@ -390,19 +393,57 @@ int enqueue_search(swgpu_db* db, swgpu_slot& S, const int8_t* query, int64_t lq,
         S.d_query, (int)lq, S.d_table, plan.R, plan.g, plan.npass, S.d_sprof);
     CU(cudaGetLastError()); st.kernel_launches++;
     const int per_warp = 32 / plan.g;
+    const bool multi = plan.npass > 1;
+    // X items: with several stripes the long streams are cut into (8 streams, one stripe) items that run
+    // concurrently on different CTAs (sw_k1s.cuh); their pairs get one set of maxima slots per stripe.
+    // A database too small to fill the GPU with (8 streams x all stripes) items goes through X items entirely.
+    const int k1s_ctas = db->sm_count * (plan.R <= K1S_R3CTA ? 3 : 2);
+    const bool all_x = multi && (db->n_streams - db->n_long_streams + swk::K1S_WARPS - 1) / swk::K1S_WARPS < 2 * (int64_t)k1s_ctas;
+    const int64_t nxs = !multi ? 0 : all_x ? db->n_streams : db->n_long_streams;
+    const int64_t nxp = !multi ? 0 : all_x ? db->n_pairs : db->n_long_pairs;
+    if (nxs > 0) {
+      const int64_t need_bnd = 2 * (all_x ? db->scols_len : db->long_cols) + 64;
+      if (need_bnd > S.xs_bnd_cap) {
+        cudaFree(S.d_xs_bnd); S.d_xs_bnd = nullptr; S.xs_bnd_cap = need_bnd;
+        CU(cudaMalloc((void**)&S.d_xs_bnd, sizeof(uint2) * (size_t)need_bnd));
+      }
+      if (nxs * plan.npass > S.xs_prog_cap) {
+        cudaFree(S.d_xs_progress); S.d_xs_progress = nullptr; S.xs_prog_cap = nxs * plan.npass * 3 / 2;
+        CU(cudaMalloc((void**)&S.d_xs_progress, sizeof(unsigned) * (size_t)S.xs_prog_cap));
+      }
+      if (nxp * plan.npass > S.xs_raw_cap) {
+        cudaFree(S.d_xs_raw); S.d_xs_raw = nullptr; S.xs_raw_cap = nxp * plan.npass * 3 / 2;
+        CU(cudaMalloc((void**)&S.d_xs_raw, sizeof(unsigned) * 32 * (size_t)S.xs_raw_cap));
+      }
+      CU(cudaMemsetAsync(S.d_xs_progress, 0, sizeof(unsigned) * (size_t)nxs * plan.npass, sm));
+    }
     PS.stream_begin = (int)nls; PS.n_streams = (int)(db->n_streams - nls);
-    PS.n_items = (PS.n_streams + per_warp - 1) / per_warp;
+    PS.n_items = multi ? (int)((nxs + swk::K1S_WARPS - 1) / swk::K1S_WARPS) * plan.npass +
+                             (int)((PS.n_streams - nxs + swk::K1S_WARPS - 1) / swk::K1S_WARPS)
+                       : (PS.n_streams + per_warp - 1) / per_warp;
     PS.prof = S.d_sprof; PS.npass = plan.npass; PS.g = plan.g; PS.g_log2 = plan.g_log2;
     PS.counter = S.d_counters + 0; PS.active_warps = swk::K1S_WARPS;
+    PS.n_x_streams = (int)nxs; PS.x_bnd = S.d_xs_bnd; PS.x_progress = S.d_xs_progress; PS.x_raw = S.d_xs_raw;
+    PS.error_flag = S.d_counters + 6;
     // the bulk's [pair][g] maxima start after the long launch's [pair][32] region
     PS.raw = S.d_raw_s + (size_t)nlp * 32 - ((size_t)nlp << plan.g_log2);
     if (PS.n_streams > 0) {
-      int ctas = plan.R <= K1S_R3CTA ? 3 : 2;
-      if (const char* ev = getenv("SWGPU_K1S_CTAS")) ctas = std::max(1, std::min(ctas, atoi(ev)));   // A/B knob (profiling)
-      if ((r = launch_k1s(db, PS, plan.g, plan.R, plan.npass > 1, sm, db->sm_count * ctas))) return r;
-      swk::k1s_finalize<<<(int)std::min<int64_t>((db->n_pairs - nlp + 255) / 256, 4096), 256, 0, sm>>>(
-          PS.raw, (long)nlp, (long)db->n_pairs, plan.g_log2, (long)db->n, B, limit, db->d_order, db->d_plain_off,
-          db->long_threshold, S.d_scores, S.d_rescore_list, S.d_counters + 2);
+      // all_x: the stripes of a stream form a pipeline that runs at the pace of its slowest stage; one CTA per SM keeps
+      // every stage at the same (higher) step rate (C4: 56 -> 21 ms)
+      int ctas = all_x ? 1 : plan.R <= K1S_R3CTA ? 3 : 2;
+      if (const char* ev = getenv("SWGPU_K1S_CTAS")) ctas = std::max(1, std::min(3, atoi(ev)));      // A/B knob (profiling)
+      if ((r = launch_k1s(db, PS, plan.g, plan.R, multi, sm, db->sm_count * ctas))) return r;
+      if (nxp > 0) {
+        swk::k1s_finalize<<<std::max(1, (int)((nxp + 255) / 256)), 256, 0, sm>>>(
+            S.d_xs_raw, 0, (long)nxp, 32 * plan.npass, (long)db->n, B, limit, db->d_order, db->d_plain_off,
+            db->long_threshold, S.d_scores, S.d_rescore_list, S.d_counters + 2);
+        st.kernel_launches++;
+      }
+      const int64_t pb = nlp + nxp;                            // first pair scored by the bulk items
+      if (db->n_pairs > pb)
+        swk::k1s_finalize<<<(int)std::min<int64_t>((db->n_pairs - pb + 255) / 256, 4096), 256, 0, sm>>>(
+            PS.raw, (long)pb, (long)db->n_pairs, 1 << plan.g_log2, (long)db->n, B, limit, db->d_order, db->d_plain_off,
+            db->long_threshold, S.d_scores, S.d_rescore_list, S.d_counters + 2);
       CU(cudaGetLastError()); st.kernel_launches += 2;
     }
     CU(cudaEventRecord(e[5], sm));

@@ -36,6 +36,9 @@ struct swgpu_slot {
                                        // [5] k3 all-targets queue, [6] k3x error flag, [7] top-k error flag,
                                        // [8] top-k coordinate queue phase 0, [9] phase 1
   uint2*    d_bnd_s = nullptr;         // k1s multi-stripe carry rows
+  // k1s X items (long streams, one stripe per item): ping-pong rows, progress words, per-stripe maxima
+  uint2*    d_xs_bnd = nullptr;  int64_t xs_bnd_cap = 0;       // two rows per X stream (2 * its columns)
+  unsigned* d_xs_progress = nullptr;  unsigned* d_xs_raw = nullptr;  int64_t xs_prog_cap = 0, xs_raw_cap = 0;
   int2*     d_bnd3 = nullptr;          // k3_intra carry rows
   // k3x (32-bit wavefront over many warps): target slots
   int2*     d_x_rows = nullptr;        // [K3X_SLOTS][2][x_row_stride]
@@ -81,6 +84,7 @@ struct swgpu_db {
   int64_t   n_pairs = 0, n_streams = 0;
   int32_t   max_stream_cols = 0;
   int64_t   n_long_streams = 0, n_long_pairs = 0;   // leading long streams get their own low-latency launch
+  int64_t   long_cols = 0, scols_len = 0;           // stream columns of the long streams / of all streams
   long long bnd_s_stride = 0;  int k1s_grid = 0;    // k1s multi-stripe carry rows: per warp slot
   long long bnd3_stride = 0;   int k3_grid = 0;     // k3_intra carry rows
   long long x_row_stride = 0;                       // k3x rows: longest target, rounded up

@@ -236,3 +236,23 @@ def test_fill_batch16_reference_layout(swgpu_mod, oracle, matrices):
     got = swgpu_mod.fill_batch16(q, batch.reshape(-1), plen, 16, tab, -10, -1)
     want = [oracle.score16_wrap(q, tg[l], plen, tab, -10, -1) for l in range(16)]
     assert list(got) == want
+
+
+def test_config4_full_size(swgpu_mod, oracle, matrices):
+    """C4 at full size: 35 213-aa query x 1 024 targets up to 35 213 aa, 62 G cells.  The scalar
+    oracle needs ~2 s per titin-length target, so it checks a sample; every target is cross-checked between the two
+    independent GPU paths (packed 16-bit K1S with X items + rescoring vs. the 32-bit kernels on everything)."""
+    from swgpu import synth
+    tab = matrices["BLOSUM62"]
+    q, codes, off = synth.config4()
+    db = swgpu_mod.Database(codes, off)
+    got, st = db.search(q, tab, -10, -1)
+    db.close()
+    assert st["passes"] > 1 and st["n_rescored"] >= 1 and got[1] > 65535
+    for i in (0, 1, 15, 40, 63, 64, 500, 1023):
+        assert got[i] == oracle.score32(q, codes[off[i]:off[i + 1]], tab, -10, -1), i
+    db32 = swgpu_mod.Database(codes, off, long_threshold=1)
+    got32, st32 = db32.search(q, tab, -10, -1)
+    db32.close()
+    assert st32["n_rescored"] == len(off) - 1
+    assert np.array_equal(got, got32)
