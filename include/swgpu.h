@@ -140,6 +140,23 @@ int swgpu_search_many(swgpu_db_t *db, int32_t n_queries, const int8_t *const *qu
                       int32_t k, swgpu_hit_t *hits, int32_t *n_hits,
                       swgpu_stats_t *per_query, swgpu_batch_stats_t *batch);
 
+/*
+ * Alignment paths for reported hits (the caller-visible step after the path; upstream seq-align printed
+ * alignments, the reference fork removed them and keeps only a score, src/alignment.c:133).  For every hit with
+ * coordinates (from swgpu_topk / swgpu_search_many, any hit of THIS database) the affine global alignment of
+ * query[q_start..q_end] and target[t_start..t_end] that starts and ends in a match state and scores hit.score is
+ * recomputed on the GPU with direction bytes and walked back.  Tie-break: a cell prefers the diagonal, then a
+ * gap in the query ('D'), then a gap in the target ('I'); a gap prefers to open rather than extend.
+ * Output: run-length encoded operations in path order, ops[ops_off[k] .. ops_off[k+1]) for hit k, each
+ * `length << 2 | code` with code 0 = 'M' (aligned pair, match or mismatch), 1 = 'I' (query residue against a gap),
+ * 2 = 'D' (target residue against a gap).  Hits with score 0 get an empty path.  ops_off has n_hits + 1 entries.
+ * The query, table and gap scores must be those of the search that produced the hits (checked: the rectangle
+ * must score hit.score).
+ */
+int swgpu_traceback(swgpu_db_t *db, const int8_t *query, int64_t query_len, const int8_t *table,
+                    int gap_open, int gap_extend, const swgpu_hit_t *hits, int32_t n_hits,
+                    uint32_t *ops, int64_t ops_cap, int64_t *ops_off);
+
 /* Statistics of the last search on this handle, with ms_topk / topk_launches of the last swgpu_topk(). */
 int swgpu_db_last_stats(const swgpu_db_t *db, swgpu_stats_t *out);
 

@@ -94,6 +94,39 @@ def end_start(q, t, table, gap_open, gap_extend):
     return s, tuple(int(x) for x in c)
 
 
+def traceback(q, t, table, gap_open, gap_extend):
+    """CIGAR of the forced-corner global alignment of q and t (the sub-sequences of a hit). Returns (cigar, score)."""
+    q, t, _, table = _prep(q, t, [0], table)
+    L = oracle()
+    L.swo_traceback.restype = C.c_long
+    ops = np.zeros(q.size + t.size + 1, dtype=np.uint32)
+    sc = C.c_int32(0)
+    n = L.swo_traceback(_p(q), C.c_long(q.size), _p(t), C.c_long(t.size), _p(table), C.c_int(gap_open), C.c_int(gap_extend),
+                        _p(ops), C.c_long(ops.size), C.byref(sc))
+    if n < 0:
+        raise RuntimeError("oracle traceback failed")
+    return "".join(f"{int(x) >> 2}{'MID'[int(x) & 3]}" for x in ops[:n]), int(sc.value)
+
+
+def cigar_score(cigar, q, t, table, gap_open, gap_extend):
+    """Score of a CIGAR over q and t (both fully consumed): the independent check of a path."""
+    import re
+    table = np.asarray(table).reshape(32, 32)
+    i = j = 0; s = 0
+    for n, op in re.findall(r"(\d+)([MID])", cigar):
+        n = int(n)
+        if op == "M":
+            for k in range(n):
+                s += int(table[q[i + k], t[j + k]])
+            i += n; j += n
+        elif op == "I":
+            s += gap_open + n * gap_extend; i += n
+        else:
+            s += gap_open + n * gap_extend; j += n
+    assert i == len(q) and j == len(t), (i, j, len(q), len(t))
+    return s
+
+
 def search32(q, codes, off, table, gap_open, gap_extend, threads=0):
     """int32 scalar oracle over a whole database (OpenMP). Returns int32[n]."""
     q, codes, off, table = _prep(q, codes, off, table)

@@ -206,6 +206,74 @@ void swo_search32(const int8_t *q, long lq, const int8_t *residues, const int64_
         scores[k] = swo_score32(q, lq, residues + offsets[k], (long)(offsets[k + 1] - offsets[k]), mat, gap_open, gap_extend);
 }
 
+/* Alignment path of a hit (no reference counterpart: PARITY UNPINNED; the rule is the one documented at
+ * include/swgpu.h::swgpu_traceback and this function is its CPU restatement).  Affine GLOBAL alignment of
+ * q[0..m) and t[0..n) forced to start and end in a match state; a cell prefers the diagonal, then a gap in the
+ * query (consumes a target residue, 'D' = code 2), then a gap in the target ('I' = code 1); a gap prefers to
+ * open rather than extend.  Writes run-length encoded operations (length << 2 | code, code 0 = 'M') in path
+ * order into ops[cap]; returns the number of operations (or -1 if cap is too small / out of memory) and the
+ * score of the path in *score. */
+long swo_traceback(const int8_t *q, long m, const int8_t *t, long n, const int8_t *table, int gap_open, int gap_extend,
+                   uint32_t *ops, long cap, int32_t *score)
+{
+    const int32_t NEG = -(1 << 29);
+    const int oe = gap_open + gap_extend, ge = gap_extend;
+    if (m <= 0 || n <= 0) { *score = 0; return 0; }
+    uint8_t *dir = (uint8_t *)malloc((size_t)m * (size_t)n);
+    int32_t *Hrow = (int32_t *)malloc(sizeof(int32_t) * (size_t)(n + 1));    /* H(i-1, .) then H(i, .) */
+    int32_t *Frow = (int32_t *)malloc(sizeof(int32_t) * (size_t)(n + 1));    /* F(i-1, .) then F(i, .) */
+    if (!dir || !Hrow || !Frow) { free(dir); free(Hrow); free(Frow); return -1; }
+    for (long j = 0; j < n; j++) { Hrow[j] = NEG; Frow[j] = NEG; }
+    for (long i = 0; i < m; i++) {
+        int32_t Hl = NEG, El = NEG;                          /* H(i, j-1), E(i, j-1) */
+        int32_t diag = (i == 0) ? 0 : NEG;                   /* H(i-1, j-1): the forced corner */
+        const int8_t *row = table + (q[i] & 31) * 32;
+        for (long j = 0; j < n; j++) {
+            const int32_t up_h = Hrow[j], up_f = Frow[j];
+            const int32_t D = diag > NEG / 2 ? diag + row[t[j] & 31] : NEG;
+            const int32_t e_open = Hl + oe, e_ext = El + ge;
+            const int32_t E = e_open > e_ext ? e_open : e_ext;
+            const int32_t f_open = up_h + oe, f_ext = up_f + ge;
+            const int32_t F = f_open > f_ext ? f_open : f_ext;
+            int32_t H = D; uint8_t code = 0;
+            if (E > H) { H = E; code = 1; }
+            if (F > H) { H = F; code = 2; }
+            if (e_ext > e_open) code |= 4;
+            if (f_ext > f_open) code |= 8;
+            if (H < NEG) H = NEG;
+            dir[(size_t)i * (size_t)n + (size_t)j] = code;
+            diag = up_h;
+            Hl = H; El = E < NEG ? NEG : E;
+            Hrow[j] = H; Frow[j] = F < NEG ? NEG : F;
+        }
+    }
+    *score = Hrow[n - 1];
+    /* walk back, collecting reversed run-length operations */
+    long nops = 0, i = m - 1, j = n - 1; int state = 0;
+    uint32_t cur_op = 3, cur_len = 0;
+    uint32_t *rev = (uint32_t *)malloc(sizeof(uint32_t) * (size_t)(m + n));
+    if (!rev) { free(dir); free(Hrow); free(Frow); return -1; }
+    while (i >= 0 && j >= 0) {
+        const uint8_t c = dir[(size_t)i * (size_t)n + (size_t)j];
+        uint32_t op;
+        if (state == 0) {
+            const int src = c & 3;
+            if (src == 1) { state = 1; continue; }
+            if (src == 2) { state = 2; continue; }
+            op = 0; i--; j--;
+        } else if (state == 1) { op = 2; state = (c & 4) ? 1 : 0; j--; }
+        else { op = 1; state = (c & 8) ? 2 : 0; i--; }
+        if (op == cur_op) cur_len++;
+        else { if (cur_len) rev[nops++] = cur_len << 2 | cur_op; cur_op = op; cur_len = 1; }
+    }
+    if (cur_len) rev[nops++] = cur_len << 2 | cur_op;
+    long ret = nops;
+    if (i != -1 || j != -1 || state != 0 || nops > cap) ret = -1;
+    else for (long x = 0; x < nops; x++) ops[x] = rev[nops - 1 - x];
+    free(rev); free(dir); free(Hrow); free(Frow);
+    return ret;
+}
+
 int swo_max_threads(void)
 {
 #ifdef _OPENMP

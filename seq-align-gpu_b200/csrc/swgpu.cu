@@ -135,6 +135,8 @@ int swgpu_db_create(swgpu_db_t** out, int device, const int8_t* codes, const int
   db->n = pk.n_targets; db->n_residues = pk.n_residues; db->max_len = pk.max_len; db->entry_base = entry_base;
   db->long_threshold = (opts && opts->long_threshold > 0) ? opts->long_threshold : 0;
   db->h_len_sorted_prefix.assign(pk.plain_off, pk.plain_off + pk.n_targets + 1);
+  db->h_inv_order.resize((size_t)pk.n_targets);
+  for (int64_t s = 0; s < pk.n_targets; ++s) db->h_inv_order[(size_t)pk.order[s]] = (int32_t)s;
   db->n_pairs = pk.n_pairs; db->n_streams = pk.n_streams; db->max_stream_cols = pk.max_stream_cols;
   db->n_long_streams = pk.n_long_streams; db->n_long_pairs = pk.n_long_pairs;
   db->scols_len = (int64_t)pk.scols_len;

@@ -89,7 +89,8 @@ struct swgpu_db {
   long long bnd3_stride = 0;   int k3_grid = 0;     // k3_intra carry rows
   long long x_row_stride = 0;                       // k3x rows: longest target, rounded up
   int64_t   device_bytes = 0;
-  std::vector<int64_t> h_len_sorted_prefix;         // plain_off on the host (statistics)
+  std::vector<int64_t> h_len_sorted_prefix;         // plain_off on the host (statistics, traceback)
+  std::vector<int32_t> h_inv_order;                 // file index -> sorted position (traceback)
   swgpu_slot slots[SWGPU_SLOTS];
   cudaEvent_t ev_batch[1] = {};                     // start of the current swgpu_search_many() batch
   swgpu_stats_t last_stats = {};

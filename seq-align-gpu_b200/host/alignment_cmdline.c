@@ -190,8 +190,20 @@ typedef struct {
     int nq; const int8_t *const *queries; const int64_t *qlens; const scoring_t *sc;
     int32_t **scores_file;                                /* [nq] shared outputs, file order (NULL in top-k mode) */
     int topk; swgpu_hit_t *hits; int32_t *n_hits;         /* [nq * topk], [nq] */
+    int want_cigar; char **cigars;                        /* [nq * topk] alignment paths of the hits (SWGPU_CIGAR=1) */
     double ms; int rc; char err[512];
 } shard_job_t;
+
+/* "12M2D30M" from run-length operations (length << 2 | code; 0 M, 1 I, 2 D) */
+static char *cigar_string(const uint32_t *ops, int64_t n)
+{
+    char *out = (char *)malloc((size_t)n * 12 + 1);
+    size_t w = 0;
+    if (!out) return NULL;
+    for (int64_t i = 0; i < n; i++) w += (size_t)sprintf(out + w, "%u%c", ops[i] >> 2, "MID?"[ops[i] & 3]);
+    out[w] = 0;
+    return out;
+}
 
 /* one GPU: pack this shard, then all queries through swgpu_search_many() (up to three in flight) */
 static void *shard_run(void *arg)
@@ -213,6 +225,20 @@ static void *shard_run(void *arg)
             j->ms = bs.ms_total;
             for (int q = 0; q < j->nq && tmp && j->entry; q++)
                 for (int64_t i = 0; i < j->n; i++) j->scores_file[q][j->entry[i]] = tmp[q][i];
+            for (int q = 0; q < j->nq && j->topk > 0 && j->want_cigar && j->rc == SWGPU_OK; q++) {
+                /* paths of this shard's hits, while the hits still carry shard-local entry indices */
+                const swgpu_hit_t *hq = &j->hits[(size_t)q * (size_t)j->topk];
+                int64_t cap = 1;
+                for (int h = 0; h < j->n_hits[q]; h++)
+                    if (hq[h].q_start >= 0) cap += (hq[h].q_end - hq[h].q_start + 1) + (hq[h].t_end - hq[h].t_start + 1);
+                uint32_t *ops = (uint32_t *)malloc(sizeof(uint32_t) * (size_t)cap);
+                int64_t *off = (int64_t *)malloc(sizeof(int64_t) * (size_t)(j->n_hits[q] + 1));
+                j->rc = swgpu_traceback(db, j->queries[q], j->qlens[q], &j->sc->swap_scores[0][0], j->sc->gap_open,
+                                        j->sc->gap_extend, hq, j->n_hits[q], ops, cap, off);
+                for (int h = 0; h < j->n_hits[q] && j->rc == SWGPU_OK; h++)
+                    j->cigars[(size_t)q * (size_t)j->topk + (size_t)h] = cigar_string(ops + off[h], off[h + 1] - off[h]);
+                free(ops); free(off);
+            }
             for (int q = 0; q < j->nq && j->topk > 0 && j->entry; q++)
                 for (int h = 0; h < j->n_hits[q]; h++) {
                     swgpu_hit_t *hit = &j->hits[(size_t)q * (size_t)j->topk + (size_t)h];
@@ -225,6 +251,8 @@ static void *shard_run(void *arg)
     swgpu_db_destroy(db);
     return NULL;
 }
+
+typedef struct { swgpu_hit_t h; const char *cigar; } hitx_t;     /* h first: hit_cmp sorts these too */
 
 static int hit_cmp(const void *a, const void *b)
 {
@@ -345,6 +373,8 @@ void align_from_query_and_db(const char *query_path, const char *db_path, scorin
     int topk = 0;
     const char *ek = getenv("SWGPU_TOPK");
     if (ek && atoi(ek) > 0) topk = atoi(ek);
+    const char *eci = getenv("SWGPU_CIGAR");
+    const int want_cigar = topk > 0 && eci && atoi(eci) > 0;
 
     int32_t **scores = NULL;
     if (!topk) {
@@ -364,6 +394,8 @@ void align_from_query_and_db(const char *query_path, const char *db_path, scorin
         j->topk = topk;
         j->hits = topk ? (swgpu_hit_t *)calloc((size_t)topk * (size_t)nq, sizeof(swgpu_hit_t)) : NULL;
         j->n_hits = topk ? (int32_t *)calloc((size_t)nq, sizeof(int32_t)) : NULL;
+        j->want_cigar = want_cigar;
+        j->cigars = want_cigar ? (char **)calloc((size_t)topk * (size_t)nq, sizeof(char *)) : NULL;
         if (g > 1) { j->codes = sc_codes[s]; j->off = sc_off[s]; j->n = sc_cnt[s]; j->entry = sc_entry[s]; }
         else { j->codes = d.codes; j->off = d.off; j->n = (int64_t)d.n; j->entry = NULL; }
         if (g > 1) pthread_create(&th[s], NULL, shard_run, j); else shard_run(j);
@@ -378,16 +410,24 @@ void align_from_query_and_db(const char *query_path, const char *db_path, scorin
     /* ---- hand-off: the reference's callback over groups of 16 entries in file order (:511-512) ---- */
     for (int k = 0; k < nq; k++) {
         if (topk > 0) {
-            swgpu_hit_t *all = (swgpu_hit_t *)calloc((size_t)topk * (size_t)g, sizeof(swgpu_hit_t));
+            hitx_t *all = (hitx_t *)calloc((size_t)topk * (size_t)g, sizeof(hitx_t));
             int m = 0;
             for (int s = 0; s < g; s++)
-                for (int h = 0; h < jobs[s].n_hits[k]; h++) all[m++] = jobs[s].hits[(size_t)k * (size_t)topk + (size_t)h];
-            qsort(all, (size_t)m, sizeof(swgpu_hit_t), hit_cmp);   /* score desc, entry asc: independent of the GPU count */
+                for (int h = 0; h < jobs[s].n_hits[k]; h++) {
+                    const size_t at = (size_t)k * (size_t)topk + (size_t)h;
+                    all[m].h = jobs[s].hits[at];
+                    all[m].cigar = jobs[s].cigars ? jobs[s].cigars[at] : NULL;
+                    m++;
+                }
+            qsort(all, (size_t)m, sizeof(hitx_t), hit_cmp);        /* score desc, entry asc: independent of the GPU count */
             if (m > topk) m = topk;
             if (all_queries) printf("Query #%d: %s\n", k, qrec[k].name);
-            for (int h = 0; h < m; h++)
-                printf("Hit #%d: entry %lld score %d query [%d..%d] target [%d..%d] %s\n", h, (long long)all[h].entry, all[h].score,
-                       all[h].q_start, all[h].q_end, all[h].t_start, all[h].t_end, d.names + d.name_off[all[h].entry]);
+            for (int h = 0; h < m; h++) {
+                const swgpu_hit_t *x = &all[h].h;
+                printf("Hit #%d: entry %lld score %d query [%d..%d] target [%d..%d] %s\n", h, (long long)x->entry, x->score,
+                       x->q_start, x->q_end, x->t_start, x->t_end, d.names + d.name_off[x->entry]);
+                if (want_cigar) printf("  cigar: %s\n", all[h].cigar ? all[h].cigar : "");
+            }
             free(all);
         } else {
             aligner_t view; aligner_init(&view);
@@ -425,6 +465,10 @@ void align_from_query_and_db(const char *query_path, const char *db_path, scorin
     printf("Total Time: %f\n", total_ms * 1e-3);
     printf("Total Entries: %lu\n", (unsigned long)d.n);
 
+    for (int s = 0; s < g; s++) {
+        for (size_t c = 0; jobs[s].cigars && c < (size_t)topk * (size_t)nq; c++) free(jobs[s].cigars[c]);
+        free(jobs[s].cigars);
+    }
     for (int s = 0; s < g; s++) { free(jobs[s].hits); free(jobs[s].n_hits); free(sc_codes[s]); free(sc_off[s]); free(sc_entry[s]); }
     free(jobs); free(sc_codes); free(sc_off); free(sc_entry); free(sc_cnt); free(th);
     for (int k = 0; k < nq && scores; k++) free(scores[k]);

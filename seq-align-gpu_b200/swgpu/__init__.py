@@ -86,6 +86,9 @@ def lib():
     L.swgpu_search_many.restype = C.c_int
     L.swgpu_search_many.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
                                     C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, P(BatchStats)]
+    L.swgpu_traceback.restype = C.c_int
+    L.swgpu_traceback.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int, C.c_int, P(Hit), C.c_int32,
+                                  C.c_void_p, C.c_int64, C.c_void_p]
     L.swgpu_db_last_stats.restype = C.c_int
     L.swgpu_db_last_stats.argtypes = [C.c_void_p, P(Stats)]
     L.swgpu_fill_batch16.restype = C.c_int
@@ -172,6 +175,28 @@ class Database:
         out_hits = [[dict(score=h.score, q_start=h.q_start, q_end=h.q_end, t_start=h.t_start, t_end=h.t_end,
                           entry=h.entry) for h in hits[q * k: q * k + int(nh[q])]] for q in range(nq)] if k else None
         return scores, out_hits, [per[q].as_dict() for q in range(nq)], bs.as_dict()
+
+    def traceback(self, query, table, gap_open, gap_extend, hits):
+        """swgpu_traceback(): CIGAR strings ('M' aligned pair, 'I' query residue vs gap, 'D' target residue vs gap)
+        for a list of hit dicts as returned by topk() / search_many()."""
+        q, pq = _i8(query)
+        t, pt = _i8(np.asarray(table).reshape(-1))
+        n = len(hits)
+        arr = (Hit * max(n, 1))()
+        cap = 0
+        for i, h in enumerate(hits):
+            arr[i] = Hit(h["score"], h["q_start"], h["q_end"], h["t_start"], h["t_end"], h["entry"])
+            if h["q_start"] >= 0:
+                cap += (h["q_end"] - h["q_start"] + 1) + (h["t_end"] - h["t_start"] + 1)
+        ops = np.zeros(max(cap, 1), dtype=np.uint32)
+        off = np.zeros(n + 1, dtype=np.int64)
+        _check(lib().swgpu_traceback(self._h, pq, q.size, pt, int(gap_open), int(gap_extend), arr, n,
+                                     ops.ctypes.data_as(C.c_void_p), ops.size, off.ctypes.data_as(C.c_void_p)))
+        out = []
+        for i in range(n):
+            o = ops[off[i]:off[i + 1]]
+            out.append("".join(f"{int(x) >> 2}{'MID'[int(x) & 3]}" for x in o))
+        return out
 
     def scores(self):
         s = np.empty(self.n, dtype=np.int32)

@@ -176,6 +176,12 @@ def test_cli_unsorted_db_partial_batch_gzip_and_topk(tmp_path, oracle, matrices)
     assert len(hits) == 3 and int(hits[0][1]) == 20 and int(hits[0][2]) == int(want.max())
     s, c = oracle.end_start(qq, codes[off[20]:off[21]], matrices["PAM250"], -10, -1)
     assert tuple(int(x) for x in hits[0][3:]) == c
+    # SWGPU_CIGAR=1 adds the alignment path of every hit
+    r = run(args, env={**os.environ, "SWGPU_TOPK": "3", "SWGPU_CIGAR": "1"})
+    cigs = re.findall(r"  cigar: (\S*)", r.stdout)
+    t20 = codes[off[20]:off[21]]
+    want_cig, sc = oracle.traceback(qq[c[0]:c[1] + 1], t20[c[2]:c[3] + 1], matrices["PAM250"], -10, -1)
+    assert len(cigs) == 3 and cigs[0] == want_cig and sc == s
 
 
 @pytest.mark.gpu
