@@ -48,7 +48,7 @@ typedef struct {
     double  ms_total;         /* first kernel launch -> last result resident in HBM */
     double  ms_inter;         /* packed 16-bit systolic kernel K1S incl. profile build and finalize */
     double  ms_intra;         /* the separate low-latency K1S launch for long streams (runs concurrently) */
-    double  ms_rescore;       /* 32-bit kernels: rescoring of saturated targets (K3 / K3W) */
+    double  ms_rescore;       /* 32-bit kernels: rescoring of saturated targets (K3 / K3X) */
     double  ms_h2d, ms_d2h;   /* query/table upload, score download (host API only) */
     int64_t cells;            /* sum over targets of Lq * Lt, real residues */
     int64_t cells_inter, cells_intra, cells_rescore;

@@ -12,7 +12,7 @@
 // K1S (sw_k1s.cuh)  inter-sequence, packed 2 x u16, the dominant kernel
 // K3  k3_intra<R3>  32-bit, one warp per target: rescoring of targets whose 16-bit result
 //                   saturated -- the reference's 16-bit / 32-bit split, README.md:11
-// K3W (sw_k3w.cuh)  32-bit wavefront, one CTA per target: long targets, top-k coordinates
+// K3X (sw_k3x.cuh)  32-bit wavefront, one warp per 128-row stripe: long targets, top-k coordinates
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -75,7 +75,7 @@ struct K3Params {
   const int64_t* order;
   int32_t*       scores_file;
   unsigned       one;
-  int            max_len;      // targets longer than this are left to the wavefront kernel k3w (0 = no limit)
+  int            max_len;      // targets longer than this are left to the wavefront kernel k3x (0 = no limit)
 };
 
 constexpr int K3_WARPS = 4;

@@ -267,7 +267,7 @@ int launch_k1s(swgpu_db* db, const swk::K1SParams& P, int g, int R, bool multi, 
 // 32-bit scoring of a work list (device-side count) or of all targets (list == nullptr): k3_intra (one warp per
 // target) takes the targets shorter than kWaveMinLen, the wavefront kernel k3x (one warp per stripe, many warps per target) the rest.
 int launch_32bit(swgpu_db* db, swgpu_slot& S, cudaStream_t stream, const int* list, const unsigned* list_count,
-                 int n_all, int lq, int oe, int ge, unsigned* q_k3, unsigned* q_k3w, int* launches) {
+                 int n_all, int lq, int oe, int ge, unsigned* q_k3, unsigned* q_k3x, int* launches) {
   swk::K3Params P; memset(&P, 0, sizeof(P));
   P.worklist = list; P.work_count = list_count; P.n_work = n_all; P.counter = q_k3;
   P.plain = db->d_plain; P.plain_off = db->d_plain_off; P.query = S.d_query; P.lq = lq; P.table = S.d_table;
@@ -281,7 +281,7 @@ int launch_32bit(swgpu_db* db, swgpu_slot& S, cudaStream_t stream, const int* li
     int r = swi::k3x_prepare(db, S, lq, stream);
     if (r) return r;
     swk::K3XParams W; memset(&W, 0, sizeof(W));
-    W.sidx_list = list; W.work_count = list_count; W.n_targets = n_all; W.counter = q_k3w;
+    W.sidx_list = list; W.work_count = list_count; W.n_targets = n_all; W.counter = q_k3x;
     W.plain = db->d_plain; W.plain_off = db->d_plain_off; W.query = S.d_query; W.lq = lq; W.nstripes_max = (lq + 127) / 128;
     W.table = S.d_table; W.oe = oe; W.ge = ge; W.rows = S.d_x_rows; W.row_stride = db->x_row_stride;
     W.progress = S.d_x_progress; W.done = S.d_x_done; W.partial = S.d_x_partial;

@@ -194,7 +194,7 @@ def test_config4_long_sequences_scaled(swgpu_mod, oracle, matrices):
 
 def test_32bit_kernels_on_everything(swgpu_mod, oracle, matrices):
     """long_threshold=1 sends every target through the 32-bit kernels: k3_intra (< 4096 aa) and the
-    wavefront kernel k3w (>= 4096 aa, several groups of stripes for the 2 700-aa query)."""
+    wavefront kernel k3x (>= 4096 aa, 22 stripes for the 2 700-aa query)."""
     from swgpu import synth
     g = synth.rng(77)
     lens = [9000, 6500, 4096, 4095, 5000] + list(synth.lognormal_lengths(g, 300))
