@@ -358,9 +358,11 @@ void align_from_query_and_db(const char *query_path, const char *db_path, scorin
     }
     clock_gettime(CLOCK_MONOTONIC, &t1);
     if (ev && atoi(ev) > 0)
-        fprintf(stderr, "swgpu: database %s: %lld entries, %lld residues, loaded in %.3f s (%s)\n", db_path, (long long)d.n,
-                (long long)d.n_residues, (double)(t1.tv_sec - t0.tv_sec) + 1e-9 * (double)(t1.tv_nsec - t0.tv_nsec),
-                d.from_cache ? "packed cache, mmap" : d.threads_used > 1 ? "parallel FASTA parser" : "streaming reader");
+        fprintf(stderr, "swgpu: database %s: %lld entries, %lld residues, loaded in %.3f s (%s, %d thread%s)\n", db_path,
+                (long long)d.n, (long long)d.n_residues,
+                (double)(t1.tv_sec - t0.tv_sec) + 1e-9 * (double)(t1.tv_nsec - t0.tv_nsec),
+                d.from_cache ? "packed cache, mmap" : d.threads_used > 0 ? "mmap FASTA parser" : "streaming reader",
+                d.threads_used > 0 ? d.threads_used : 1, d.threads_used > 1 ? "s" : "");
 
     /* ---- GPU search (the reference's timed `omp parallel for`, src/alignment_cmdline.c:503-509) ---- */
     int ndev = swgpu_device_count();

@@ -77,7 +77,7 @@ static int load_streaming(const char *path, bool use_zlib, swdb_t *out)
     }
     if (!out->off) { out->off = (int64_t *)xmalloc(sizeof(int64_t)); out->name_off = (int64_t *)xmalloc(sizeof(int64_t)); }
     out->off[n] = res; out->name_off[n] = nb;
-    out->n = n; out->n_residues = res; out->threads_used = 1;
+    out->n = n; out->n_residues = res; out->threads_used = 0;
     swfa_record_free(&rec);
     swfa_close(r);
     return 0;

@@ -27,7 +27,7 @@ typedef struct {
     char    *text;         /* the residues as written in the file (case preserved), same offsets as codes;
                               NULL when the database came from a cache file (decode codes instead) */
     int      from_cache;   /* 1 = mmap'ed from a .swdb file */
-    int      threads_used; /* parser threads (1 = streaming reader) */
+    int      threads_used; /* threads of the mmap parser; 0 = streaming reader or cache */
     void    *map; size_t map_len;   /* private: backing mapping of a cache file */
 } swdb_t;
 
