@@ -7,10 +7,14 @@
 //   * items = (target, stripe), enumerated target-major / stripe-ascending and pulled from one atomic queue, so
 //     the producer of an item's input row always has a smaller item index: it is already running (or done) when
 //     the consumer starts -- no deadlock whatever the number of resident warps;
-//   * stripe s-1 -> stripe s: the bottom row (H, V per column) goes through a full-length row in global memory
-//     (two rows per target slot, ping-pong by stripe parity) and a 64-bit progress word per (slot, stripe),
-//     published with st.release.gpu every 32 columns and polled with ld.acquire.gpu by lane 0 of the consumer;
-//   * target slots (rows, progress words, per-stripe results) are reused round-robin: a warp starts an item of
+//   * stripe s-1 -> stripe s: the bottom row goes through a full-length row in global memory (two rows per target
+//     slot, ping-pong by stripe parity).  Every column is ONE aligned 16-byte store (H, tag, V, tag) by the
+//     producer's lane 31 and one 16-byte volatile load by the consumer, which simply re-reads until both tags are
+//     the producer's (tag = f(item, launch epoch), so neither an older stripe of the same parity nor an earlier
+//     launch can be mistaken for it).  The flag travels with the data: no fence, no separate progress word
+//     (the first version published a counter with st.release.gpu every 32 columns and polled it with
+//     ld.acquire.gpu: the MEMBAR and the L1 invalidate were the two hottest instructions in ncu);
+//   * target slots (rows, per-stripe results) are reused round-robin: a warp starts an item of
 //     target t only after target t - K3X_SLOTS has completed (done counter per slot);
 //   * the last warp to finish a target reduces the per-stripe results and writes the target's output.
 // Inside a warp the scheme is k3_intra's: lane l owns 4 rows, the target streams through the lanes by
@@ -41,9 +45,9 @@ struct K3XParams {
   int             nstripes_max; // ceil(lq / 128)
   const int8_t*   table;
   int             oe, ge;
-  int2*           rows;         // [K3X_SLOTS][2][row_stride] (H, V)
+  int4*           rows;         // [K3X_SLOTS][2][row_stride] (H, tag, V, tag)
   long long       row_stride;
-  unsigned long long* progress; // [K3X_SLOTS][nstripes_max]: (target + 1) << 32 | columns published
+  unsigned        epoch;        // launch counter of this slot set: makes tags unique across launches
   unsigned*       done;         // [K3X_SLOTS]: items finished on this slot since the launch
   int4*           partial;      // [K3X_SLOTS][nstripes_max]: (best, j, i, -) per stripe
   const int64_t*  order;        // !TRACK: scores_file[order[sidx]] = score
@@ -55,13 +59,16 @@ struct K3XParams {
   int             min_len;      // !TRACK: targets shorter than this are left to k3_intra
 };
 
-__device__ __forceinline__ unsigned long long ld_acquire_u64(const unsigned long long* p) {
-  unsigned long long v;
-  asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+__device__ __forceinline__ int4 ld_volatile_v4(const int4* p) {
+  int4 v;
+  asm volatile("ld.volatile.global.v4.s32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
   return v;
 }
-__device__ __forceinline__ void st_release_u64(unsigned long long* p, unsigned long long v) {
-  asm volatile("st.release.gpu.global.u64 [%0], %1;" :: "l"(p), "l"(v) : "memory");
+__device__ __forceinline__ void st_volatile_v4(int4* p, int a, int b, int c, int d) {
+  asm volatile("st.volatile.global.v4.s32 [%0], {%1, %2, %3, %4};" :: "l"(p), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+__device__ __forceinline__ int k3x_tag(long long item, unsigned epoch) {
+  return (int)((((unsigned)(item + 1) * 2654435761u) ^ (epoch * 40503u + 0x5bd1e995u)) | 1u);   // never 0 (zeroed rows)
 }
 __device__ __forceinline__ unsigned ld_acquire_u32(const unsigned* p) {
   unsigned v;
@@ -138,11 +145,9 @@ __global__ void __launch_bounds__(K3X_WARPS * 32) k3x(const K3XParams P) {
       }
       __syncwarp();
       const bool has_in = stripe > 0, has_out = stripe + 1 < nstripes;
-      const int2* row_in = P.rows + ((size_t)slot * 2 + ((stripe + 1) & 1)) * (size_t)P.row_stride;
-      int2* row_out = P.rows + ((size_t)slot * 2 + (stripe & 1)) * (size_t)P.row_stride;
-      const unsigned long long* prog_in = P.progress + (size_t)slot * P.nstripes_max + (stripe - 1);
-      unsigned long long* prog_out = P.progress + (size_t)slot * P.nstripes_max + stripe;
-      const unsigned long long tag = (unsigned long long)(t + 1) << 32;
+      const int4* row_in = P.rows + ((size_t)slot * 2 + ((stripe + 1) & 1)) * (size_t)P.row_stride;
+      int4* row_out = P.rows + ((size_t)slot * 2 + (stripe & 1)) * (size_t)P.row_stride;
+      const int tag_in = k3x_tag(item - 1, P.epoch), tag_out = k3x_tag(item, P.epoch);
       int H[R3], G[R3];
 #pragma unroll
       for (int k = 0; k < R3; ++k) { H[k] = 0; G[k] = 0; }
@@ -152,22 +157,18 @@ __global__ void __launch_bounds__(K3X_WARPS * 32) k3x(const K3XParams P) {
       for (int s = 0; s < nsteps; ++s) {
         if ((s & 31) == 0) {
           const int j = s + lane;
-          if (has_in && s < lt) {                          // wait until the stripe above has published columns [s, s+32)
-            if (lane == 0) {
-              const unsigned long long need = tag | (unsigned long long)min(s + 32, lt);
-              unsigned spins = 0;
-              for (;;) {
-                const unsigned long long v = ld_acquire_u64(prog_in);
-                if ((v >> 32) == (tag >> 32) && v >= need) break;
-                __nanosleep(100);
-                if (++spins > K3X_SPIN_LIMIT) { atomicExch(P.error_flag, 1u); break; }
-              }
+          int4 b = make_int4(0, 0, 0, 0);
+          if (has_in && j < lt) {                          // my column of the stripe above: re-read until it carries its tag
+            unsigned spins = 0;
+            for (;;) {
+              b = ld_volatile_v4(&row_in[j]);
+              if (b.y == tag_in && b.w == tag_in) break;
+              __nanosleep(40);
+              if (++spins > K3X_SPIN_LIMIT) { atomicExch(P.error_flag, 1u); break; }
             }
-            __syncwarp();
           }
-          int2 b = make_int2(0, 0);
-          if (has_in && j < lt) b = __ldcg(&row_in[j]);
-          pre_h = b.x; pre_v = b.y;
+          __syncwarp();
+          pre_h = b.x; pre_v = b.z;
           pre_code = (j < lt) ? (int)tp[(long)j * tstep] : 0;
         }
         int code = __shfl_up_sync(0xffffffffu, my_code, 1);
@@ -199,10 +200,7 @@ __global__ void __launch_bounds__(K3X_WARPS * 32) k3x(const K3XParams P) {
           if (TRACK && k3x_better(colbest, j, row0 + colk, best, bj, bi)) { best = colbest; bj = j; bi = row0 + colk; }
           out_h = H[R3 - 1];
           out_v = V;
-          if (lane == 31 && has_out) {
-            row_out[j] = make_int2(out_h, out_v);
-            if ((j & 31) == 31 || j == lt - 1) st_release_u64(prog_out, tag | (unsigned long long)(j + 1));
-          }
+          if (lane == 31 && has_out) st_volatile_v4(&row_out[j], out_h, tag_out, out_v, tag_out);
         }
       }
       // this stripe's candidate

@@ -48,6 +48,7 @@ int slot_prepare(swgpu_db* db, swgpu_slot& S) {
   if ((r = dalloc(db, &S.d_bnd3, (size_t)db->k3_grid * swk::K3_WARPS * (size_t)db->bnd3_stride))) return r;
   if (db->max_len >= kWaveMinLen) {
     if ((r = dalloc(db, &S.d_x_rows, (size_t)swk::K3X_SLOTS * 2 * (size_t)db->x_row_stride))) return r;
+    CU(cudaMemset(S.d_x_rows, 0, sizeof(int4) * (size_t)swk::K3X_SLOTS * 2 * (size_t)db->x_row_stride));
     if ((r = dalloc(db, &S.d_x_done, (size_t)swk::K3X_SLOTS))) return r;
   }
   CU(cudaMallocHost((void**)&S.h_ctr, 16 * sizeof(unsigned)));
@@ -55,22 +56,22 @@ int slot_prepare(swgpu_db* db, swgpu_slot& S) {
   return SWGPU_OK;
 }
 
-// k3x slot state for a query of lq rows: progress words and per-stripe partial results grow with the query;
-// progress and done counters are zeroed on `stream` before every k3x launch.
+// k3x slot state for a query of lq rows: the per-stripe partial results grow with the query; the completion
+// counters are zeroed on `stream` and the tag epoch advances before every k3x launch.
 int k3x_prepare(swgpu_db* db, swgpu_slot& S, int lq, cudaStream_t stream) {
   const int ns = std::max(1, (lq + 127) / 128);
   if (!S.d_x_rows) {                                       // top-k coordinates on a database without long targets
-    CU(cudaMalloc((void**)&S.d_x_rows, sizeof(int2) * (size_t)swk::K3X_SLOTS * 2 * (size_t)db->x_row_stride));
+    CU(cudaMalloc((void**)&S.d_x_rows, sizeof(int4) * (size_t)swk::K3X_SLOTS * 2 * (size_t)db->x_row_stride));
+    CU(cudaMemsetAsync(S.d_x_rows, 0, sizeof(int4) * (size_t)swk::K3X_SLOTS * 2 * (size_t)db->x_row_stride, stream));
     CU(cudaMalloc((void**)&S.d_x_done, sizeof(unsigned) * swk::K3X_SLOTS));
   }
   if (ns > S.x_stripes_cap) {
-    cudaFree(S.d_x_progress); cudaFree(S.d_x_partial); S.d_x_progress = nullptr; S.d_x_partial = nullptr;
+    cudaFree(S.d_x_partial); S.d_x_partial = nullptr;
     S.x_stripes_cap = ns + ns / 2;
-    CU(cudaMalloc((void**)&S.d_x_progress, sizeof(unsigned long long) * (size_t)swk::K3X_SLOTS * S.x_stripes_cap));
     CU(cudaMalloc((void**)&S.d_x_partial, sizeof(int4) * (size_t)swk::K3X_SLOTS * S.x_stripes_cap));
   }
-  CU(cudaMemsetAsync(S.d_x_progress, 0, sizeof(unsigned long long) * (size_t)swk::K3X_SLOTS * ns, stream));
   CU(cudaMemsetAsync(S.d_x_done, 0, sizeof(unsigned) * swk::K3X_SLOTS, stream));
+  ++S.x_epoch;
   return SWGPU_OK;
 }
 
@@ -80,7 +81,7 @@ void slot_release(swgpu_slot& S) {
   cudaFree(S.d_sprof); cudaFree(S.d_sprof2);
   cudaFree(S.d_keys); cudaFree(S.d_hit_sidx); cudaFree(S.d_sel); cudaFree(S.d_coords);
   cudaFree(S.d_xs_bnd); cudaFree(S.d_xs_progress); cudaFree(S.d_xs_raw);
-  cudaFree(S.d_x_rows); cudaFree(S.d_x_progress); cudaFree(S.d_x_partial); cudaFree(S.d_x_done);
+  cudaFree(S.d_x_rows); cudaFree(S.d_x_partial); cudaFree(S.d_x_done);
   cudaFreeHost(S.h_ctr); cudaFreeHost(S.h_keys); cudaFreeHost(S.h_coords); cudaFreeHost(S.h_best); cudaFreeHost(S.h_sidx);
   cudaFreeHost(S.h_scores);
   for (auto& e : S.ev) if (e) cudaEventDestroy(e);
@@ -284,7 +285,7 @@ int launch_32bit(swgpu_db* db, swgpu_slot& S, cudaStream_t stream, const int* li
     W.sidx_list = list; W.work_count = list_count; W.n_targets = n_all; W.counter = q_k3x;
     W.plain = db->d_plain; W.plain_off = db->d_plain_off; W.query = S.d_query; W.lq = lq; W.nstripes_max = (lq + 127) / 128;
     W.table = S.d_table; W.oe = oe; W.ge = ge; W.rows = S.d_x_rows; W.row_stride = db->x_row_stride;
-    W.progress = S.d_x_progress; W.done = S.d_x_done; W.partial = S.d_x_partial;
+    W.epoch = S.x_epoch; W.done = S.d_x_done; W.partial = S.d_x_partial;
     W.order = db->d_order; W.scores_file = S.d_scores; W.error_flag = S.d_counters + 6; W.min_len = kWaveMinLen;
     if ((double)db->n * W.nstripes_max >= 4.0e9) return fail(SWGPU_EINVAL, "query too long for this database size (32-bit path)");
     swk::k3x<false><<<db->sm_count * 2, swk::K3X_WARPS * 32, 0, stream>>>(W);

@@ -41,8 +41,9 @@ struct swgpu_slot {
   unsigned* d_xs_progress = nullptr;  unsigned* d_xs_raw = nullptr;  int64_t xs_prog_cap = 0, xs_raw_cap = 0;
   int2*     d_bnd3 = nullptr;          // k3_intra carry rows
   // k3x (32-bit wavefront over many warps): target slots
-  int2*     d_x_rows = nullptr;        // [K3X_SLOTS][2][x_row_stride]
-  unsigned long long* d_x_progress = nullptr;  int4* d_x_partial = nullptr;  int x_stripes_cap = 0;   // [K3X_SLOTS][x_stripes_cap]
+  int4*     d_x_rows = nullptr;        // [K3X_SLOTS][2][x_row_stride] (H, tag, V, tag)
+  int4*     d_x_partial = nullptr;  int x_stripes_cap = 0;   // [K3X_SLOTS][x_stripes_cap]
+  unsigned  x_epoch = 0;               // k3x launches on this slot so far (tags are unique per launch)
   unsigned* d_x_done = nullptr;        // [K3X_SLOTS]
   int8_t*   d_query = nullptr;  int64_t query_cap = 0;
   int8_t*   d_table = nullptr;

@@ -165,7 +165,7 @@ int enqueue_topk(swgpu_db* db, swgpu_slot& S, int k) {
     for (int phase = 0; phase < 2; ++phase) {
       int r = swi::k3x_prepare(db, S, (int)S.lq, st);
       if (r) return r;
-      P.progress = S.d_x_progress; P.done = S.d_x_done; P.partial = S.d_x_partial; P.rows = S.d_x_rows;
+      P.epoch = S.x_epoch; P.done = S.d_x_done; P.partial = S.d_x_partial; P.rows = S.d_x_rows;
       P.phase = phase; P.counter = S.d_counters + 8 + phase;
       swk::k3x<true><<<grid, swk::K3X_WARPS * 32, 0, st>>>(P);
     }
