@@ -310,6 +310,11 @@ def main():
         sms = torch.cuda.get_device_properties(local).multi_processor_count
         peak_gcups = alu_rate * 32 * sms * sm_max * 1e6 / 2.25 / 1e9
         k1_gcups = k1cells / (k1ms * 1e-3) / 1e9 if k1ms > 0 else 0.0
+        try:
+            with open(os.path.join(ROOT, "profiles", "k1s_traffic.json")) as f:
+                traffic = json.load(f)
+        except OSError:
+            traffic = {}
         # algorithmic HBM bytes of K1 per step: 1 B per target residue per query pass + 4 B score per target per query
         k1_bytes = a.steps * len(queries) * (n_res + 4 * n)
         hbm_gbs = k1_bytes / (k1ms * 1e-3) / 1e9 if k1ms > 0 else 0.0
@@ -332,7 +337,11 @@ def main():
                          "k1_timing": "CUDA events around K1S in a serial pass of the same K steps right after the timed region "
                                       "(one query at a time; in the pipelined region consecutive queries overlap)",
                          "serial_ms_per_step": ser_ms / a.steps,
-                         "traffic": None,
+                         "traffic": traffic.get("single_stripe_lq1000", {}).get("bytes"),
+                         "traffic_note": "DRAM bytes of ONE k1s launch over this database (ncu --set full, profiles/k1s_traffic.json): "
+                                         "single-stripe Lq=1000; multi-stripe Lq=2005 moves "
+                                         f"{traffic.get('multi_stripe_lq2005', {}).get('bytes')} B; algorithmic "
+                                         f"{n_res + 4 * n} B per launch",
                          "hbm": {"achieved": hbm_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": hbm_gbs / hbm_peak, "peak_src": peak_src}},
             "cpu_baseline": cpu,
             "rescored_per_step": resc / a.steps,
