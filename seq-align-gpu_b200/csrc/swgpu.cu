@@ -7,6 +7,9 @@
 #include "sw_k1s.cuh"
 #include "sw_k3x.cuh"
 
+// multi-stripe K1S with R >= 28 lives in sw_k1s_o1.cu (different ptxas options)
+namespace swk { cudaError_t launch_k1s_multi_o1(int R, const K1SParams& P, cudaStream_t stream, int grid, int device); }
+
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -142,6 +145,17 @@ int swgpu_db_create(swgpu_db_t** out, int device, const int8_t* codes, const int
   db->n_long_streams = pk.n_long_streams; db->n_long_pairs = pk.n_long_pairs;
   db->scols_len = (int64_t)pk.scols_len;
   db->long_cols = pk.n_long_streams < pk.n_streams ? pk.stream_off[pk.n_long_streams] : (int64_t)pk.scols_len;
+  // A stream is a serial chain of columns run by ONE warp.  Sharing its scheduler with the bulk warps, that warp
+  // takes ~7 cycles per instruction, the whole GPU retires 592 x 0.73 per cycle: a stream longer than
+  // scols_len / 3000 columns finishes after everything else (measured on C2: the 35 213-column stream added
+  // 8-25 % to 2 launches out of 3, profiles/README.md).  Streams past a third of that get a warp of their own.
+  {
+    const int64_t crit = std::max<int64_t>(SWPACK_LONG_STREAM_COLS, (int64_t)pk.scols_len / 9000);
+    int64_t nv = 0;
+    while (nv < pk.n_long_streams && pk.stream_ncols[nv] > crit) ++nv;
+    db->n_vlong_streams = nv;
+    db->n_vlong_pairs = nv < pk.n_streams ? pk.stream_pair0[nv] : pk.n_pairs;
+  }
 
   auto body = [&]() -> int {
     cudaDeviceProp prop;
@@ -256,8 +270,12 @@ int launch_k1s(swgpu_db* db, const swk::K1SParams& P, int g, int R, bool multi, 
   if (!k1s_has_plan(g, R, multi)) return fail(SWGPU_EINVAL, "no k1s instantiation for g=%d R=%d multi=%d", g, R, (int)multi);
   if (multi) {
 #define K1S_CASEM(r) case r: return launch_k1s_t<r, 32, true>(db, P, stream, grid);
-    switch (R) { K1S_CASEM(16) K1S_CASEM(20) K1S_CASEM(24) K1S_CASEM(26) K1S_CASEM(28) K1S_CASEM(30) K1S_CASEM(32) default: break; }
+    switch (R) { K1S_CASEM(16) K1S_CASEM(20) K1S_CASEM(24) K1S_CASEM(26) default: break; }
 #undef K1S_CASEM
+    if (R >= 28) {                                             // built with other ptxas options: sw_k1s_o1.cu
+      CU(swk::launch_k1s_multi_o1(R, P, stream, grid, db->device));
+      return SWGPU_OK;
+    }
     return fail(SWGPU_EINVAL, "no multi-stripe k1s instantiation for R=%d", R);
   }
   if (g == 8) return launch_k1s_g<8>(db, P, R, stream, grid);
@@ -338,7 +356,10 @@ int enqueue_search(swgpu_db* db, swgpu_slot& S, const int8_t* query, int64_t lq,
   // Long streams (one target pair of thousands of columns) are latency-bound on their serial column chain: when the
   // bulk plan uses fewer than 32 lanes per pair they get their own launch with all 32 lanes and the fewest rows per
   // lane, one stream per CTA, on the high-priority CUDA stream.
-  const bool split_long = use16 && plan.npass == 1 && plan.g < 32 && db->n_long_streams > 0;
+  // With 32 lanes per pair already, only the streams that would outlast the bulk launch (n_vlong_streams) are split off.
+  const int64_t n_split_streams = plan.g < 32 ? db->n_long_streams : db->n_vlong_streams;
+  const int64_t n_split_pairs = plan.g < 32 ? db->n_long_pairs : db->n_vlong_pairs;
+  const bool split_long = use16 && plan.npass == 1 && n_split_streams > 0;
   K1SPlan plan_long = plan;
   if (split_long) {
     int R = (int)((lq + 31) / 32); R += R & 1; if (R < 8) R = 8;
@@ -358,7 +379,7 @@ int enqueue_search(swgpu_db* db, swgpu_slot& S, const int8_t* query, int64_t lq,
       CU(cudaMalloc((void**)&S.d_sprof2, S.sprof2_cap * sizeof(unsigned)));
     }
   }
-  S.use16 = use16; S.split_long = split_long; S.lq = lq; S.oe = oe; S.ge = ge;
+  S.use16 = use16; S.split_long = split_long; S.n_split_pairs = split_long ? n_split_pairs : 0; S.lq = lq; S.oe = oe; S.ge = ge;
 
   // ---- timed region: first kernel -> last result resident in HBM ----
   CU(cudaEventRecord(e[0], sm));
@@ -376,7 +397,7 @@ int enqueue_search(swgpu_db* db, swgpu_slot& S, const int8_t* query, int64_t lq,
     PS.BB = B * 0x10001u; PS.BBM = (B + (unsigned)(-oe)) * 0x10001u;
     PS.OE2 = ((unsigned)oe & 0xffffu) * 0x10001u; PS.GE2 = ((unsigned)ge & 0xffffu) * 0x10001u;
     const unsigned limit = 65535u - 129u;
-    const int64_t nls = split_long ? db->n_long_streams : 0, nlp = split_long ? db->n_long_pairs : 0;
+    const int64_t nls = split_long ? n_split_streams : 0, nlp = split_long ? n_split_pairs : 0;
     CU(cudaEventRecord(e[3], sm));
     CU(cudaStreamWaitEvent(sa, e[3], 0));
     if (split_long) {
@@ -519,7 +540,7 @@ int collect_search(swgpu_db* db, swgpu_slot& S, swgpu_stats_t* stats) {
     if (S.use16) {
       CU(cudaEventElapsedTime(&ms, e[0], e[1])); st.ms_inter = ms;
       CU(cudaEventElapsedTime(&ms, e[1], e[2])); st.ms_rescore = ms;
-      if (S.split_long) { CU(cudaEventElapsedTime(&ms, e[3], e[4])); st.ms_intra = ms; st.n_long = 2 * db->n_long_pairs; }
+      if (S.split_long) { CU(cudaEventElapsedTime(&ms, e[3], e[4])); st.ms_intra = ms; st.n_long = 2 * S.n_split_pairs; }
       st.cells_inter = st.cells;
       st.n_rescored = ctr[2];
       if (ctr[2]) {

@@ -62,6 +62,7 @@ struct swgpu_slot {
   int32_t* h_scores = nullptr;  int64_t h_scores_cap = 0;   // staging when the caller's score buffer is pageable
   // host-side state of the search in flight / last finished
   bool in_flight = false, have_scores = false, use16 = false, split_long = false;
+  int64_t n_split_pairs = 0;                   // pairs scored by the separate long-stream launch of this search
   int64_t lq = 0;  int oe = 0, ge = 0;
   int topk_k = 0, topk_launches = 0;
   int32_t* user_scores = nullptr;  bool scores_staged = false;
@@ -85,6 +86,7 @@ struct swgpu_db {
   int64_t   n_pairs = 0, n_streams = 0;
   int32_t   max_stream_cols = 0;
   int64_t   n_long_streams = 0, n_long_pairs = 0;   // leading long streams get their own low-latency launch
+  int64_t   n_vlong_streams = 0, n_vlong_pairs = 0; // the few streams long enough to outlast the whole bulk launch (swgpu.cu)
   int64_t   long_cols = 0, scols_len = 0;           // stream columns of the long streams / of all streams
   long long bnd_s_stride = 0;  int k1s_grid = 0;    // k1s multi-stripe carry rows: per warp slot
   long long bnd3_stride = 0;   int k3_grid = 0;     // k3_intra carry rows

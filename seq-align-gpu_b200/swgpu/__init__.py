@@ -13,7 +13,8 @@ from dataclasses import dataclass
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(os.path.dirname(_HERE), "libswgpu.so")
+# SWGPU_LIB: profiling knob (scripts/ab_lib.py compares two builds of the same library on one box)
+LIB_PATH = os.environ.get("SWGPU_LIB") or os.path.join(os.path.dirname(_HERE), "libswgpu.so")
 
 
 class SwgpuError(RuntimeError):
