@@ -225,10 +225,13 @@ K1SPlan plan_k1s(int64_t lq, int64_t n_streams, int warp_slots) {
     if (best_cost < 0 || cost <= best_cost) { best_cost = cost; best = K1SPlan{g, gl, R, 1}; }
   }
   if (best_cost < 0) {
-    for (int R = 24; R <= 32; R += 2) {
-      const int np = (int)((lq + 32 * R - 1) / (32 * R));
-      const double cost = (double)np * 32 * R * (9.0 * R + 18.0) / R;
-      if (best_cost < 0 || cost < best_cost) { best_cost = cost; best = K1SPlan{32, 5, R, np}; }
+    // multi-stripe: measured time per padded query row on the C2 database (scripts/tune_plan.py, us per row)
+    static const struct { int R; double us_per_row; } kMulti[] = {{16, 44.1}, {20, 43.3}, {24, 40.8}, {26, 39.0},
+                                                                  {28, 39.1}, {30, 37.3}, {32, 38.9}};
+    for (const auto& m : kMulti) {
+      const int np = (int)((lq + 32 * m.R - 1) / (32 * m.R));
+      const double cost = (double)np * 32 * m.R * m.us_per_row;
+      if (best_cost < 0 || cost < best_cost) { best_cost = cost; best = K1SPlan{32, 5, m.R, np}; }
     }
   }
   if (const char* ev = getenv("SWGPU_K1S_PLAN")) {               // "g,R": profiling override of the plan
