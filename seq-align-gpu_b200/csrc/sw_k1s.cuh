@@ -24,36 +24,57 @@
 
 namespace swk {
 
-template <int R> struct SProf {
+// Profile layout.  From K1S_PAIRED_MIN_R rows per lane on, the words of a lane are stored in PAIRS (8 bytes per lane,
+// [code][word pair][lane][2]) and fetched with one 64-bit shared load per pair: half the LDS instructions for the
+// same bytes.  Below that (the 3-CTA/SM plans, at their register limit) it is [code][word][lane], 32-bit loads.
+#ifndef K1S_PAIRED_MIN_R
+#define K1S_PAIRED_MIN_R 20
+#endif
+// Measured per instantiation (scripts/ab_lib.py): pairs gain 4-5 % at R = 28 and 32, 0-2 % at R = 24, and lose 1 % at
+// R = 22 and in the multi-stripe R = 30 kernel, which therefore keep the 32-bit layout.
+__host__ __device__ constexpr bool sprof_paired(int R, bool multi) {
+  return R >= K1S_PAIRED_MIN_R && R != 22 && !(multi && R == 30);
+}
+__host__ __device__ constexpr int sprof_wa(int R, bool multi) { return sprof_paired(R, multi) ? 2 * (((R + 3) / 4 + 1) / 2) : (R + 3) / 4; }
+__host__ __device__ constexpr int sprof_wb(int R, bool multi) { return sprof_paired(R, multi) ? 2 * ((R / 2 + 1) / 2) : R / 2; }
+__host__ __device__ constexpr int sprof_words(int R, bool multi) { return 32 * (sprof_wa(R, multi) + sprof_wb(R, multi)) * 32; }
+
+template <int R, bool MULTI> struct SProf {
   static_assert(R % 2 == 0 && R >= 4 && R <= 32, "R must be even, 4..32");
-  static constexpr int WA = (R + 3) / 4;            // int8x4 words: s(k..k+3) for the LOW-half target
-  static constexpr int WB = R / 2;                  // int8x4 words: s(k),s(k),s(k+1),s(k+1) for the HIGH-half target
-  static constexpr int WORDS = 32 * (WA + WB) * 32; // [code][word][lane] for A, then for B
+  static constexpr bool PAIRED = sprof_paired(R, MULTI);
+  static constexpr int WA = sprof_wa(R, MULTI);            // int8x4 words: s(k..k+3) for the LOW-half target (padded to even if PAIRED)
+  static constexpr int WB = sprof_wb(R, MULTI);          // int8x4 words: s(k),s(k),s(k+1),s(k+1) for the HIGH-half target
+  static constexpr int WORDS = sprof_words(R, MULTI);    // A section (all codes), then B section
 };
 
-// prof[pass][A: code][w][lane] | [B: code][w][lane]; lane l of a g-lane group owns rows
-// pass*g*R + (l % g)*R + k.  Code 0 (padding) and rows past the query end score -128.
+// prof[pass][A section | B section]; lane l of a g-lane group owns rows pass*g*R + (l % g)*R + k.
+// Code 0 (padding) and rows past the query end (or past R) score -128.
 static __global__ void build_sprofile(const int8_t* __restrict__ query, int lq, const int8_t* __restrict__ table,
                                       int R, int g, int npass, unsigned* __restrict__ prof) {
-  const int WA = (R + 3) / 4, WB = R / 2;
+  const bool multi = npass > 1;
+  const int WA = sprof_wa(R, multi), WB = sprof_wb(R, multi);
+  const bool paired = sprof_paired(R, multi);
   const int words = 32 * (WA + WB) * 32;
   const long total = (long)npass * words;
   for (long idx = blockIdx.x * (long)blockDim.x + threadIdx.x; idx < total; idx += (long)gridDim.x * blockDim.x) {
     const int pass = (int)(idx / words), w = (int)(idx % words);
-    const int lane = w & 31, cw = w >> 5;
+    const bool isA = w < 32 * WA * 32;
+    const int v = isA ? w : w - 32 * WA * 32, W = isA ? WA : WB;
+    const int c = v / (W * 32), r = v % (W * 32);
+    // word index within the code and lane: [word][lane], or [word pair][lane][2]
+    const int word = paired ? 2 * (r / 64) + (r & 1) : r / 32;
+    const int lane = paired ? (r % 64) / 2 : r % 32;
     const long row0 = (long)pass * g * R + (long)(lane & (g - 1)) * R;
-    auto score = [&](int c, int k) -> unsigned {
+    auto score = [&](int k) -> unsigned {
       const long i = row0 + k;
       const int s = (c == 0 || k >= R || i >= lq) ? -128 : (int)table[(query[i] & 31) * 32 + c];
       return (unsigned)(s & 0xff);
     };
     unsigned out;
-    if (cw < 32 * WA) {
-      const int c = cw / WA, k4 = cw % WA;
-      out = score(c, 4 * k4) | (score(c, 4 * k4 + 1) << 8) | (score(c, 4 * k4 + 2) << 16) | (score(c, 4 * k4 + 3) << 24);
+    if (isA) {
+      out = score(4 * word) | (score(4 * word + 1) << 8) | (score(4 * word + 2) << 16) | (score(4 * word + 3) << 24);
     } else {
-      const int v = cw - 32 * WA, c = v / WB, k2 = v % WB;
-      const unsigned s0 = score(c, 2 * k2), s1 = score(c, 2 * k2 + 1);
+      const unsigned s0 = score(2 * word), s1 = score(2 * word + 1);
       out = s0 | (s0 << 8) | (s1 << 16) | (s1 << 24);
     }
     prof[idx] = out;
@@ -105,9 +126,9 @@ constexpr int K1S_WARPS = 8;
 #define K1S_R3CTA 18                         // R up to this: three CTAs per SM (<= 85 registers per thread)
 #endif
 
-template <int R>
+template <int R, bool MULTI>
 constexpr size_t k1s_smem_bytes() {
-  return (size_t)SProf<R>::WORDS * 4 + (size_t)K1S_WARPS * (128 * 2 + 32 * 8) + 16;
+  return (size_t)SProf<R, MULTI>::WORDS * 4 + (size_t)K1S_WARPS * (128 * 2 + 32 * 8) + 16;
 }
 
 // LANES = lanes per target pair (g), a compile-time constant (shuffle widths, ring masks and the block period fold into
@@ -119,7 +140,7 @@ template <int R, int LANES, bool MULTI>
 __global__ void __launch_bounds__(K1S_WARPS * 32, (R <= K1S_R3CTA ? 3 : 2)) k1s(const K1SParams P) {
   static_assert(LANES == 8 || LANES == 16 || LANES == 32, "lanes per pair");
   static_assert(!MULTI || LANES == 32, "multi-stripe mode uses all 32 lanes");
-  using S = SProf<R>;
+  using S = SProf<R, MULTI>;
   extern __shared__ __align__(16) unsigned smem_u32[];
   unsigned* prof_s = smem_u32;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -132,7 +153,7 @@ __global__ void __launch_bounds__(K1S_WARPS * 32, (R <= K1S_R3CTA ? 3 : 2)) k1s(
   constexpr int rmask = 4 * g - 1;                       // ring of 4g columns per group (g-step blocks, generous slack)
   unsigned short* gring = ring + grp * (4 * g);
   const unsigned BB = P.BB, BBM = P.BBM, OE2 = P.OE2, GE2 = P.GE2;
-  const unsigned pa_lane = (unsigned)__cvta_generic_to_shared(prof_s) + lane * 4;
+  const unsigned pa_lane = (unsigned)__cvta_generic_to_shared(prof_s) + lane * (S::PAIRED ? 8 : 4);
   const unsigned pb_lane = pa_lane + 32 * S::WA * 128;
   uint2* bnd = MULTI ? P.bnd + (size_t)(blockIdx.x * K1S_WARPS + warp) * (size_t)P.bnd_stride : nullptr;
 
@@ -269,7 +290,9 @@ __global__ void __launch_bounds__(K1S_WARPS * 32, (R <= K1S_R3CTA ? 3 : 2)) k1s(
         // t of row k+1 is formed from H[k] of the previous column BEFORE H[k] is overwritten, so the
         // row registers are updated in place (no register moves).
         unsigned V = v_in;
-        unsigned wA = lds32(aoff), wB = lds32(boff), hprev = BB;
+        unsigned wA, wB, wA2 = 0, wB2 = 0, hprev = BB;
+        if (S::PAIRED) { lds64(aoff, wA, wA2); lds64(boff, wB, wB2); }
+        else { wA = lds32(aoff); wB = lds32(boff); }
         unsigned t = add_hi_lo(wB, add_byte(wA, 1u, diag_in));
         diag_in = h_up;
 #pragma unroll
@@ -277,8 +300,13 @@ __global__ void __launch_bounds__(K1S_WARPS * 32, (R <= K1S_R3CTA ? 3 : 2)) k1s(
           unsigned tn = 0;
           if (k + 1 < R) {
             const int k1 = k + 1;
-            if ((k1 & 3) == 0) wA = lds32(aoff + (k1 >> 2) * 128);
-            if ((k1 & 1) == 0) wB = lds32(boff + (k1 >> 1) * 128);
+            if (S::PAIRED) {
+              if ((k1 & 7) == 0) lds64(aoff + (k1 >> 3) * 256, wA, wA2); else if ((k1 & 3) == 0) wA = wA2;
+              if ((k1 & 3) == 0) lds64(boff + (k1 >> 2) * 256, wB, wB2); else if ((k1 & 1) == 0) wB = wB2;
+            } else {
+              if ((k1 & 3) == 0) wA = lds32(aoff + (k1 >> 2) * 128);
+              if ((k1 & 1) == 0) wB = lds32(boff + (k1 >> 1) * 128);
+            }
             tn = add_byte(wA, 1u << (8 * (k1 & 3)), H[k]);
             tn = (k1 & 1) ? add_hi_hi(wB, tn) : add_hi_lo(wB, tn);
           }

@@ -13,7 +13,7 @@ namespace swk {
 
 template <int R>
 static cudaError_t launch_multi(const K1SParams& P, cudaStream_t stream, int grid, int device) {
-  const size_t smem = k1s_smem_bytes<R>();
+  const size_t smem = k1s_smem_bytes<R, true>();
   static thread_local bool attr_done[16] = {};
   if (!attr_done[device & 15]) {
     const cudaError_t e = cudaFuncSetAttribute(k1s<R, 32, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

@@ -28,6 +28,9 @@ namespace swk {
 __device__ __forceinline__ unsigned lds32(unsigned saddr) {
   unsigned v; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(saddr)); return v;
 }
+__device__ __forceinline__ void lds64(unsigned saddr, unsigned& lo, unsigned& hi) {
+  asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(lo), "=r"(hi) : "r"(saddr));
+}
 // c + (signed byte `sel` of a): IDP.4A on the FMA-heavy pipe.  sel_mask = 1 << (8*byte).
 __device__ __forceinline__ unsigned add_byte(unsigned a, unsigned sel_mask, unsigned c) {
   return (unsigned)__dp4a((int)a, (int)sel_mask, (int)c);

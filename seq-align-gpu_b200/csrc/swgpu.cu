@@ -247,7 +247,7 @@ K1SPlan plan_k1s(int64_t lq, int64_t n_streams, int warp_slots) {
 
 template <int R, int G, bool MULTI>
 int launch_k1s_t(swgpu_db* db, const swk::K1SParams& P, cudaStream_t stream, int grid) {
-  const size_t smem = swk::k1s_smem_bytes<R>();
+  const size_t smem = swk::k1s_smem_bytes<R, MULTI>();
   static thread_local bool attr_done[16] = {};
   if (!attr_done[db->device & 15]) {
     CU(cudaFuncSetAttribute(swk::k1s<R, G, MULTI>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -368,7 +368,7 @@ int enqueue_search(swgpu_db* db, swgpu_slot& S, const int8_t* query, int64_t lq,
     int R = (int)((lq + 31) / 32); R += R & 1; if (R < 8) R = 8;
     plan_long = K1SPlan{32, 5, R, 1};
   }
-  auto words_of = [](const K1SPlan& p) { return (size_t)p.npass * 32 * ((p.R + 3) / 4 + p.R / 2) * 32; };
+  auto words_of = [](const K1SPlan& p) { return (size_t)p.npass * (size_t)swk::sprof_words(p.R, p.npass > 1); };
   if (use16) {
     st.tile_rows = plan.R; st.lanes_per_pair = plan.g; st.passes = plan.npass;
     if (words_of(plan) > S.sprof_cap) {
