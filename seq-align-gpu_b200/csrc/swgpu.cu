@@ -226,8 +226,8 @@ K1SPlan plan_k1s(int64_t lq, int64_t n_streams, int warp_slots) {
   }
   if (best_cost < 0) {
     // multi-stripe: measured time per padded query row on the C2 database (scripts/tune_plan.py, us per row)
-    static const struct { int R; double us_per_row; } kMulti[] = {{16, 44.1}, {20, 43.3}, {24, 40.8}, {26, 39.0},
-                                                                  {28, 39.1}, {30, 37.3}, {32, 38.9}};
+    static const struct { int R; double us_per_row; } kMulti[] = {{16, 44.1}, {20, 42.3}, {24, 39.9}, {26, 39.5},
+                                                                  {28, 37.5}, {30, 37.25}, {32, 37.4}};
     for (const auto& m : kMulti) {
       const int np = (int)((lq + 32 * m.R - 1) / (32 * m.R));
       const double cost = (double)np * 32 * m.R * m.us_per_row;
