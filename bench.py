@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py -- GCUPS of the one-to-many Smith-Waterman scoring path (BASELINE.json metric).
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--scale F]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--scale F] [--workload c2|c5]
   torchrun --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...        (N > 1: one rank per GPU, NCCL)
 
 Workload (config 2 of BASELINE.json, SURVEY.md 8(d) "C2"): a Swiss-Prot-shaped synthetic database
@@ -10,6 +10,11 @@ gap open 10 / extend 1, and the classic 20-query length sweep 144..5478 aa.  One
 over the HBM-resident database = 41 752 x n_residues cell updates per GPU.  N > 1 is weak scaling: every
 rank holds its own 205 M-residue shard (the database shards by residue count, no data-path collective);
 after each step the per-rank top-k lists are merged with one small NCCL all_gather.
+
+--workload c5 (config 5 of BASELINE.json, not the default bench line): a UniRef50-shaped database of 10 G residues
+(32.8 M targets) GENERATED ON THE DEVICE (swgpu_db_create_synthetic), dealt longest-first round-robin over the ranks
+(strong scaling: the total is fixed), 64 queries cycling through the same 20 lengths, BLOSUM45, top-100 per query merged
+over NCCL.  One step = the 64 queries; a warm-up step = the first three.  --scale shrinks the database.
 
 value  = GCUPS, device-timed (CUDA events on the engine's streams: first kernel launch of the sweep -> last
          top-k result of the sweep), real unpadded cells of all ranks / max-over-ranks time.  The sweep goes
@@ -112,6 +117,21 @@ def make_workload(rank, scale):
     return codes, off, queries, tab
 
 
+def make_workload_c5(rank, world, scale):
+    """Lengths on the host, residues on the device.  Returns (lens of this rank's shard, global entry ids of the shard
+    or None, queries, table, total residues of this shard)."""
+    from swgpu import synth
+    lens = synth.c5_lengths(scale)
+    queries, _ = synth.c5_queries(lens, 64)
+    tab, _ = synth.load_matrix(os.path.join(ROOT, "scoring", "BLOSUM45.txt"))
+    entries = None
+    if world > 1:
+        order = np.argsort(-lens.astype(np.int64), kind="stable")
+        entries = np.sort(order[rank::world])
+        lens = lens[entries]
+    return lens, entries, queries, tab
+
+
 def cpu_sample(codes, off, stride):
     """Every stride-th GROUP of 16 consecutive targets of the length-sorted database: the reference batches 16
     consecutive records and pads them to the first one (src/alignment_cmdline.c:429-459), so sampling whole
@@ -168,6 +188,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--scale", type=float, default=1.0, help="database size as a fraction of C2 (dev only; 1.0 = the benchmark)")
+    ap.add_argument("--workload", default="c2", choices=["c2", "c5"], help="c2 = the benchmark line; c5 = device-generated 10 G-residue database")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu", action="store_true")
     a = ap.parse_args()
@@ -179,8 +200,21 @@ def main():
               "cache": "database + scratch per GPU (>=0.6 GB) exceed L2 (126 MB); every query pass streams the whole DB",
               "sharding": "one 205M-residue shard per rank, no data-path collective; NCCL all_gather of per-rank top-k"}
 
+    c5 = a.workload == "c5"
+    if c5:
+        config = {"workload": f"C5: UniRef50-shaped synthetic DB generated on the device ({a.scale:g} x 10 G residues in total, "
+                              "LogNormal(ln 230, 0.75) lengths), BLOSUM45, gap open 10 / extend 1, 64 queries cycling through "
+                              "144..5478 aa, top-100 per query; one step = the 64 queries",
+                  "queries": 64, "topk": TOPK,
+                  "cache": "the database per GPU exceeds L2 (126 MB) by orders of magnitude; every query pass streams it",
+                  "sharding": "targets dealt longest-first round-robin over the ranks (total fixed: strong scaling), no data-path "
+                              "collective; NCCL all_gather of per-rank top-k"}
     if a.impl == "reference":
         if rank != 0:
+            return 0
+        if c5:
+            print(json.dumps({"impl": "reference", "unavailable": "the reference arm is timed on the C2 workload only "
+                              "(C5 exists on the device alone; a 1/1024 CPU extrapolation is not a measurement)"}))
             return 0
         codes, off, queries, tab = make_workload(0, a.scale)
         # each step is a bounded sample sized so steps+warmup finish within a few minutes
@@ -212,13 +246,23 @@ def main():
     hbm_peak, sm_max, peak_src = load_peaks()
 
     t0 = time.time()
-    codes, off, queries, tab = make_workload(rank, a.scale)
-    t_gen = time.time() - t0
-    t0 = time.time()
-    db = swgpu.Database(codes, off, device=local, entry_base=rank * (len(off) - 1))
-    t_pack = time.time() - t0
-    n = len(off) - 1
-    n_res = int(off[-1])
+    entries = None
+    if c5:
+        from swgpu import synth
+        lens, entries, queries, tab = make_workload_c5(rank, world, a.scale)
+        t_gen = time.time() - t0
+        t0 = time.time()
+        db = swgpu.Database.synthetic(lens, synth.C5_SEED, entry_ids=entries, device=local)
+        t_pack = time.time() - t0
+        n, n_res = len(lens), int(db.n_residues)
+    else:
+        codes, off, queries, tab = make_workload(rank, a.scale)
+        t_gen = time.time() - t0
+        t0 = time.time()
+        db = swgpu.Database(codes, off, device=local, entry_base=rank * (len(off) - 1))
+        t_pack = time.time() - t0
+        n = len(off) - 1
+        n_res = int(off[-1])
     cells_step = sum(len(q) for q in queries) * n_res
 
     def barrier():
@@ -231,27 +275,31 @@ def main():
 
     def merge_topk(hits_local):
         """per-rank top-k -> NCCL all_gather -> deterministic merge (score desc, entry asc)."""
-        return gather_topk([[h["score"], h["entry"]] for h in hits_local], TOPK, dist, device="cuda" if dist is not None else None)
+        gid = (lambda e: int(entries[e])) if entries is not None else (lambda e: e)
+        return gather_topk([[h["score"], gid(h["entry"])] for h in hits_local], TOPK, dist, device="cuda" if dist is not None else None)
 
-    def step_resident():
+    def step_resident(qsub=None):
         """The sweep through swgpu_search_many(): up to three queries in flight, scores stay in HBM, top-k with
         coordinates per query; then the per-query merge (NCCL all_gather when N > 1)."""
-        _, hits, per, bs = db.search_many(queries, tab, GAP_OPEN, GAP_EXTEND, k=TOPK, want_scores=False)
+        _, hits, per, bs = db.search_many(qsub or queries, tab, GAP_OPEN, GAP_EXTEND, k=TOPK, want_scores=False)
         for h in hits:
             merge_topk(h)
         return bs["ms_total"], bs["kernel_launches"], bs["n_rescored"]
 
+    # C5: the serial per-kernel pass runs five queries spanning the lengths (the whole 64 would double the run)
+    serial_queries = [queries[i] for i in (0, 5, 9, 11, 19)] if c5 else queries
+
     def step_serial():
         """Same sweep, one query at a time (nothing overlaps): the pass the per-kernel K1S time is taken from."""
         ms, k1ms, k1cells = 0.0, 0.0, 0
-        for q in queries:
+        for q in serial_queries:
             st = db.search_resident(q, tab, GAP_OPEN, GAP_EXTEND)
             db.topk(TOPK)
             ms += st["ms_total"] + db.last_topk_ms
             k1ms += st["ms_inter"]; k1cells += st["cells_inter"]
         return ms, k1ms, k1cells
 
-    pinned = [torch.empty(n, dtype=torch.int32).pin_memory().numpy() for _ in queries]
+    pinned = None if c5 else [torch.empty(n, dtype=torch.int32).pin_memory().numpy() for _ in queries]
 
     def step_e2e():
         t = time.perf_counter()
@@ -259,13 +307,15 @@ def main():
         return time.perf_counter() - t
 
     for _ in range(a.warmup):
-        step_resident()
+        step_resident(queries[:3] if c5 else None)
     barrier()
     sampler = ClockSampler(local); sampler.start(); time.sleep(0.25)
     tw0 = time.time()
-    dev_ms, launches, resc = 0.0, 0, 0
+    dev_ms, launches, resc, wall_steps = 0.0, 0, 0, 0.0
     for _ in range(a.steps):
+        t = time.perf_counter()
         r = step_resident()
+        wall_steps += time.perf_counter() - t
         dev_ms += r[0]; launches += r[1]; resc += r[2]
     barrier()
     tw1 = time.time()
@@ -274,18 +324,23 @@ def main():
     # per-kernel time of the dominant kernel: the same K steps, serially (in the pipelined region above the
     # event intervals of consecutive queries overlap, so they cannot be added up)
     ser_ms, k1ms, k1cells = 0.0, 0.0, 0
-    for _ in range(a.steps):
+    for _ in range(1 if c5 else a.steps):
         r = step_serial()
         ser_ms += r[0]; k1ms += r[1]; k1cells += r[2]
     barrier()
 
-    # e2e: host buffers in, host buffers out, wall clock
-    step_e2e()
-    barrier()
-    e2e_s = 0.0
-    for _ in range(a.steps):
-        e2e_s += step_e2e()
-    barrier()
+    # e2e: host buffers in, host buffers out, wall clock.  C5: 64 score vectors of 32.8 M entries are not what a caller of a
+    # database this size reads back -- the e2e figure is the host wall clock of the timed steps themselves (host queries and
+    # table in, top-100 hits with coordinates per query out to host memory, merge included).
+    if c5:
+        e2e_s = wall_steps
+    else:
+        step_e2e()
+        barrier()
+        e2e_s = 0.0
+        for _ in range(a.steps):
+            e2e_s += step_e2e()
+        barrier()
 
     if dist is not None:
         v = torch.tensor([dev_ms, e2e_s, tw1 - tw0], dtype=torch.float64, device="cuda")
@@ -297,7 +352,7 @@ def main():
         dev_ms_max, e2e_max, wall_max, cells_all = dev_ms, e2e_s, tw1 - tw0, float(cells_step)
 
     cpu = None
-    if rank == 0 and world == 1 and not a.no_cpu:
+    if rank == 0 and world == 1 and not a.no_cpu and not c5:
         cpu, _ = run_cpu_reference(codes, off, queries, tab, a.cpu_seconds)
         cpu.pop("seconds", None)
 
@@ -316,27 +371,30 @@ def main():
         except OSError:
             traffic = {}
         # algorithmic HBM bytes of K1 per step: 1 B per target residue per query pass + 4 B score per target per query
-        k1_bytes = a.steps * len(queries) * (n_res + 4 * n)
+        k1_bytes = (1 if c5 else a.steps) * len(serial_queries) * (n_res + 4 * n)
         hbm_gbs = k1_bytes / (k1ms * 1e-3) / 1e9 if k1ms > 0 else 0.0
         line = {
             "metric": "GCUPS", "value": gcups, "unit": "GCUPS", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
-            "ms_per_step": dev_ms_max / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "ms_per_step": dev_ms_max / a.steps, "higher_is_better": True, "scaling": "strong" if c5 else "weak", "vs_baseline": None,
             "dtype": "u16x2 (packed 16-bit, 32-bit rescoring of saturated targets)", "data": "synthetic", "config": config,
             "clocks": clocks, "gpu_launches": launches,
             "e2e": {"value": cells_all * a.steps / e2e_max / 1e9, "unit": "GCUPS",
                     "h2d_bytes_per_step": int(sum(len(q) + 1024 for q in queries)),
-                    "d2h_bytes_per_step": int(len(queries) * 4 * n),
-                    "note": "swgpu_search_many(): host queries/table in, all per-entry int32 scores of every query out to pinned host "
+                    "d2h_bytes_per_step": int(len(queries) * TOPK * 32) if c5 else int(len(queries) * 4 * n),
+                    "note": ("swgpu_search_many(): host queries/table in, top-100 hits with coordinates per query out to host memory, "
+                             "merge included, host wall clock of the timed steps; bytes are per rank; database generated on the device "
+                             "and HBM-resident (one-off cost in setup_s)") if c5 else
+                            "swgpu_search_many(): host queries/table in, all per-entry int32 scores of every query out to pinned host "
                             "memory, host wall clock; bytes are per rank; database packed and HBM-resident (one-off cost in setup_s)"},
             "roofline": {"bound": "int-alu", "kernel": "k1s", "achieved": k1_gcups, "peak": peak_gcups, "unit": "GCUPS",
                          "frac": k1_gcups / peak_gcups if peak_gcups else None,
                          "peak_how": f"{alu_rate:.3f} warp-inst/clk/SM {alu_src} x 32 lanes x {sms} SMs x {sm_max:.0f} MHz / 2.25 ALU-pipe "
                                      f"thread-instructions per cell",
-                         "sm_mhz_seen": sm_clk, "k1_ms_per_step": k1ms / a.steps,
+                         "sm_mhz_seen": sm_clk, "k1_ms_per_step": k1ms / (1 if c5 else a.steps),
                          "k1_share_of_step": k1ms / ser_ms if ser_ms else None,
                          "k1_timing": "CUDA events around K1S in a serial pass of the same K steps right after the timed region "
                                       "(one query at a time; in the pipelined region consecutive queries overlap)",
-                         "serial_ms_per_step": ser_ms / a.steps,
+                         "serial_ms_per_step": ser_ms / (1 if c5 else a.steps),
                          "traffic": traffic.get("single_stripe_lq1000", {}).get("bytes"),
                          "traffic_note": "DRAM bytes of ONE k1s launch over this database (ncu --set full, profiles/k1s_traffic.json): "
                                          "single-stripe Lq=1000; multi-stripe Lq=2005 moves "
@@ -346,6 +404,7 @@ def main():
             "cpu_baseline": cpu,
             "rescored_per_step": resc / a.steps,
             "setup_s": {"generate": t_gen, "pack_upload": t_pack}, "wall_s_timed": wall_max,
+            "db": {"targets_per_gpu": n, "residues_per_gpu": n_res, "device_bytes": int(db.device_bytes)},
         }
         print(json.dumps(line))
     if dist is not None:

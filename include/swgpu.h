@@ -85,6 +85,33 @@ const char *swgpu_version(void);
  */
 int  swgpu_db_create(swgpu_db_t **out, int device, const int8_t *codes, const int64_t *offsets,
                      int64_t n_targets, int64_t entry_base, const swgpu_pack_opts_t *opts);
+
+/*
+ * Synthetic database generated ON THE DEVICE (a UniRef50-shaped 10 G-residue database is
+ * never materialised on the host or in a FASTA file).  The host supplies the target lengths only; the layout
+ * (length sort, pairs, streams) is built from them and the residues are produced by a counter-based generator
+ * straight into the packed buffers: residue j of the target with global entry id e is
+ *     u = mix64((seed ^ e * 0x9E3779B97F4A7C15) + (j + 1) * 0xBF58476D1CE4E5B9) >> 48        (16 bits)
+ *     code = codes[first i with u < cdf[i]]
+ * where mix64 is the splitmix64 finaliser.  A target therefore depends on (seed, e, j) alone -- not on the shard it
+ * lands in or on the number of GPUs -- and any single target can be regenerated on the host for a sampled parity
+ * check (swgpu/synth.py::synth_target).  entry_ids[t] (NULL: entry_base + t) is the global id of local target t.
+ * No reference counterpart (the reference reads FASTA only, src/alignment_cmdline.c:422-457).
+ */
+typedef struct {
+    uint64_t seed;
+    int32_t  n_letters;       /* 1..32 */
+    int32_t  reserved;
+    uint32_t cdf[32];         /* cumulative thresholds out of 65536, non-decreasing, cdf[n_letters-1] == 65536 */
+    int8_t   codes[32];       /* residue code of letter i (1..31) */
+} swgpu_synth_t;
+
+int  swgpu_db_create_synthetic(swgpu_db_t **out, int device, const int32_t *lengths, const int64_t *entry_ids,
+                               int64_t n_targets, int64_t entry_base, const swgpu_synth_t *gen,
+                               const swgpu_pack_opts_t *opts);
+/* Residues of one target (local file-order index) copied back from the packed database: *len = its length;
+ * out == NULL only queries the length.  Used by the sampled parity checks of device-generated databases. */
+int  swgpu_db_fetch_target(swgpu_db_t *db, int64_t local_entry, int8_t *out, int64_t cap, int64_t *len);
 void swgpu_db_destroy(swgpu_db_t *db);
 int64_t swgpu_db_num_targets(const swgpu_db_t *db);
 int64_t swgpu_db_num_residues(const swgpu_db_t *db);

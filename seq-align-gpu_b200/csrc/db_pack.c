@@ -11,7 +11,8 @@ void swpack_free(swpack_t *p)
     memset(p, 0, sizeof(*p));
 }
 
-static int build_streams(swpack_t *p, int32_t stream_cols);
+static int layout_streams(swpack_t *p, int32_t stream_cols, int64_t *pair_col);
+static int fill_streams(swpack_t *p);
 
 int swpack_build(swpack_t *p, const int8_t *codes, const int64_t *offsets, int64_t n, int32_t stream_cols)
 {
@@ -54,11 +55,40 @@ int swpack_build(swpack_t *p, const int8_t *codes, const int64_t *offsets, int64
     }
     if (bad) { swpack_free(p); return -1; }
 
-    return build_streams(p, stream_cols);
+    if (layout_streams(p, stream_cols, NULL) != 0) return -1;
+    return fill_streams(p);
 }
 
-/* 3. streams of paired targets for the systolic kernel (see db_pack.h) */
-static int build_streams(swpack_t *p, int32_t stream_cols)
+/* Layout only: the database is described by its target lengths; `plain` and `scols` stay NULL (the caller fills
+ * them on the device).  pair_col[n_pairs] receives the first stream column of every pair. */
+int swpack_layout(swpack_t *p, const int32_t *lengths, int64_t n, int32_t stream_cols, int64_t *pair_col)
+{
+    memset(p, 0, sizeof(*p));
+    if (n < 0) return -1;
+    p->n_targets = n;
+    int64_t max_len = 0, total = 0;
+    for (int64_t t = 0; t < n; t++) {
+        if (lengths[t] < 0) return -1;
+        if (lengths[t] > max_len) max_len = lengths[t];
+        total += lengths[t];
+    }
+    p->n_residues = total;
+    p->max_len = (int32_t)max_len;
+    int64_t *bucket = (int64_t *)calloc((size_t)max_len + 2, sizeof(int64_t));
+    p->order = (int64_t *)malloc(sizeof(int64_t) * (size_t)(n ? n : 1));
+    p->plain_off = (int64_t *)malloc(sizeof(int64_t) * (size_t)(n + 1));
+    if (!bucket || !p->order || !p->plain_off) { free(bucket); swpack_free(p); return -1; }
+    for (int64_t t = 0; t < n; t++) bucket[max_len - lengths[t] + 1]++;
+    for (int64_t l = 0; l <= max_len; l++) bucket[l + 1] += bucket[l];
+    for (int64_t t = 0; t < n; t++) p->order[bucket[max_len - lengths[t]]++] = t;
+    free(bucket);
+    p->plain_off[0] = 0;
+    for (int64_t s = 0; s < n; s++) p->plain_off[s + 1] = p->plain_off[s] + lengths[p->order[s]];
+    return layout_streams(p, stream_cols, pair_col);
+}
+
+/* 3. streams of paired targets for the systolic kernel (see db_pack.h): the stream tables from the lengths ... */
+static int layout_streams(swpack_t *p, int32_t stream_cols, int64_t *pair_col)
 {
     const int64_t n = p->n_targets;
     const int64_t n_pairs = (n + 1) / 2;
@@ -85,6 +115,7 @@ static int build_streams(swpack_t *p, int32_t stream_cols)
         int64_t len = p->plain_off[2 * q + 1] - p->plain_off[2 * q];
         if (len < 1) len = 1;
         if (cur == 0) { s++; p->stream_off[s] = off; p->stream_pair0[s] = q; }
+        if (pair_col) pair_col[q] = off + cur;
         cur += len;
         if (cur > 0x7fffff00) { swpack_free(p); return -1; }
         if (cur >= stream_cols || q == n_pairs - 1) {
@@ -100,7 +131,14 @@ static int build_streams(swpack_t *p, int32_t stream_cols)
     p->n_long_pairs = p->n_long_streams < n_streams ? p->stream_pair0[p->n_long_streams] : n_pairs;
     p->scols_len = off;
     p->max_stream_cols = maxc;
-    p->scols = (uint16_t *)calloc((size_t)(off ? off : 1), sizeof(uint16_t));
+    return 0;
+}
+
+/* ... and the columns themselves from `plain` */
+static int fill_streams(swpack_t *p)
+{
+    const int64_t n = p->n_targets, n_pairs = p->n_pairs, n_streams = p->n_streams;
+    p->scols = (uint16_t *)calloc((size_t)(p->scols_len ? p->scols_len : 1), sizeof(uint16_t));
     if (!p->scols) { swpack_free(p); return -1; }
 #pragma omp parallel for schedule(dynamic, 64)
     for (int64_t st = 0; st < n_streams; st++) {

@@ -44,6 +44,10 @@ typedef struct {
 
 /* returns 0, or -1 on allocation failure / bad input (negative length, code outside 0..31) */
 int  swpack_build(swpack_t *p, const int8_t *codes, const int64_t *offsets, int64_t n_targets, int32_t stream_cols);
+/* Same layout from target lengths alone (synthetic databases whose residues are generated on the device):
+ * order, plain_off and the stream tables are filled, plain and scols stay NULL; pair_col[(n+1)/2] (may be NULL)
+ * receives the first column of every pair in scols. */
+int  swpack_layout(swpack_t *p, const int32_t *lengths, int64_t n_targets, int32_t stream_cols, int64_t *pair_col);
 void swpack_free(swpack_t *p);
 
 #ifdef __cplusplus

@@ -95,45 +95,12 @@ void slot_release(swgpu_slot& S) {
 
 }  // namespace swi
 
-extern "C" {
+namespace {
 
-int swgpu_device_count(void) {
-  int n = 0;
-  if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
-  return n;
-}
-
-const char* swgpu_last_error(void) { return swi::err_buf(); }
-const char* swgpu_version(void) { return "swgpu 0.2 (sm_100a)"; }
-
-void swgpu_db_destroy(swgpu_db_t* db) {
-  if (!db) return;
-  cudaSetDevice(db->device);
-  cudaDeviceSynchronize();
-  cudaFree(db->d_plain); cudaFree(db->d_plain_off); cudaFree(db->d_order);
-  cudaFree(db->d_scols); cudaFree(db->d_stream_off); cudaFree(db->d_stream_ncols); cudaFree(db->d_stream_pair0);
-  for (auto& S : db->slots) swi::slot_release(S);
-  for (auto& e : db->ev_batch) if (e) cudaEventDestroy(e);
-  delete db;
-}
-
-int swgpu_db_create(swgpu_db_t** out, int device, const int8_t* codes, const int64_t* offsets,
-                    int64_t n_targets, int64_t entry_base, const swgpu_pack_opts_t* opts) {
-  if (!out || n_targets < 0 || (n_targets > 0 && (!codes || !offsets))) return fail(SWGPU_EINVAL, "swgpu_db_create: bad argument");
-  if (n_targets > 0x7ffffff0ll) return fail(SWGPU_EINVAL, "swgpu_db_create: more than 2^31 targets per GPU; shard the database");
-  *out = nullptr;
-  int ndev = 0;
-  CU(cudaGetDeviceCount(&ndev));
-  if (ndev <= 0) return fail(SWGPU_ENODEV, "no CUDA device");
-  if (device < 0 || device >= ndev) return fail(SWGPU_EINVAL, "device %d out of range (%d devices)", device, ndev);
-  CU(cudaSetDevice(device));
-
-  const int stream_cols = (opts && opts->stream_cols > 0) ? opts->stream_cols : kDefaultStreamCols;
-  swpack_t pk;
-  static const int64_t zero_off[1] = {0};
-  if (swpack_build(&pk, codes, n_targets ? offsets : zero_off, n_targets, stream_cols) != 0)
-    return fail(SWGPU_EINVAL, "database packing failed (residue code outside 0..31, negative length, or out of memory)");
-
+// Host tables + device buffers of a packed database.  With pk.plain / pk.scols present they are uploaded; without
+// (layout only, swgpu_db_create_synthetic) the two buffers are allocated and `fill` generates them on the device.
+template <typename Fill>
+static int db_from_pack(swgpu_db_t** out, int device, swpack_t& pk, int64_t entry_base, const swgpu_pack_opts_t* opts, Fill fill) {
   swgpu_db* db = new swgpu_db();
   db->device = device;
   db->n = pk.n_targets; db->n_residues = pk.n_residues; db->max_len = pk.max_len; db->entry_base = entry_base;
@@ -170,13 +137,17 @@ int swgpu_db_create(swgpu_db_t** out, int device, const int8_t* codes, const int
     if ((r = dalloc(db, &db->d_stream_off, (size_t)pk.n_streams + 1))) return r;
     if ((r = dalloc(db, &db->d_stream_ncols, (size_t)pk.n_streams))) return r;
     if ((r = dalloc(db, &db->d_stream_pair0, (size_t)pk.n_streams))) return r;
-    CU(cudaMemcpy(db->d_plain, pk.plain, (size_t)pk.n_residues, cudaMemcpyHostToDevice));
     CU(cudaMemcpy(db->d_plain_off, pk.plain_off, sizeof(int64_t) * ((size_t)pk.n_targets + 1), cudaMemcpyHostToDevice));
     CU(cudaMemcpy(db->d_order, pk.order, sizeof(int64_t) * (size_t)pk.n_targets, cudaMemcpyHostToDevice));
-    CU(cudaMemcpy(db->d_scols, pk.scols, sizeof(uint16_t) * (size_t)pk.scols_len, cudaMemcpyHostToDevice));
     CU(cudaMemcpy(db->d_stream_off, pk.stream_off, sizeof(int64_t) * ((size_t)pk.n_streams + 1), cudaMemcpyHostToDevice));
     CU(cudaMemcpy(db->d_stream_ncols, pk.stream_ncols, sizeof(int32_t) * (size_t)pk.n_streams, cudaMemcpyHostToDevice));
     CU(cudaMemcpy(db->d_stream_pair0, pk.stream_pair0, sizeof(int64_t) * (size_t)pk.n_streams, cudaMemcpyHostToDevice));
+    if (pk.plain && pk.scols) {
+      CU(cudaMemcpy(db->d_plain, pk.plain, (size_t)pk.n_residues, cudaMemcpyHostToDevice));
+      CU(cudaMemcpy(db->d_scols, pk.scols, sizeof(uint16_t) * (size_t)pk.scols_len, cudaMemcpyHostToDevice));
+    } else if ((r = fill(db))) {
+      return r;
+    }
     // persistent grids: k1s two CTAs of 8 warps per SM; k3 at most four CTAs of 4 warps per SM
     db->k1s_grid = db->sm_count * 3;                          // upper bound of resident k1s CTAs (carry-row slots)
     db->bnd_s_stride = ((long long)std::max<int32_t>(pk.max_stream_cols, 64) + 63) & ~63ll;
@@ -189,6 +160,105 @@ int swgpu_db_create(swgpu_db_t** out, int device, const int8_t* codes, const int
   swpack_free(&pk);
   if (rc != SWGPU_OK) { swgpu_db_destroy(db); return rc; }
   *out = db;
+  return SWGPU_OK;
+}
+
+static int pick_device(int device) {
+  int ndev = 0;
+  CU(cudaGetDeviceCount(&ndev));
+  if (ndev <= 0) return fail(SWGPU_ENODEV, "no CUDA device");
+  if (device < 0 || device >= ndev) return fail(SWGPU_EINVAL, "device %d out of range (%d devices)", device, ndev);
+  CU(cudaSetDevice(device));
+  return SWGPU_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int swgpu_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return n;
+}
+
+const char* swgpu_last_error(void) { return swi::err_buf(); }
+const char* swgpu_version(void) { return "swgpu 0.2 (sm_100a)"; }
+
+void swgpu_db_destroy(swgpu_db_t* db) {
+  if (!db) return;
+  cudaSetDevice(db->device);
+  cudaDeviceSynchronize();
+  cudaFree(db->d_plain); cudaFree(db->d_plain_off); cudaFree(db->d_order);
+  cudaFree(db->d_scols); cudaFree(db->d_stream_off); cudaFree(db->d_stream_ncols); cudaFree(db->d_stream_pair0);
+  for (auto& S : db->slots) swi::slot_release(S);
+  for (auto& e : db->ev_batch) if (e) cudaEventDestroy(e);
+  delete db;
+}
+
+int swgpu_db_create(swgpu_db_t** out, int device, const int8_t* codes, const int64_t* offsets,
+                    int64_t n_targets, int64_t entry_base, const swgpu_pack_opts_t* opts) {
+  if (!out || n_targets < 0 || (n_targets > 0 && (!codes || !offsets))) return fail(SWGPU_EINVAL, "swgpu_db_create: bad argument");
+  if (n_targets > 0x7ffffff0ll) return fail(SWGPU_EINVAL, "swgpu_db_create: more than 2^31 targets per GPU; shard the database");
+  *out = nullptr;
+  if (int r = pick_device(device)) return r;
+  const int stream_cols = (opts && opts->stream_cols > 0) ? opts->stream_cols : kDefaultStreamCols;
+  swpack_t pk;
+  static const int64_t zero_off[1] = {0};
+  if (swpack_build(&pk, codes, n_targets ? offsets : zero_off, n_targets, stream_cols) != 0)
+    return fail(SWGPU_EINVAL, "database packing failed (residue code outside 0..31, negative length, or out of memory)");
+  return db_from_pack(out, device, pk, entry_base, opts, [](swgpu_db*) { return (int)SWGPU_OK; });
+}
+
+int swgpu_db_create_synthetic(swgpu_db_t** out, int device, const int32_t* lengths, const int64_t* entry_ids,
+                              int64_t n_targets, int64_t entry_base, const swgpu_synth_t* gen, const swgpu_pack_opts_t* opts) {
+  if (!out || n_targets < 0 || (n_targets > 0 && !lengths) || !gen) return fail(SWGPU_EINVAL, "swgpu_db_create_synthetic: bad argument");
+  if (n_targets > 0x7ffffff0ll) return fail(SWGPU_EINVAL, "swgpu_db_create_synthetic: more than 2^31 targets per GPU; shard the database");
+  if (gen->n_letters < 1 || gen->n_letters > 32) return fail(SWGPU_EINVAL, "swgpu_db_create_synthetic: n_letters must be 1..32");
+  for (int i = 0; i < gen->n_letters; ++i) {
+    if (gen->codes[i] < 1 || gen->codes[i] > 31) return fail(SWGPU_EINVAL, "swgpu_db_create_synthetic: residue code outside 1..31");
+    if (gen->cdf[i] > 65536u || (i && gen->cdf[i] < gen->cdf[i - 1])) return fail(SWGPU_EINVAL, "swgpu_db_create_synthetic: cdf must be non-decreasing, <= 65536");
+  }
+  if (gen->cdf[gen->n_letters - 1] != 65536u) return fail(SWGPU_EINVAL, "swgpu_db_create_synthetic: cdf must end at 65536");
+  *out = nullptr;
+  if (int r = pick_device(device)) return r;
+  const int stream_cols = (opts && opts->stream_cols > 0) ? opts->stream_cols : kDefaultStreamCols;
+  swpack_t pk;
+  std::vector<int64_t> pair_col((size_t)(n_targets + 1) / 2 + 1);
+  static const int32_t zero_len[1] = {0};
+  if (swpack_layout(&pk, n_targets ? lengths : zero_len, n_targets, stream_cols, pair_col.data()) != 0)
+    return fail(SWGPU_EINVAL, "database layout failed (negative length or out of memory)");
+  auto fill = [&](swgpu_db* db) -> int {
+    // the residues exist only on the device: generated straight into `plain` (sorted order), then paired into streams
+    int64_t *d_ids = nullptr, *d_pair_col = nullptr;
+    auto body = [&]() -> int {
+      if (entry_ids) {
+        CU(cudaMalloc((void**)&d_ids, sizeof(int64_t) * (size_t)std::max<int64_t>(n_targets, 1)));
+        CU(cudaMemcpy(d_ids, entry_ids, sizeof(int64_t) * (size_t)n_targets, cudaMemcpyHostToDevice));
+      }
+      CU(cudaMalloc((void**)&d_pair_col, sizeof(int64_t) * pair_col.size()));
+      CU(cudaMemcpy(d_pair_col, pair_col.data(), sizeof(int64_t) * pair_col.size(), cudaMemcpyHostToDevice));
+      CU(cudaMemset(db->d_scols, 0, sizeof(uint16_t) * ((size_t)pk.scols_len + 64)));
+      CU(swi::synth_fill(db, *gen, d_ids, entry_base, d_pair_col));
+      CU(cudaDeviceSynchronize());
+      return SWGPU_OK;
+    };
+    const int r = body();
+    cudaFree(d_ids); cudaFree(d_pair_col);
+    return r;
+  };
+  return db_from_pack(out, device, pk, entry_base, opts, fill);
+}
+
+int swgpu_db_fetch_target(swgpu_db_t* db, int64_t local_entry, int8_t* out, int64_t cap, int64_t* len) {
+  if (!db || local_entry < 0 || local_entry >= db->n || !len) return fail(SWGPU_EINVAL, "swgpu_db_fetch_target: bad argument");
+  const size_t s = (size_t)db->h_inv_order[(size_t)local_entry];
+  const int64_t b = db->h_len_sorted_prefix[s], L = db->h_len_sorted_prefix[s + 1] - b;
+  *len = L;
+  if (!out) return SWGPU_OK;                       // length query
+  if (cap < L) return fail(SWGPU_EINVAL, "swgpu_db_fetch_target: buffer too small (%lld needed)", (long long)L);
+  CU(cudaSetDevice(db->device));
+  CU(cudaMemcpy(out, db->d_plain + b, (size_t)L, cudaMemcpyDeviceToHost));
   return SWGPU_OK;
 }
 

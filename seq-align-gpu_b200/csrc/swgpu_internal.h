@@ -105,4 +105,7 @@ void slot_release(swgpu_slot& S);
 int k3x_prepare(swgpu_db* db, swgpu_slot& S, int lq, cudaStream_t stream);   // (re)allocate + zero the k3x slot state
 int enqueue_topk(swgpu_db* db, swgpu_slot& S, int k);                  // no host synchronisation
 int collect_topk(swgpu_db* db, swgpu_slot& S, swgpu_hit_t* hits, int* n_hits);   // after S.ev[11] has completed
+// swgpu_synth.cu: generate the residues of a layout-only database into d_plain, then pair them into d_scols
+cudaError_t synth_fill(swgpu_db* db, const swgpu_synth_t& gen, const int64_t* d_entry_ids, int64_t entry_base,
+                       const int64_t* d_pair_col);
 }  // namespace swi

@@ -49,6 +49,11 @@ class BatchStats(C.Structure):
         return {k: getattr(self, k) for k, _ in self._fields_ if k != "reserved"}
 
 
+class SynthGen(C.Structure):
+    _fields_ = [("seed", C.c_uint64), ("n_letters", C.c_int32), ("reserved", C.c_int32),
+                ("cdf", C.c_uint32 * 32), ("codes", C.c_int8 * 32)]
+
+
 class PackOpts(C.Structure):
     _fields_ = [("long_threshold", C.c_int32), ("stream_cols", C.c_int32), ("reserved", C.c_int32 * 6)]
 
@@ -71,6 +76,11 @@ def lib():
     L.swgpu_version.restype = C.c_char_p
     L.swgpu_db_create.restype = C.c_int
     L.swgpu_db_create.argtypes = [P(C.c_void_p), C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p]
+    L.swgpu_db_create_synthetic.restype = C.c_int
+    L.swgpu_db_create_synthetic.argtypes = [P(C.c_void_p), C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64,
+                                            P(SynthGen), C.c_void_p]
+    L.swgpu_db_fetch_target.restype = C.c_int
+    L.swgpu_db_fetch_target.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, P(C.c_int64)]
     L.swgpu_db_destroy.argtypes = [C.c_void_p]
     L.swgpu_db_destroy.restype = None
     for f in ("swgpu_db_num_targets", "swgpu_db_num_residues", "swgpu_db_device_bytes"):
@@ -122,6 +132,39 @@ class Database:
         _check(L.swgpu_db_create(C.byref(h), device, pc, self._off.ctypes.data_as(C.c_void_p), self.n, entry_base,
                                  C.byref(opts)))
         self._h = h
+
+    @classmethod
+    def synthetic(cls, lengths, seed, entry_ids=None, entry_base=0, spec=None, device=0, long_threshold=0, stream_cols=0):
+        """swgpu_db_create_synthetic(): the residues are generated on the device from (seed, global entry id, position);
+        swgpu.synth.synth_target() is the host mirror."""
+        from . import synth
+        cdf, cd, nl = spec or synth.synth_spec()
+        self = cls.__new__(cls)
+        self._lens = np.ascontiguousarray(lengths, dtype=np.int32)
+        self._ids = None if entry_ids is None else np.ascontiguousarray(entry_ids, dtype=np.int64)
+        self.n = len(self._lens)
+        gen = SynthGen(seed=int(seed), n_letters=int(nl))
+        for i in range(32):
+            gen.cdf[i] = int(cdf[i]); gen.codes[i] = int(cd[i])
+        opts = PackOpts(long_threshold=long_threshold, stream_cols=stream_cols)
+        h = C.c_void_p()
+        _check(lib().swgpu_db_create_synthetic(C.byref(h), device, self._lens.ctypes.data_as(C.c_void_p),
+                                               None if self._ids is None else self._ids.ctypes.data_as(C.c_void_p),
+                                               self.n, int(entry_base), C.byref(gen), C.byref(opts)))
+        self._h = h
+        return self
+
+    def fetch_target(self, local_entry):
+        """Residues of one target as they sit in the packed database on the device."""
+        ln = C.c_int64(0)
+        _check(lib().swgpu_db_fetch_target(self._h, int(local_entry), None, 0, C.byref(ln)))
+        out = np.empty(ln.value, dtype=np.int8)
+        _check(lib().swgpu_db_fetch_target(self._h, int(local_entry), out.ctypes.data_as(C.c_void_p), out.size, C.byref(ln)))
+        return out
+
+    @property
+    def n_residues(self):
+        return lib().swgpu_db_num_residues(self._h)
 
     def close(self):
         if getattr(self, "_h", None):

@@ -107,3 +107,71 @@ def load_matrix(path):
                 tab[r, c] = int(v)
     diag = np.array([1 if (i in cols) else 0 for i in range(32)], dtype=np.uint8)
     return tab, diag
+
+
+# ---- device-generated databases (swgpu_db_create_synthetic, include/swgpu.h) ----------------
+_M64 = np.uint64(0xFFFFFFFFFFFFFFFF)
+
+
+def synth_spec(freq=FREQ, codes=CODES):
+    """(cdf uint32[32], codes int8[32], n_letters): cumulative thresholds out of 65536 for the 16-bit draw."""
+    c = np.floor(np.cumsum(freq) * 65536.0 + 0.5).astype(np.int64)
+    c[-1] = 65536
+    cdf = np.zeros(32, dtype=np.uint32); cdf[: len(c)] = c
+    cd = np.zeros(32, dtype=np.int8); cd[: len(codes)] = codes
+    return cdf, cd, len(codes)
+
+
+def _mix64(x):
+    x = x ^ (x >> np.uint64(30)); x = x * np.uint64(0xBF58476D1CE4E5B9)
+    x = x ^ (x >> np.uint64(27)); x = x * np.uint64(0x94D049BB133111EB)
+    return x ^ (x >> np.uint64(31))
+
+
+def synth_target(seed, entry, length, spec=None):
+    """Host mirror of the device generator: the residues of the target with global entry id `entry`."""
+    cdf, cd, n = spec or synth_spec()
+    with np.errstate(over="ignore"):
+        key = np.uint64(seed) ^ (np.uint64(entry) * np.uint64(0x9E3779B97F4A7C15))
+        j = np.arange(1, int(length) + 1, dtype=np.uint64)
+        u = (_mix64(key + j * np.uint64(0xBF58476D1CE4E5B9)) >> np.uint64(48)).astype(np.int64)
+    i = np.minimum(np.searchsorted(cdf[:n].astype(np.int64), u, side="right"), n - 1)
+    return cd[i]
+
+
+C5_SEED = 46
+C5_TOTAL_RESIDUES = 10_000_000_000
+
+
+def c5_lengths(scale=1.0, seed=C5_SEED):
+    """C5: UniRef50-shaped lengths, LogNormal(ln 230, 0.75) clipped to [11, 35 213] (mean ~305), ~32.8 M targets for
+    10 G residues at scale 1; entry 0 is forced to the maximum when the database is big enough to carry it."""
+    n = max(64, int(round(C5_TOTAL_RESIDUES * scale / 304.9)))
+    lens = lognormal_lengths(rng(seed), n, median=230.0, sigma=0.75, lo=11, hi=35213).astype(np.int32)
+    if scale >= 0.001:
+        lens[0] = 35213
+    return lens
+
+
+def c5_queries(lens, n_queries=64, seed=C5_SEED, spec=None, min_len=200, identity=0.9):
+    """64 queries with lengths cycling through the C2 list.  Query i carries a mutated copy (90 % identity) of the
+    first min(Lq, Lt) residues of one database target (entry planted[i], the first target of >= min_len residues at
+    or after i * n / n_queries), so every query has a known best hit whatever the size of the database."""
+    n = len(lens)
+    qs, planted = [], []
+    for i in range(n_queries):
+        lq = C2_QUERY_LENGTHS[i % len(C2_QUERY_LENGTHS)]
+        g = rng(4600 + i)
+        q = residues(g, lq)
+        e = (i * n) // n_queries
+        while lens[e] < min_len:
+            e = (e + 1) % n
+        t = synth_target(seed, e, int(lens[e]), spec)
+        m = min(lq, len(t))
+        a = int(g.integers(0, lq - m + 1))
+        seg = t[:m].copy()
+        mut = g.random(m) >= identity
+        seg[mut] = residues(g, int(mut.sum()))
+        q[a:a + m] = seg
+        qs.append(q); planted.append(e)
+    return qs, planted

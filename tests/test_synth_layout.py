@@ -1,0 +1,135 @@
+"""CPU suite: host logic of the device-generated databases (swgpu_db_create_synthetic).
+
+  * db_pack.c::swpack_layout (layout from lengths alone) produces exactly the tables swpack_build produces from real
+    residues, and its pair_col[] points at the flagged first column of every pair in swpack_build's streams;
+  * the host mirror of the generator (swgpu.synth.synth_target) is deterministic, depends on (seed, entry, position)
+    only, and draws the Swiss-Prot background composition;
+  * the C5 workload definition (lengths, planted queries) has the shape SURVEY.md 8(d) names;
+  * swgpu_db_create_synthetic fails loudly without a CUDA device (no CPU fallback).
+No GPU work is launched."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+
+class SwPack(C.Structure):
+    _fields_ = [("n_targets", C.c_int64), ("n_residues", C.c_int64), ("max_len", C.c_int32),
+                ("order", C.POINTER(C.c_int64)), ("plain_off", C.POINTER(C.c_int64)), ("plain", C.POINTER(C.c_int8)),
+                ("n_pairs", C.c_int64), ("n_streams", C.c_int64), ("max_stream_cols", C.c_int32),
+                ("n_long_streams", C.c_int64), ("n_long_pairs", C.c_int64),
+                ("scols", C.POINTER(C.c_uint16)), ("scols_len", C.c_int64),
+                ("stream_off", C.POINTER(C.c_int64)), ("stream_ncols", C.POINTER(C.c_int32)),
+                ("stream_pair0", C.POINTER(C.c_int64))]
+
+
+def arr(ptr, n, dtype):
+    return np.ctypeslib.as_array(ptr, shape=(max(int(n), 1),))[: int(n)].astype(dtype).copy()
+
+
+@pytest.mark.parametrize("seed,n,stream_cols", [(1, 1, 1536), (2, 2, 1536), (3, 257, 64), (4, 5000, 1536), (5, 4001, 300)])
+def test_layout_from_lengths_matches_the_packer(seed, n, stream_cols):
+    import swgpu
+    from swgpu import synth
+    L = swgpu.lib()
+    g = synth.rng(seed)
+    lens = synth.lognormal_lengths(g, n, median=230.0, sigma=0.75, lo=0 if seed == 3 else 11, hi=35213).astype(np.int32)
+    if n > 100:
+        lens[7] = 9000; lens[8] = 0                           # a long stream of its own, an empty target
+    off = np.zeros(n + 1, dtype=np.int64); np.cumsum(lens, out=off[1:])
+    codes = synth.residues(g, int(off[-1]))
+    a, b = SwPack(), SwPack()
+    assert L.swpack_build(C.byref(a), codes.ctypes.data_as(C.c_void_p), off.ctypes.data_as(C.c_void_p), C.c_int64(n),
+                          C.c_int32(stream_cols)) == 0
+    pair_col = np.zeros((n + 1) // 2 + 1, dtype=np.int64)
+    assert L.swpack_layout(C.byref(b), lens.ctypes.data_as(C.c_void_p), C.c_int64(n), C.c_int32(stream_cols),
+                           pair_col.ctypes.data_as(C.c_void_p)) == 0
+    try:
+        for f in ("n_targets", "n_residues", "max_len", "n_pairs", "n_streams", "max_stream_cols", "n_long_streams",
+                  "n_long_pairs", "scols_len"):
+            assert getattr(a, f) == getattr(b, f), f
+        assert not b.plain and not b.scols                     # layout only
+        assert np.array_equal(arr(a.order, n, np.int64), arr(b.order, n, np.int64))
+        assert np.array_equal(arr(a.plain_off, n + 1, np.int64), arr(b.plain_off, n + 1, np.int64))
+        ns = a.n_streams
+        assert np.array_equal(arr(a.stream_off, ns + 1, np.int64), arr(b.stream_off, ns + 1, np.int64))
+        assert np.array_equal(arr(a.stream_ncols, ns, np.int32), arr(b.stream_ncols, ns, np.int32))
+        assert np.array_equal(arr(a.stream_pair0, ns, np.int64), arr(b.stream_pair0, ns, np.int64))
+        # pair_col: the flagged columns of the packer's streams, in pair order
+        scols = arr(a.scols, a.scols_len, np.uint16)
+        flagged = np.flatnonzero(scols & 0x80)
+        assert np.array_equal(flagged, pair_col[: a.n_pairs])
+        # and the pair's columns there are its two members, as the device kernel will write them
+        order, poff, plain = arr(a.order, n, np.int64), arr(a.plain_off, n + 1, np.int64), arr(a.plain, a.n_residues, np.int8)
+        for q in range(0, int(a.n_pairs), max(1, int(a.n_pairs) // 50)):
+            la = int(poff[2 * q + 1] - poff[2 * q]); lb = int(poff[2 * q + 2] - poff[2 * q + 1]) if 2 * q + 1 < n else 0
+            col = scols[pair_col[q]: pair_col[q] + max(la, 1)].astype(np.int64)
+            lo = np.zeros(max(la, 1), dtype=np.int64); lo[:la] = plain[poff[2 * q]: poff[2 * q] + la]
+            hi = np.zeros(max(la, 1), dtype=np.int64); hi[:lb] = plain[poff[2 * q + 1]: poff[2 * q + 1] + lb]
+            want = lo | (hi << 8); want[0] |= 0x80
+            assert np.array_equal(col, want), q
+    finally:
+        L.swpack_free(C.byref(a)); L.swpack_free(C.byref(b))
+
+
+def test_generator_mirror_is_a_pure_function_of_seed_entry_position():
+    from swgpu import synth
+    spec = synth.synth_spec()
+    cdf, cd, nl = spec
+    assert nl == 20 and cdf[nl - 1] == 65536 and np.all(np.diff(cdf[:nl].astype(np.int64)) > 0)
+    a = synth.synth_target(46, 12345, 500, spec)
+    assert np.array_equal(a, synth.synth_target(46, 12345, 500, spec))
+    assert np.array_equal(a[:200], synth.synth_target(46, 12345, 200, spec))          # prefix property
+    assert not np.array_equal(a, synth.synth_target(46, 12346, 500, spec))
+    assert not np.array_equal(a, synth.synth_target(47, 12345, 500, spec))
+    assert set(np.unique(a)) <= set(int(c) for c in synth.CODES)
+    # known answer, frozen, and the formula of include/swgpu.h restated with Python integers
+    assert synth.synth_target(46, 0, 12, spec).tolist() == [1, 4, 12, 1, 16, 22, 20, 19, 19, 5, 17, 19]
+    for seed, e, ln in ((46, 0, 40), (46, 32_797_638, 64), (2**63 + 11, 2**40 + 7, 33)):
+        assert synth.synth_target(seed, e, ln, spec).tolist() == plain_python_target(seed, e, ln, spec)
+    big = synth.synth_target(1, 2**40 + 7, 400_000, spec)
+    freq = np.array([(big == c).mean() for c in synth.CODES])
+    assert np.abs(freq - synth.FREQ).max() < 0.003
+
+
+def plain_python_target(seed, entry, length, spec):
+    cdf, cd, nl = spec
+    M = (1 << 64) - 1
+    out = []
+    for j in range(length):
+        x = ((seed ^ (entry * 0x9E3779B97F4A7C15 & M)) + (j + 1) * 0xBF58476D1CE4E5B9) & M
+        x ^= x >> 30; x = x * 0xBF58476D1CE4E5B9 & M
+        x ^= x >> 27; x = x * 0x94D049BB133111EB & M
+        x ^= x >> 31
+        u = x >> 48
+        i = 0
+        while i < nl - 1 and u >= int(cdf[i]):
+            i += 1
+        out.append(int(cd[i]))
+    return out
+
+
+def test_c5_workload_shape():
+    from swgpu import synth
+    lens = synth.c5_lengths(0.001)
+    assert lens.dtype == np.int32 and lens.min() >= 11 and lens.max() == 35213 and lens[0] == 35213
+    assert abs(lens.astype(np.int64).sum() / (synth.C5_TOTAL_RESIDUES * 0.001) - 1) < 0.02
+    assert abs(lens.mean() - 305) < 8
+    qs, planted = synth.c5_queries(lens, 64)
+    assert [len(q) for q in qs] == [synth.C2_QUERY_LENGTHS[i % 20] for i in range(64)]
+    assert len(set(planted)) == 64 and all(lens[e] >= 200 for e in planted)
+    # the planted segment is really there: >= 80 % identity with the target's head somewhere in the query
+    for i in (0, 9, 37):
+        t = synth.synth_target(synth.C5_SEED, planted[i], int(lens[planted[i]]))
+        m = min(len(qs[i]), len(t))
+        best = max(float((qs[i][a:a + m] == t[:m]).mean()) for a in range(len(qs[i]) - m + 1))
+        assert best > 0.8, (i, best)
+
+
+def test_synthetic_create_fails_loudly_without_a_device():
+    import swgpu
+    if swgpu.lib().swgpu_device_count() > 0:
+        pytest.skip("a CUDA device is present")
+    with pytest.raises(swgpu.SwgpuError) as e:
+        swgpu.Database.synthetic(np.array([10, 20], dtype=np.int32), 46)
+    assert "swgpu error -1" in str(e.value) or "swgpu error -2" in str(e.value)
