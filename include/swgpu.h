@@ -40,7 +40,10 @@ typedef struct swgpu_db swgpu_db_t;   /* packed, HBM-resident database on one GP
 typedef struct {
     int32_t long_threshold;   /* > 0: targets longer than this are always scored by the 32-bit kernels */
     int32_t stream_cols;      /* length of one stream of concatenated target pairs (16-bit kernel); default 1536 */
-    int32_t reserved[6];
+    int32_t no_taper;         /* != 0: every stream gets stream_cols columns (default: the streams of the last 1/16 of the
+                                 database are half as long, those of the last 1/64 a quarter -- smaller work units at the
+                                 end of the kernel's work queue) */
+    int32_t reserved[5];
 } swgpu_pack_opts_t;
 
 /* Per-search statistics, all device-timed with CUDA events on the engine's stream. */

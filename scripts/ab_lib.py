@@ -25,10 +25,28 @@ def child(reps):
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("--a"); ap.add_argument("--b"); ap.add_argument("--rounds", type=int, default=2)
+    ap.add_argument("--libs", help="comma-separated list of more than two builds (replaces --a/--b); the first is the baseline")
     ap.add_argument("--reps", type=int, default=3); ap.add_argument("--child", action="store_true")
     a = ap.parse_args()
     if a.child:
         child(a.reps); sys.exit(0)
+    if a.libs:
+        libs = a.libs.split(",")
+        res = {l: [] for l in libs}
+        for r in range(a.rounds):
+            for l in libs:
+                env = dict(os.environ, SWGPU_LIB=os.path.abspath(l))
+                o = subprocess.run([sys.executable, __file__, "--child", "--reps", str(a.reps)], env=env, capture_output=True, text=True)
+                if o.returncode:
+                    print(o.stderr[-2000:]); sys.exit(1)
+                d = json.loads(o.stdout.strip().splitlines()[-1]); res[l].append(d)
+                print(json.dumps({"lib": os.path.basename(l), "many_ms": d["many_ms"]}), flush=True)
+        best = lambda l, lq: min(d["ms"][str(lq)] for d in res[l])
+        for lq in LQS:
+            base = best(libs[0], lq)
+            print(json.dumps({"lq": lq, "base_ms": base} | {os.path.basename(l)[9:-3]: round(best(l, lq) / base, 4) for l in libs[1:]}))
+        print(json.dumps({os.path.basename(l): min(d["many_ms"] for d in res[l]) for l in libs}))
+        sys.exit(0)
     res = {"a": [], "b": []}
     for r in range(a.rounds):
         for key in ("a", "b"):

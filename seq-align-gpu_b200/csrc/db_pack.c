@@ -11,10 +11,10 @@ void swpack_free(swpack_t *p)
     memset(p, 0, sizeof(*p));
 }
 
-static int layout_streams(swpack_t *p, int32_t stream_cols, int64_t *pair_col);
+static int layout_streams(swpack_t *p, int32_t stream_cols, int32_t taper, int64_t *pair_col);
 static int fill_streams(swpack_t *p);
 
-int swpack_build(swpack_t *p, const int8_t *codes, const int64_t *offsets, int64_t n, int32_t stream_cols)
+int swpack_build(swpack_t *p, const int8_t *codes, const int64_t *offsets, int64_t n, int32_t stream_cols, int32_t taper)
 {
     memset(p, 0, sizeof(*p));
     if (n < 0) return -1;
@@ -55,13 +55,13 @@ int swpack_build(swpack_t *p, const int8_t *codes, const int64_t *offsets, int64
     }
     if (bad) { swpack_free(p); return -1; }
 
-    if (layout_streams(p, stream_cols, NULL) != 0) return -1;
+    if (layout_streams(p, stream_cols, taper, NULL) != 0) return -1;
     return fill_streams(p);
 }
 
 /* Layout only: the database is described by its target lengths; `plain` and `scols` stay NULL (the caller fills
  * them on the device).  pair_col[n_pairs] receives the first stream column of every pair. */
-int swpack_layout(swpack_t *p, const int32_t *lengths, int64_t n, int32_t stream_cols, int64_t *pair_col)
+int swpack_layout(swpack_t *p, const int32_t *lengths, int64_t n, int32_t stream_cols, int32_t taper, int64_t *pair_col)
 {
     memset(p, 0, sizeof(*p));
     if (n < 0) return -1;
@@ -84,41 +84,60 @@ int swpack_layout(swpack_t *p, const int32_t *lengths, int64_t n, int32_t stream
     free(bucket);
     p->plain_off[0] = 0;
     for (int64_t s = 0; s < n; s++) p->plain_off[s + 1] = p->plain_off[s] + lengths[p->order[s]];
-    return layout_streams(p, stream_cols, pair_col);
+    return layout_streams(p, stream_cols, taper, pair_col);
+}
+
+/* Length limit of a stream that starts with `remaining` of `total` columns still to place.  With `taper` the streams
+ * of the last 1/16 of the database are half as long and those of the last 1/64 a quarter: a stream (times the query
+ * stripes) is the unit of the kernel's work queue, and equal-sized units leave the GPU partly idle for up to one unit
+ * at the end of every launch (measured: 2-6 % of a multi-stripe launch on the C2 database).  The short targets live
+ * at the end of the sorted database, so the shorter streams still hold many pairs each. */
+static int64_t stream_limit(int64_t stream_cols, int32_t taper, int64_t remaining, int64_t total)
+{
+    if (!taper) return stream_cols;
+    int64_t lim = stream_cols;
+    if (remaining <= total / 64) lim = stream_cols / 4;
+    else if (remaining <= total / 16) lim = stream_cols / 2;
+    return lim < 64 ? 64 : lim;
 }
 
 /* 3. streams of paired targets for the systolic kernel (see db_pack.h): the stream tables from the lengths ... */
-static int layout_streams(swpack_t *p, int32_t stream_cols, int64_t *pair_col)
+static int layout_streams(swpack_t *p, int32_t stream_cols, int32_t taper, int64_t *pair_col)
 {
     const int64_t n = p->n_targets;
     const int64_t n_pairs = (n + 1) / 2;
     p->n_pairs = n_pairs;
     if (stream_cols < 32) stream_cols = 32;
+    int64_t total = 0;
+    for (int64_t q = 0; q < n_pairs; q++) {
+        const int64_t len = p->plain_off[2 * q + 1] - p->plain_off[2 * q];
+        total += len < 1 ? 1 : len;
+    }
     /* pass 1: count streams.  pair length = its first (longer) member; an empty pair still takes one
      * (flagged, all-padding) column so that every pair has a flush point */
-    int64_t n_streams = 0, cur = 0;
+    int64_t n_streams = 0, cur = 0, done = 0, limit = stream_cols;
     for (int64_t q = 0; q < n_pairs; q++) {
         int64_t len = p->plain_off[2 * q + 1] - p->plain_off[2 * q];
         if (len < 1) len = 1;
-        if (cur == 0) n_streams++;
-        cur += len;
-        if (cur >= stream_cols) cur = 0;
+        if (cur == 0) { n_streams++; limit = stream_limit(stream_cols, taper, total - done, total); }
+        cur += len; done += len;
+        if (cur >= limit) cur = 0;
     }
     p->n_streams = n_streams;
     p->stream_off = (int64_t *)malloc(sizeof(int64_t) * (size_t)(n_streams + 1));
     p->stream_ncols = (int32_t *)malloc(sizeof(int32_t) * (size_t)(n_streams ? n_streams : 1));
     p->stream_pair0 = (int64_t *)malloc(sizeof(int64_t) * (size_t)(n_streams ? n_streams : 1));
     if (!p->stream_off || !p->stream_ncols || !p->stream_pair0) { swpack_free(p); return -1; }
-    int64_t s = -1, off = 0; cur = 0;
+    int64_t s = -1, off = 0; cur = 0; done = 0;
     int32_t maxc = 0;
     for (int64_t q = 0; q < n_pairs; q++) {
         int64_t len = p->plain_off[2 * q + 1] - p->plain_off[2 * q];
         if (len < 1) len = 1;
-        if (cur == 0) { s++; p->stream_off[s] = off; p->stream_pair0[s] = q; }
+        if (cur == 0) { s++; p->stream_off[s] = off; p->stream_pair0[s] = q; limit = stream_limit(stream_cols, taper, total - done, total); }
         if (pair_col) pair_col[q] = off + cur;
-        cur += len;
+        cur += len; done += len;
         if (cur > 0x7fffff00) { swpack_free(p); return -1; }
-        if (cur >= stream_cols || q == n_pairs - 1) {
+        if (cur >= limit || q == n_pairs - 1) {
             p->stream_ncols[s] = (int32_t)cur;
             if (cur > maxc) maxc = (int32_t)cur;
             off += (cur + 63) & ~(int64_t)63;

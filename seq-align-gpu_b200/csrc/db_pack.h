@@ -13,7 +13,8 @@
  *     target 2p (bit 7 set on the first column of a pair), high byte = code of target 2p+1
  *     (0 once the shorter one has ended; code 0 = padding, which can never score -- the
  *     reference pads with '*' = 31, :448-450).  A pair never straddles two streams; a pair
- *     longer than stream_cols is a stream of its own.
+ *     longer than stream_cols is a stream of its own.  With `taper` the streams of the last 1/16 of the columns are
+ *     half as long and those of the last 1/64 a quarter (smaller work units at the end of the kernel's queue).
  */
 #ifndef SWGPU_DB_PACK_H
 #define SWGPU_DB_PACK_H
@@ -43,11 +44,11 @@ typedef struct {
 } swpack_t;
 
 /* returns 0, or -1 on allocation failure / bad input (negative length, code outside 0..31) */
-int  swpack_build(swpack_t *p, const int8_t *codes, const int64_t *offsets, int64_t n_targets, int32_t stream_cols);
+int  swpack_build(swpack_t *p, const int8_t *codes, const int64_t *offsets, int64_t n_targets, int32_t stream_cols, int32_t taper);
 /* Same layout from target lengths alone (synthetic databases whose residues are generated on the device):
  * order, plain_off and the stream tables are filled, plain and scols stay NULL; pair_col[(n+1)/2] (may be NULL)
  * receives the first column of every pair in scols. */
-int  swpack_layout(swpack_t *p, const int32_t *lengths, int64_t n_targets, int32_t stream_cols, int64_t *pair_col);
+int  swpack_layout(swpack_t *p, const int32_t *lengths, int64_t n_targets, int32_t stream_cols, int32_t taper, int64_t *pair_col);
 void swpack_free(swpack_t *p);
 
 #ifdef __cplusplus

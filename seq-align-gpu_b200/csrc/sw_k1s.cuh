@@ -122,13 +122,27 @@ __device__ __forceinline__ void k1s_st_release(unsigned* p, unsigned v) {
 constexpr unsigned K1S_SPIN_LIMIT = 1u << 24;
 
 constexpr int K1S_WARPS = 8;
+
+// Per-step overhead variants (A/B knobs, scripts/build_variant.sh):
+//   K1S_RING32   32-bit double-mapped column ring ([R + UR] addressing, profile offsets by IDP.2A) vs the 16-bit ring
+//   K1S_SHFLP    the shuffle's range predicate selects the first lane's default vs a separate compare
+//   K1S_RINGLD   0 = ordered inline-asm ring load, 1 = plain C++ load
+#ifndef K1S_RING32
+#define K1S_RING32 1
+#endif
+#ifndef K1S_SHFLP
+#define K1S_SHFLP 1
+#endif
+#ifndef K1S_RINGLD
+#define K1S_RINGLD 0
+#endif
 #ifndef K1S_R3CTA
 #define K1S_R3CTA 18                         // R up to this: three CTAs per SM (<= 85 registers per thread)
 #endif
 
 template <int R, bool MULTI>
 constexpr size_t k1s_smem_bytes() {
-  return (size_t)SProf<R, MULTI>::WORDS * 4 + (size_t)K1S_WARPS * (128 * 2 + 32 * 8) + 16;
+  return (size_t)SProf<R, MULTI>::WORDS * 4 + (size_t)K1S_WARPS * (128 * 4 + 32 * 8) + 16;
 }
 
 // LANES = lanes per target pair (g), a compile-time constant (shuffle widths, ring masks and the block period fold into
@@ -144,17 +158,27 @@ __global__ void __launch_bounds__(K1S_WARPS * 32, (R <= K1S_R3CTA ? 3 : 2)) k1s(
   extern __shared__ __align__(16) unsigned smem_u32[];
   unsigned* prof_s = smem_u32;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  unsigned short* ring = reinterpret_cast<unsigned short*>(smem_u32 + S::WORDS) + warp * 128;
-  uint2* ring2 = reinterpret_cast<uint2*>(reinterpret_cast<unsigned short*>(smem_u32 + S::WORDS) + K1S_WARPS * 128) + warp * 32;
+  // Column ring: 128 words per warp.  A group's segment holds RN = 2g columns, each stored TWICE (at p and p + RN), so
+  // that the read index (s mod RN) - lane_g + RN never wraps: the address is a per-lane constant plus a warp-uniform
+  // term, no per-lane arithmetic per step.  A ring word is (code of the low target | code of the high target << 8 |
+  // first-column flag << 31): the two profile addresses come out of it with one IDP.2A each (FMA pipe).
+  constexpr bool RING32 = K1S_RING32 != 0, SHFLP = K1S_SHFLP != 0;
+  unsigned* ring = smem_u32 + S::WORDS + warp * 128;
+  uint2* ring2 = reinterpret_cast<uint2*>(smem_u32 + S::WORDS + K1S_WARPS * 128) + warp * 32;
   __shared__ unsigned cta_item;
 
   constexpr int g = LANES, g_log2 = (LANES == 8 ? 3 : LANES == 16 ? 4 : 5);
   const int lane_g = lane & (g - 1), grp = lane >> g_log2, per_warp = 32 >> g_log2;
-  constexpr int rmask = 4 * g - 1;                       // ring of 4g columns per group (g-step blocks, generous slack)
-  unsigned short* gring = ring + grp * (4 * g);
+  constexpr int RN = 2 * g;
+  unsigned* gring = ring + grp * (2 * RN);
+  const unsigned* gring_rd = gring + (RN - lane_g);
+  const unsigned rd_lane = (unsigned)__cvta_generic_to_shared(gring_rd);
+  constexpr int rmask = 4 * g - 1;                       // 16-bit ring: 4g columns per group
+  unsigned short* gring16 = reinterpret_cast<unsigned short*>(ring) + grp * (4 * g);
   const unsigned BB = P.BB, BBM = P.BBM, OE2 = P.OE2, GE2 = P.GE2;
   const unsigned pa_lane = (unsigned)__cvta_generic_to_shared(prof_s) + lane * (S::PAIRED ? 8 : 4);
   const unsigned pb_lane = pa_lane + 32 * S::WA * 128;
+  constexpr unsigned MUL_A = (unsigned)(S::WA * 128), MUL_B = (unsigned)(S::WB * 128) << 16;
   uint2* bnd = MULTI ? P.bnd + (size_t)(blockIdx.x * K1S_WARPS + warp) * (size_t)P.bnd_stride : nullptr;
 
   auto load_profile = [&](int pass) {
@@ -232,6 +256,7 @@ __global__ void __launch_bounds__(K1S_WARPS * 32, (R <= K1S_R3CTA ? 3 : 2)) k1s(
       long pair_idx = pair0 - 1;
       __syncwarp();
       for (int i = lane; i < 128; i += 32) ring[i] = 0;
+      auto ring_word = [](unsigned c) { return (c & 0x1f1fu) | ((c & 0x80u) << 24); };
       unsigned pre = (lane_g < ncols) ? (unsigned)cp[lane_g] : 0u;
       uint2 pre_b = make_uint2(BB, BBM);
       if (MULTI && !first) {
@@ -254,7 +279,8 @@ __global__ void __launch_bounds__(K1S_WARPS * 32, (R <= K1S_R3CTA ? 3 : 2)) k1s(
       for (int s = 0; s < nsteps; ++s) {
         if ((s & (g - 1)) == 0) {                  // every g steps: publish the prefetched block, fetch the next
           __syncwarp();
-          gring[(s + lane_g) & rmask] = (unsigned short)pre;
+          if (RING32) { const int p = (s & (RN - 1)) + lane_g; const unsigned w = ring_word(pre); gring[p] = w; gring[p + RN] = w; }
+          else gring16[(s + lane_g) & rmask] = (unsigned short)pre;
           const int c = s + g + lane_g;
           pre = (c < ncols) ? (unsigned)cp[c] : 0u;
           if (MULTI) {
@@ -268,21 +294,29 @@ __global__ void __launch_bounds__(K1S_WARPS * 32, (R <= K1S_R3CTA ? 3 : 2)) k1s(
           }
           __syncwarp();
         }
-        const unsigned cw = gring[(s - lane_g) & rmask];
-        unsigned h_up = __shfl_up_sync(0xffffffffu, out_h, 1, g);
-        unsigned v_in = __shfl_up_sync(0xffffffffu, out_v, 1, g);
-        if (lane_g == 0) {
-          h_up = BB; v_in = BBM;
-          if (MULTI && !first) { const uint2 b = ring2[s & 31]; h_up = b.x; v_in = b.y; }
+        unsigned cw;
+        if (!RING32) cw = gring16[(s - lane_g) & rmask];
+        else if (K1S_RINGLD) cw = gring_rd[s & (RN - 1)];
+        else cw = lds32_ordered(rd_lane + ((unsigned)(s & (RN - 1)) << 2));
+        unsigned h_up, v_in;
+        if (SHFLP) {
+          h_up = shfl_up1_or<g>(out_h, BB);               // first lane of the group: row above the stripe = (0, no gap)
+          v_in = shfl_up1_or<g>(out_v, BBM);
+        } else {
+          h_up = __shfl_up_sync(0xffffffffu, out_h, 1, g);
+          v_in = __shfl_up_sync(0xffffffffu, out_v, 1, g);
+          if (lane_g == 0) { h_up = BB; v_in = BBM; }
         }
-        if (cw & 0x80u) {                          // first column of a new pair: flush, reset the rows
+        if (MULTI && !first && lane_g == 0) { const uint2 b = ring2[s & 31]; h_up = b.x; v_in = b.y; }
+        if (RING32 ? (int)cw < 0 : (cw & 0x80u) != 0) {   // first column of a new pair: flush, reset the rows
           flush();
           ++pair_idx; best = BB; diag_in = BB;
 #pragma unroll
           for (int k = 0; k < R; ++k) { H[k] = BB; G[k] = BBM; }
         }
-        const unsigned aoff = pa_lane + (cw & 0x1fu) * (S::WA * 128);
-        const unsigned boff = pb_lane + ((cw >> 8) & 0x1fu) * (S::WB * 128);
+        // pa_lane + code(low target) * WA * 128, pb_lane + code(high target) * WB * 128
+        const unsigned aoff = RING32 ? mul_bytes01(MUL_A, cw, pa_lane) : pa_lane + (cw & 0x1fu) * (S::WA * 128);
+        const unsigned boff = RING32 ? mul_bytes01(MUL_B, cw, pb_lane) : pb_lane + ((cw >> 8) & 0x1fu) * (S::WB * 128);
         // Cell update.  G and V are kept SHIFTED by -oe (Gs = G - oe, Vs = V - oe), which turns
         //   G' = max(G + ge, H + oe)  into  Gs' = max(Gs + ge, H)          (no separate H + oe add)
         //   H  = max(0, t, G, V)      into  H   = max(max3(Gs, Vs, 0 - oe) + oe, t)

@@ -28,6 +28,10 @@ namespace swk {
 __device__ __forceinline__ unsigned lds32(unsigned saddr) {
   unsigned v; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(saddr)); return v;
 }
+// same, ordered against ordinary shared-memory stores (data another lane wrote before a __syncwarp)
+__device__ __forceinline__ unsigned lds32_ordered(unsigned saddr) {
+  unsigned v; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(saddr) : "memory"); return v;
+}
 __device__ __forceinline__ void lds64(unsigned saddr, unsigned& lo, unsigned& hi) {
   asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(lo), "=r"(hi) : "r"(saddr));
 }
@@ -42,6 +46,19 @@ __device__ __forceinline__ unsigned add_hi_lo(unsigned b, unsigned c) {
 // c + 65536 * (signed byte 2 of b)  [bytes 2 and 3 equal]
 __device__ __forceinline__ unsigned add_hi_hi(unsigned b, unsigned c) {
   unsigned d; asm("dp2a.hi.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(0x80008000u), "r"(b), "r"(c)); return d;
+}
+// value of the lane below within a `width`-lane segment; the segment's first lane (no lane below) gets `dflt`.
+// The shuffle's own range predicate drives the select: no separate compare.
+template <int WIDTH>
+__device__ __forceinline__ unsigned shfl_up1_or(unsigned v, unsigned dflt) {
+  unsigned d;
+  asm volatile("{ .reg .pred p; shfl.sync.up.b32 %0|p, %1, 1, %2, 0xffffffff; @!p mov.b32 %0, %3; }"
+               : "=r"(d) : "r"(v), "n"((32 - WIDTH) << 8), "r"(dflt));
+  return d;
+}
+// c + lo16(m) * byte0(b) + hi16(m) * byte1(b): IDP.2A on the FMA-heavy pipe (bytes of b below 128)
+__device__ __forceinline__ unsigned mul_bytes01(unsigned m, unsigned b, unsigned c) {
+  unsigned d; asm("dp2a.lo.u32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(m), "r"(b), "r"(c)); return d;
 }
 // a + b as IMAD (FMA-heavy pipe); `one` is an opaque register holding 1.
 __device__ __forceinline__ unsigned add_fma(unsigned a, unsigned one, unsigned b) {

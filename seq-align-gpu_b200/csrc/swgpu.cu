@@ -163,6 +163,13 @@ static int db_from_pack(swgpu_db_t** out, int device, swpack_t& pk, int64_t entr
   return SWGPU_OK;
 }
 
+// shorter streams at the end of the database (db_pack.c::stream_limit); opts->no_taper or SWGPU_PACK_TAPER=0 turn it off
+static int pack_taper(const swgpu_pack_opts_t* opts) {
+  if (opts && opts->no_taper) return 0;
+  const char* ev = getenv("SWGPU_PACK_TAPER");
+  return !(ev && ev[0] == '0');
+}
+
 static int pick_device(int device) {
   int ndev = 0;
   CU(cudaGetDeviceCount(&ndev));
@@ -205,7 +212,7 @@ int swgpu_db_create(swgpu_db_t** out, int device, const int8_t* codes, const int
   const int stream_cols = (opts && opts->stream_cols > 0) ? opts->stream_cols : kDefaultStreamCols;
   swpack_t pk;
   static const int64_t zero_off[1] = {0};
-  if (swpack_build(&pk, codes, n_targets ? offsets : zero_off, n_targets, stream_cols) != 0)
+  if (swpack_build(&pk, codes, n_targets ? offsets : zero_off, n_targets, stream_cols, pack_taper(opts)) != 0)
     return fail(SWGPU_EINVAL, "database packing failed (residue code outside 0..31, negative length, or out of memory)");
   return db_from_pack(out, device, pk, entry_base, opts, [](swgpu_db*) { return (int)SWGPU_OK; });
 }
@@ -226,7 +233,7 @@ int swgpu_db_create_synthetic(swgpu_db_t** out, int device, const int32_t* lengt
   swpack_t pk;
   std::vector<int64_t> pair_col((size_t)(n_targets + 1) / 2 + 1);
   static const int32_t zero_len[1] = {0};
-  if (swpack_layout(&pk, n_targets ? lengths : zero_len, n_targets, stream_cols, pair_col.data()) != 0)
+  if (swpack_layout(&pk, n_targets ? lengths : zero_len, n_targets, stream_cols, pack_taper(opts), pair_col.data()) != 0)
     return fail(SWGPU_EINVAL, "database layout failed (negative length or out of memory)");
   auto fill = [&](swgpu_db* db) -> int {
     // the residues exist only on the device: generated straight into `plain` (sorted order), then paired into streams

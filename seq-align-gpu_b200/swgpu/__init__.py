@@ -55,7 +55,8 @@ class SynthGen(C.Structure):
 
 
 class PackOpts(C.Structure):
-    _fields_ = [("long_threshold", C.c_int32), ("stream_cols", C.c_int32), ("reserved", C.c_int32 * 6)]
+    _fields_ = [("long_threshold", C.c_int32), ("stream_cols", C.c_int32), ("no_taper", C.c_int32),
+                ("reserved", C.c_int32 * 5)]
 
 
 _lib = None
@@ -122,13 +123,13 @@ def _i8(a):
 class Database:
     """Packed, HBM-resident database on one GPU (swgpu_db_t)."""
 
-    def __init__(self, codes, offsets, device=0, entry_base=0, long_threshold=0, stream_cols=0):
+    def __init__(self, codes, offsets, device=0, entry_base=0, long_threshold=0, stream_cols=0, no_taper=0):
         L = lib()
         self._codes, pc = _i8(codes)
         self._off = np.ascontiguousarray(offsets, dtype=np.int64)
         self.n = len(self._off) - 1
         h = C.c_void_p()
-        opts = PackOpts(long_threshold=long_threshold, stream_cols=stream_cols)
+        opts = PackOpts(long_threshold=long_threshold, stream_cols=stream_cols, no_taper=no_taper)
         _check(L.swgpu_db_create(C.byref(h), device, pc, self._off.ctypes.data_as(C.c_void_p), self.n, entry_base,
                                  C.byref(opts)))
         self._h = h

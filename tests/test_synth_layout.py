@@ -27,8 +27,9 @@ def arr(ptr, n, dtype):
     return np.ctypeslib.as_array(ptr, shape=(max(int(n), 1),))[: int(n)].astype(dtype).copy()
 
 
+@pytest.mark.parametrize("taper", [0, 1])
 @pytest.mark.parametrize("seed,n,stream_cols", [(1, 1, 1536), (2, 2, 1536), (3, 257, 64), (4, 5000, 1536), (5, 4001, 300)])
-def test_layout_from_lengths_matches_the_packer(seed, n, stream_cols):
+def test_layout_from_lengths_matches_the_packer(seed, n, stream_cols, taper):
     import swgpu
     from swgpu import synth
     L = swgpu.lib()
@@ -40,10 +41,10 @@ def test_layout_from_lengths_matches_the_packer(seed, n, stream_cols):
     codes = synth.residues(g, int(off[-1]))
     a, b = SwPack(), SwPack()
     assert L.swpack_build(C.byref(a), codes.ctypes.data_as(C.c_void_p), off.ctypes.data_as(C.c_void_p), C.c_int64(n),
-                          C.c_int32(stream_cols)) == 0
+                          C.c_int32(stream_cols), C.c_int32(taper)) == 0
     pair_col = np.zeros((n + 1) // 2 + 1, dtype=np.int64)
     assert L.swpack_layout(C.byref(b), lens.ctypes.data_as(C.c_void_p), C.c_int64(n), C.c_int32(stream_cols),
-                           pair_col.ctypes.data_as(C.c_void_p)) == 0
+                           C.c_int32(taper), pair_col.ctypes.data_as(C.c_void_p)) == 0
     try:
         for f in ("n_targets", "n_residues", "max_len", "n_pairs", "n_streams", "max_stream_cols", "n_long_streams",
                   "n_long_pairs", "scols_len"):
@@ -68,6 +69,15 @@ def test_layout_from_lengths_matches_the_packer(seed, n, stream_cols):
             hi = np.zeros(max(la, 1), dtype=np.int64); hi[:lb] = plain[poff[2 * q + 1]: poff[2 * q + 1] + lb]
             want = lo | (hi << 8); want[0] |= 0x80
             assert np.array_equal(col, want), q
+        # taper: full-length streams first, half-length ones in the last 1/16 of the columns, quarter-length in the last 1/64
+        ncols, soff = arr(a.stream_ncols, ns, np.int32), arr(a.stream_pair0, ns, np.int64)
+        if n >= 4000 and stream_cols == 1536:
+            body = ncols[1: ns // 2]                               # (stream 0 may be the 9 000-column pair)
+            assert body.min() >= stream_cols
+            if taper:
+                assert ncols[-2] < stream_cols // 4 + 400 and ncols[ns - ns // 40] < stream_cols // 2 + 400
+            else:
+                assert ncols[:-1].min() >= stream_cols
     finally:
         L.swpack_free(C.byref(a)); L.swpack_free(C.byref(b))
 
