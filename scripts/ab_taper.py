@@ -8,12 +8,18 @@ import swgpu
 from swgpu import synth
 
 ap = argparse.ArgumentParser()
-ap.add_argument("--reps", type=int, default=5)
+ap.add_argument("--reps", type=int, default=3)
 ap.add_argument("--lqs", default=",".join(str(x) for x in synth.C2_QUERY_LENGTHS))
 a = ap.parse_args()
 codes, off = synth.make_db(43, 570000, lo=2, hi=35213, total=int(205e6), force_max=35213)
 tab, _ = synth.load_matrix(os.path.join(ROOT, "scoring", "BLOSUM62.txt"))
-dbs = {"flat": swgpu.Database(codes, off, no_taper=1), "taper": swgpu.Database(codes, off)}
+def mk(cols, taper):
+    os.environ["SWGPU_PACK_TAPER"] = str(taper)
+    return swgpu.Database(codes, off, stream_cols=cols)
+# name -> (stream_cols, halvings); the first is the baseline
+variants = {"c1536t2": (1536, 2), "c1536t3": (1536, 3), "c2304t3": (2304, 3), "c3072t3": (3072, 3), "c3072t4": (3072, 4)}
+dbs = {k: mk(*v) for k, v in variants.items()}
+base = next(iter(dbs))
 tot = {k: 0.0 for k in dbs}
 for lq in [int(x) for x in a.lqs.split(",")]:
     q = synth.make_query(777, lq)
@@ -26,13 +32,11 @@ for lq in [int(x) for x in a.lqs.split(",")]:
     med = {k: statistics.median(v) for k, v in t.items()}
     for k in dbs:
         tot[k] += med[k]
-    print(json.dumps({"lq": lq, "flat_med": round(med["flat"], 3), "taper_med": round(med["taper"], 3),
-                      "flat_min": round(min(t["flat"]), 3), "taper_min": round(min(t["taper"]), 3),
-                      "taper_over_flat": round(med["taper"] / med["flat"], 4)}), flush=True)
-print(json.dumps({"sum_flat": round(tot["flat"], 1), "sum_taper": round(tot["taper"], 1)}))
+    print(json.dumps({"lq": lq, base + "_med": round(med[base], 3)} | {k: round(med[k] / med[base], 4) for k in dbs if k != base}), flush=True)
+print(json.dumps({"sum_" + k: round(v, 1) for k, v in tot.items()}))
 qs = [synth.make_query(100 + i, L) for i, L in enumerate(synth.C2_QUERY_LENGTHS)]
 many = {k: [] for k in dbs}
 for r in range(3):
     for k, d in dbs.items():
         many[k].append(d.search_many(qs, tab, -10, -1, k=100, want_scores=False)[3]["ms_total"])
-print(json.dumps({"many_flat": [round(x, 1) for x in many["flat"]], "many_taper": [round(x, 1) for x in many["taper"]]}))
+print(json.dumps({"many_" + k: [round(x, 1) for x in v] for k, v in many.items()}))

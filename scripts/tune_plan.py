@@ -15,7 +15,7 @@ n = int(570000 * a.scale)
 codes, off = synth.make_db(43, n, lo=2, hi=35213, total=int(205e6 * a.scale), force_max=35213)
 tab, _ = synth.load_matrix(os.path.join(ROOT, "scoring", "BLOSUM62.txt"))
 db = swgpu.Database(codes, off)
-MULTI_R = (16, 20, 24, 26, 28, 30, 32)
+MULTI_R = (16, 20, 24, 25, 26, 27, 28, 29, 30, 31, 32)
 for lq in sorted(LQS):
     q = synth.make_query(777, lq)
     os.environ.pop("SWGPU_K1S_PLAN", None)
@@ -25,11 +25,10 @@ for lq in sorted(LQS):
     default = (st["lanes_per_pair"], st["tile_rows"], st["passes"], st["ms_total"])
     plans = set()
     for g in (8, 16, 32):
-        R = -(-lq // g); R += R & 1; R = max(R, 8)
-        if R <= 32:
-            plans.add((g, R))
-            if R + 2 <= 32:
-                plans.add((g, R + 2))
+        R = max(-(-lq // g), 8)
+        for d in (0, 1, 2):
+            if R + d <= 32:
+                plans.add((g, R + d))
     for R in MULTI_R:
         if 32 * R < lq or True:
             plans.add((32, R))

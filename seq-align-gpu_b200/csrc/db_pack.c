@@ -94,10 +94,11 @@ int swpack_layout(swpack_t *p, const int32_t *lengths, int64_t n, int32_t stream
  * at the end of the sorted database, so the shorter streams still hold many pairs each. */
 static int64_t stream_limit(int64_t stream_cols, int32_t taper, int64_t remaining, int64_t total)
 {
-    if (!taper) return stream_cols;
-    int64_t lim = stream_cols;
-    if (remaining <= total / 64) lim = stream_cols / 4;
-    else if (remaining <= total / 16) lim = stream_cols / 2;
+    int64_t lim = stream_cols, frac = 16;
+    for (int32_t level = 0; level < taper; level++, frac *= 4) {     /* taper = number of halvings: at 1/16, 1/64, 1/256 ... */
+        if (remaining > total / frac) break;
+        lim /= 2;
+    }
     return lim < 64 ? 64 : lim;
 }
 

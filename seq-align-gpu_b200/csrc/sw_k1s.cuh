@@ -33,14 +33,14 @@ namespace swk {
 // Measured per instantiation (scripts/ab_lib.py): pairs gain 4-5 % at R = 28 and 32, 0-2 % at R = 24, and lose 1 % at
 // R = 22 and in the multi-stripe R = 30 kernel, which therefore keep the 32-bit layout.
 __host__ __device__ constexpr bool sprof_paired(int R, bool multi) {
-  return R >= K1S_PAIRED_MIN_R && R != 22 && !(multi && R == 30);
+  return R >= K1S_PAIRED_MIN_R && R != 21 && R != 22 && !(multi && R == 30);
 }
 __host__ __device__ constexpr int sprof_wa(int R, bool multi) { return sprof_paired(R, multi) ? 2 * (((R + 3) / 4 + 1) / 2) : (R + 3) / 4; }
-__host__ __device__ constexpr int sprof_wb(int R, bool multi) { return sprof_paired(R, multi) ? 2 * ((R / 2 + 1) / 2) : R / 2; }
+__host__ __device__ constexpr int sprof_wb(int R, bool multi) { return sprof_paired(R, multi) ? 2 * (((R + 1) / 2 + 1) / 2) : (R + 1) / 2; }
 __host__ __device__ constexpr int sprof_words(int R, bool multi) { return 32 * (sprof_wa(R, multi) + sprof_wb(R, multi)) * 32; }
 
 template <int R, bool MULTI> struct SProf {
-  static_assert(R % 2 == 0 && R >= 4 && R <= 32, "R must be even, 4..32");
+  static_assert(R >= 4 && R <= 32, "R must be 4..32");
   static constexpr bool PAIRED = sprof_paired(R, MULTI);
   static constexpr int WA = sprof_wa(R, MULTI);            // int8x4 words: s(k..k+3) for the LOW-half target (padded to even if PAIRED)
   static constexpr int WB = sprof_wb(R, MULTI);          // int8x4 words: s(k),s(k),s(k+1),s(k+1) for the HIGH-half target
@@ -352,6 +352,7 @@ __global__ void __launch_bounds__(K1S_WARPS * 32, (R <= K1S_R3CTA ? 3 : 2)) k1s(
           if (k & 1) best = __vimax3_u16x2(best, hprev, h); else hprev = h;
           t = tn;
         }
+        if (R & 1) best = __vmaxu2(best, hprev);           // odd R: the last row has no partner
         out_h = H[R - 1];
         out_v = V;
         if (MULTI && !last && lane == 31) {

@@ -1,4 +1,4 @@
-// sw_k1s_o1.cu -- the multi-stripe K1S instantiations with the most rows per lane (R = 28, 30, 32), built in a
+// sw_k1s_o1.cu -- the multi-stripe K1S instantiations with the most rows per lane (R = 26..32), built in a
 // translation unit of their own so that the Makefile can give ptxas a different optimisation level for them.
 //
 // Why: at ptxas -O3 these three kernels hit the 128-register ceiling of two CTAs per SM and spill (24/32/40 bytes
@@ -24,11 +24,15 @@ static cudaError_t launch_multi(const K1SParams& P, cudaStream_t stream, int gri
   return cudaGetLastError();
 }
 
-// R must be 28, 30 or 32 (cudaErrorInvalidValue otherwise).
+// R must be 26..32 (cudaErrorInvalidValue otherwise).
 cudaError_t launch_k1s_multi_o1(int R, const K1SParams& P, cudaStream_t stream, int grid, int device) {
   switch (R) {
+    case 26: return launch_multi<26>(P, stream, grid, device);
+    case 27: return launch_multi<27>(P, stream, grid, device);
     case 28: return launch_multi<28>(P, stream, grid, device);
+    case 29: return launch_multi<29>(P, stream, grid, device);
     case 30: return launch_multi<30>(P, stream, grid, device);
+    case 31: return launch_multi<31>(P, stream, grid, device);
     case 32: return launch_multi<32>(P, stream, grid, device);
     default: return cudaErrorInvalidValue;
   }

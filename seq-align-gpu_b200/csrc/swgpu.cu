@@ -20,7 +20,8 @@ namespace {
 
 using swi::fail;
 
-constexpr int kDefaultStreamCols = 1536;
+constexpr int kDefaultStreamCols = 2304;
+constexpr int kDefaultTaper = 3;             // stream lengths halve at the last 1/16, 1/64 and 1/256 of the database (scripts/ab_taper.py)
 constexpr int kWaveMinLen = 4096;          // 32-bit path: targets at least this long take k3x (one warp per 128-row stripe)
 
 template <typename T>
@@ -166,8 +167,8 @@ static int db_from_pack(swgpu_db_t** out, int device, swpack_t& pk, int64_t entr
 // shorter streams at the end of the database (db_pack.c::stream_limit); opts->no_taper or SWGPU_PACK_TAPER=0 turn it off
 static int pack_taper(const swgpu_pack_opts_t* opts) {
   if (opts && opts->no_taper) return 0;
-  const char* ev = getenv("SWGPU_PACK_TAPER");
-  return !(ev && ev[0] == '0');
+  if (const char* ev = getenv("SWGPU_PACK_TAPER")) return std::max(0, std::min(8, atoi(ev)));   // number of halvings (profiling knob)
+  return kDefaultTaper;
 }
 
 static int pick_device(int device) {
@@ -280,9 +281,9 @@ int64_t swgpu_db_device_bytes(const swgpu_db_t* db) { return db ? db->device_byt
 // ------------------------------------------------------------------------------------------
 namespace {
 
-// Instantiated kernels: every even R in 8..32 for g = 8, 16, 32; multi-stripe (g = 32) with R in {16, 20, 24..32}.
+// Instantiated kernels: every R in 8..32 for g = 8, 16, 32; multi-stripe (g = 32) with R in {16, 20, 24..32}.
 bool k1s_has_plan(int g, int R, bool multi) {
-  if (R < 8 || R > 32 || (R & 1) || (g != 8 && g != 16 && g != 32)) return false;
+  if (R < 8 || R > 32 || (g != 8 && g != 16 && g != 32)) return false;
   return !multi || (g == 32 && (R == 16 || R == 20 || R >= 24));
 }
 
@@ -290,21 +291,34 @@ bool k1s_has_plan(int g, int R, bool multi) {
 // Cost model: padded rows x (cell work + per-step overhead / R); few work items -> prefer more lanes per pair.
 struct K1SPlan { int g, g_log2, R, npass; };
 
+// Measured deviations of single instantiations from the smooth model (scripts/tune_plan.py on the C2 database,
+// profiles/r1f_tune_plan_odd.jsonl): the planner may take one or two rows per lane more than needed to avoid them.
+double k1s_penalty(int g, int R) {
+  if (R == 21) return 1.09;                        // unpaired profile loads, 95 registers
+  if (R == 11) return 1.06;
+  if (R == 8 && g == 8) return 1.25;
+  if (R == 25 && g < 32) return 1.05;
+  if (R == 24 && g == 32) return 1.05;
+  if (R == 19 || R == 18) return 1.01;
+  return 1.0;
+}
+
 K1SPlan plan_k1s(int64_t lq, int64_t n_streams, int warp_slots) {
   K1SPlan best{32, 5, 32, 1}; double best_cost = -1;
   for (int gl = 3; gl <= 5; ++gl) {
     const int g = 1 << gl;
-    int R = (int)((lq + g - 1) / g); R += R & 1; if (R < 8) R = 8;
-    if (R > 32) continue;
-    double cost = (double)g * R * (9.0 * R + 16.0) / R;
-    const double items = (double)n_streams * g / 32.0;
-    if (items < 2.0 * warp_slots) cost *= (2.0 * warp_slots) / std::max(items, 1.0);
-    if (best_cost < 0 || cost <= best_cost) { best_cost = cost; best = K1SPlan{g, gl, R, 1}; }
+    const int R0 = std::max((int)((lq + g - 1) / g), 8);
+    for (int R = R0; R <= std::min(R0 + 2, 32); ++R) {
+      double cost = (double)g * (9.0 * R + 16.0) * k1s_penalty(g, R);
+      const double items = (double)n_streams * g / 32.0;
+      if (items < 2.0 * warp_slots) cost *= (2.0 * warp_slots) / std::max(items, 1.0);
+      if (best_cost < 0 || cost <= best_cost) { best_cost = cost; best = K1SPlan{g, gl, R, 1}; }
+    }
   }
   if (best_cost < 0) {
     // multi-stripe: measured time per padded query row on the C2 database (scripts/tune_plan.py, us per row)
-    static const struct { int R; double us_per_row; } kMulti[] = {{16, 44.1}, {20, 42.3}, {24, 39.9}, {26, 39.5},
-                                                                  {28, 37.5}, {30, 37.25}, {32, 37.4}};
+    static const struct { int R; double us_per_row; } kMulti[] = {{16, 44.2}, {20, 39.7}, {24, 37.63}, {25, 37.96}, {26, 36.94}, {27, 36.85},
+                                                                  {28, 36.3}, {29, 36.55}, {30, 36.8}, {31, 37.8}, {32, 36.72}};
     for (const auto& m : kMulti) {
       const int np = (int)((lq + 32 * m.R - 1) / (32 * m.R));
       const double cost = (double)np * 32 * m.R * m.us_per_row;
@@ -313,7 +327,7 @@ K1SPlan plan_k1s(int64_t lq, int64_t n_streams, int warp_slots) {
   }
   if (const char* ev = getenv("SWGPU_K1S_PLAN")) {               // "g,R": profiling override of the plan
     int g = 0, R = 0;
-    if (sscanf(ev, "%d,%d", &g, &R) == 2 && (g == 8 || g == 16 || g == 32) && R >= 8 && R <= 32 && !(R & 1)) {
+    if (sscanf(ev, "%d,%d", &g, &R) == 2 && (g == 8 || g == 16 || g == 32) && R >= 8 && R <= 32) {
       const int gl = g == 8 ? 3 : g == 16 ? 4 : 5;
       const int np = (int)((lq + (int64_t)g * R - 1) / ((int64_t)g * R));
       if (k1s_has_plan(g, R, np > 1)) best = K1SPlan{g, gl, R, np};
@@ -339,8 +353,9 @@ template <int G>
 int launch_k1s_g(swgpu_db* db, const swk::K1SParams& P, int R, cudaStream_t stream, int grid) {
 #define K1S_CASE(r) case r: return launch_k1s_t<r, G, false>(db, P, stream, grid);
   switch (R) {
-    K1S_CASE(8) K1S_CASE(10) K1S_CASE(12) K1S_CASE(14) K1S_CASE(16) K1S_CASE(18) K1S_CASE(20) K1S_CASE(22)
-    K1S_CASE(24) K1S_CASE(26) K1S_CASE(28) K1S_CASE(30) K1S_CASE(32)
+    K1S_CASE(8) K1S_CASE(9) K1S_CASE(10) K1S_CASE(11) K1S_CASE(12) K1S_CASE(13) K1S_CASE(14) K1S_CASE(15) K1S_CASE(16)
+    K1S_CASE(17) K1S_CASE(18) K1S_CASE(19) K1S_CASE(20) K1S_CASE(21) K1S_CASE(22) K1S_CASE(23) K1S_CASE(24) K1S_CASE(25)
+    K1S_CASE(26) K1S_CASE(27) K1S_CASE(28) K1S_CASE(29) K1S_CASE(30) K1S_CASE(31) K1S_CASE(32)
     default: return fail(SWGPU_EINVAL, "no k1s instantiation for g=%d R=%d", G, R);
   }
 #undef K1S_CASE
@@ -350,9 +365,9 @@ int launch_k1s(swgpu_db* db, const swk::K1SParams& P, int g, int R, bool multi, 
   if (!k1s_has_plan(g, R, multi)) return fail(SWGPU_EINVAL, "no k1s instantiation for g=%d R=%d multi=%d", g, R, (int)multi);
   if (multi) {
 #define K1S_CASEM(r) case r: return launch_k1s_t<r, 32, true>(db, P, stream, grid);
-    switch (R) { K1S_CASEM(16) K1S_CASEM(20) K1S_CASEM(24) K1S_CASEM(26) default: break; }
+    switch (R) { K1S_CASEM(16) K1S_CASEM(20) K1S_CASEM(24) K1S_CASEM(25) default: break; }
 #undef K1S_CASEM
-    if (R >= 28) {                                             // built with other ptxas options: sw_k1s_o1.cu
+    if (R >= 26) {                                             // built with other ptxas options: sw_k1s_o1.cu
       CU(swk::launch_k1s_multi_o1(R, P, stream, grid, db->device));
       return SWGPU_OK;
     }
@@ -442,7 +457,7 @@ int enqueue_search(swgpu_db* db, swgpu_slot& S, const int8_t* query, int64_t lq,
   const bool split_long = use16 && plan.npass == 1 && n_split_streams > 0;
   K1SPlan plan_long = plan;
   if (split_long) {
-    int R = (int)((lq + 31) / 32); R += R & 1; if (R < 8) R = 8;
+    int R = (int)((lq + 31) / 32); if (R < 8) R = 8;
     plan_long = K1SPlan{32, 5, R, 1};
   }
   auto words_of = [](const K1SPlan& p) { return (size_t)p.npass * (size_t)swk::sprof_words(p.R, p.npass > 1); };

@@ -27,7 +27,7 @@ def arr(ptr, n, dtype):
     return np.ctypeslib.as_array(ptr, shape=(max(int(n), 1),))[: int(n)].astype(dtype).copy()
 
 
-@pytest.mark.parametrize("taper", [0, 1])
+@pytest.mark.parametrize("taper", [0, 3])
 @pytest.mark.parametrize("seed,n,stream_cols", [(1, 1, 1536), (2, 2, 1536), (3, 257, 64), (4, 5000, 1536), (5, 4001, 300)])
 def test_layout_from_lengths_matches_the_packer(seed, n, stream_cols, taper):
     import swgpu
@@ -69,13 +69,15 @@ def test_layout_from_lengths_matches_the_packer(seed, n, stream_cols, taper):
             hi = np.zeros(max(la, 1), dtype=np.int64); hi[:lb] = plain[poff[2 * q + 1]: poff[2 * q + 1] + lb]
             want = lo | (hi << 8); want[0] |= 0x80
             assert np.array_equal(col, want), q
-        # taper: full-length streams first, half-length ones in the last 1/16 of the columns, quarter-length in the last 1/64
+        # taper (number of halvings): full-length streams first, half-length ones in the last 1/16 of the columns,
+        # quarter-length in the last 1/64, an eighth in the last 1/256
         ncols, soff = arr(a.stream_ncols, ns, np.int32), arr(a.stream_pair0, ns, np.int64)
         if n >= 4000 and stream_cols == 1536:
             body = ncols[1: ns // 2]                               # (stream 0 may be the 9 000-column pair)
             assert body.min() >= stream_cols
             if taper:
-                assert ncols[-2] < stream_cols // 4 + 400 and ncols[ns - ns // 40] < stream_cols // 2 + 400
+                assert ncols[-2] < stream_cols // 8 + 400
+                assert np.any((ncols >= stream_cols // 2) & (ncols < stream_cols)) and np.any((ncols >= stream_cols // 4) & (ncols < stream_cols // 2))
             else:
                 assert ncols[:-1].min() >= stream_cols
     finally:
