@@ -145,3 +145,24 @@ def test_synthetic_create_fails_loudly_without_a_device():
     with pytest.raises(swgpu.SwgpuError) as e:
         swgpu.Database.synthetic(np.array([10, 20], dtype=np.int32), 46)
     assert "swgpu error -1" in str(e.value) or "swgpu error -2" in str(e.value)
+
+
+def test_c5_bench_shards_partition_the_database():
+    """bench.py --workload c5 under N ranks: the shards are a partition of the global entry ids, balanced in residues
+    (within one target) and in length mix; the queries do not depend on the rank."""
+    import importlib.util, os
+    from conftest import ROOT
+    spec = importlib.util.spec_from_file_location("bench_mod", os.path.join(ROOT, "bench.py"))
+    bench = importlib.util.module_from_spec(spec); spec.loader.exec_module(bench)
+    world = 4
+    parts = [bench.make_workload_c5(r, world, 0.0005) for r in range(world)]
+    full_lens, none_entries, q1, _ = bench.make_workload_c5(0, 1, 0.0005)
+    assert none_entries is None
+    ids = np.concatenate([p[1] for p in parts])
+    assert np.array_equal(np.sort(ids), np.arange(len(full_lens)))
+    for lens, entries, qs, _ in parts:
+        assert np.array_equal(lens, full_lens[entries]) and np.all(np.diff(entries) > 0)
+        assert all(np.array_equal(a, b) for a, b in zip(qs, q1))
+    res = [int(p[0].astype(np.int64).sum()) for p in parts]
+    assert max(res) - min(res) <= 35213
+    assert max(int(p[0].max()) for p in parts[1:]) >= np.sort(full_lens)[-world]
