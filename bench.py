@@ -241,6 +241,9 @@ def main():
     torch.cuda.set_device(local)
     dist = None
     if world > 1:
+        # stdout carries the one JSON line and nothing else: NCCL prints its version banner there at NCCL_DEBUG=VERSION/INFO
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("VERSION", "INFO", "TRACE") and not os.environ.get("NCCL_DEBUG_FILE"):
+            os.environ["NCCL_DEBUG"] = "WARN"
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     hbm_peak, sm_max, peak_src = load_peaks()
@@ -413,5 +416,19 @@ def main():
     return 0
 
 
+def _main_quiet_stdout():
+    """stdout carries the ONE JSON line and nothing else: while the bench runs, file descriptor 1 points at stderr (NCCL
+    prints its version banner to stdout at NCCL_DEBUG=VERSION, other libraries may chat there too); print() is routed
+    to the saved descriptor."""
+    sys.stdout.flush()
+    saved = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(saved, "w", buffering=1)
+    try:
+        return main()
+    finally:
+        sys.stdout.flush()
+
+
 if __name__ == "__main__":
-    sys.exit(main())
+    sys.exit(_main_quiet_stdout())
