@@ -184,7 +184,7 @@ __global__ void __launch_bounds__(K1S_WARPS * 32, (R <= K1S_R3CTA ? 3 : 2)) k1s(
   auto load_profile = [&](int pass) {
     const uint4* src = reinterpret_cast<const uint4*>(P.prof + (size_t)pass * S::WORDS);
     uint4* dst = reinterpret_cast<uint4*>(prof_s);
-    for (int i = threadIdx.x; i < S::WORDS / 4; i += K1S_WARPS * 32) dst[i] = src[i];
+    for (int i = threadIdx.x; i < S::WORDS / 4; i += blockDim.x) dst[i] = src[i];
   };
   if (!MULTI) { load_profile(0); __syncthreads(); if (warp >= P.active_warps) return; }
 
