@@ -344,12 +344,7 @@ int launch_k1s_t(swgpu_db* db, const swk::K1SParams& P, cudaStream_t stream, int
     CU(cudaFuncSetAttribute(swk::k1s<R, G, MULTI>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attr_done[db->device & 15] = true;
   }
-  // The long-stream launch runs ONE warp per CTA (active_warps == 1): it is launched with 32 threads, so that its CTAs
-  // (one per long stream, resident for the whole chain) do not hold the registers of seven idle warps and displace
-  // one of the three bulk CTAs of their SM.  SWGPU_LONG_CTA_FULL=1 restores 256-thread CTAs (A/B knob).
-  int threads = swk::K1S_WARPS * 32;
-  if (!MULTI && P.active_warps == 1 && !getenv("SWGPU_LONG_CTA_FULL")) threads = 32;
-  swk::k1s<R, G, MULTI><<<grid, threads, smem, stream>>>(P);
+  swk::k1s<R, G, MULTI><<<grid, swk::K1S_WARPS * 32, smem, stream>>>(P);
   CU(cudaGetLastError());
   return SWGPU_OK;
 }
