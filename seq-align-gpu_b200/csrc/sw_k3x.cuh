@@ -88,7 +88,14 @@ __global__ void __launch_bounds__(K3X_WARPS * 32) k3x(const K3XParams P) {
   static_assert(R3 == 4, "profile layout assumes 4 rows per lane");
   for (int i = threadIdx.x; i < 1024; i += blockDim.x) tab[i] = P.table[i];
   __syncthreads();
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // lane id through a volatile shared-memory round trip: ptxas otherwise re-derives it from the special register with an
+  // S2R (tens of cycles) twice per column step, on the critical path of the step's range test and first-lane select;
+  // a volatile load cannot be re-materialised, so the value stays in a register
+  __shared__ unsigned lane_ids[K3X_WARPS * 32];
+  lane_ids[threadIdx.x] = threadIdx.x & 31;
+  unsigned lane_v;
+  asm volatile("ld.volatile.shared.u32 %0, [%1];" : "=r"(lane_v) : "r"((unsigned)__cvta_generic_to_shared(&lane_ids[threadIdx.x])) : "memory");
+  const int warp = threadIdx.x >> 5, lane = (int)lane_v;
   unsigned* pl = pl_all[warp];
   const unsigned pl_addr = (unsigned)__cvta_generic_to_shared(pl) + lane * 4;
   const int n_targets = P.work_count ? (int)*P.work_count : P.n_targets;
