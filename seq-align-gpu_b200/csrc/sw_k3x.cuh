@@ -98,6 +98,13 @@ __global__ void __launch_bounds__(K3X_WARPS * 32) k3x(const K3XParams P) {
   const int warp = threadIdx.x >> 5, lane = (int)lane_v;
   unsigned* pl = pl_all[warp];
   const unsigned pl_addr = (unsigned)__cvta_generic_to_shared(pl) + lane * 4;
+  // per-warp rings: the profile byte offset (code * 128) of the last 64 target columns, and the (H, V) of the stripe
+  // above for the current block of 32 columns.  A lane reads its column's code and the first lane its boundary inputs
+  // with one shared load each, instead of passing the code from lane to lane and broadcasting three values by shuffle.
+  __shared__ unsigned ringc_all[K3X_WARPS][64];
+  __shared__ int2 ringb_all[K3X_WARPS][32];
+  unsigned* rc = ringc_all[warp];
+  int2* rb = ringb_all[warp];
   const int n_targets = P.work_count ? (int)*P.work_count : P.n_targets;
   const long long n_items = (long long)n_targets * P.nstripes_max;
   const int oe = P.oe, ge = P.ge;
@@ -158,9 +165,11 @@ __global__ void __launch_bounds__(K3X_WARPS * 32) k3x(const K3XParams P) {
       int H[R3], G[R3];
 #pragma unroll
       for (int k = 0; k < R3; ++k) { H[k] = 0; G[k] = 0; }
-      int diag_in = 0, out_h = 0, out_v = 0, my_code = 0;
-      int pre_code = 0, pre_h = 0, pre_v = 0;
+      int diag_in = 0, out_h = 0, out_v = 0;
+      rc[lane] = 0; rc[lane + 32] = 0;                      // columns before the first one: padding code
       const int nsteps = lt + 31;
+      int4* pcol = row_out - lane;                          // &row_out[s - lane], advanced every step (a loop-carried pointer
+                                                            // is not re-derived from the slot/stripe arithmetic each step)
       for (int s = 0; s < nsteps; ++s) {
         if ((s & 31) == 0) {
           const int j = s + lane;
@@ -174,24 +183,26 @@ __global__ void __launch_bounds__(K3X_WARPS * 32) k3x(const K3XParams P) {
               if (++spins > K3X_SPIN_LIMIT) { atomicExch(P.error_flag, 1u); break; }
             }
           }
+          __syncwarp();                                    // the previous block's rb has been read by the first lane
+          rb[lane] = make_int2(b.x, b.z);
+          rc[j & 63] = (j < lt) ? ((unsigned)tp[(long)j * tstep] & 31u) * 128u : 0u;
           __syncwarp();
-          pre_h = b.x; pre_v = b.z;
-          pre_code = (j < lt) ? (int)tp[(long)j * tstep] : 0;
         }
-        int code = __shfl_up_sync(0xffffffffu, my_code, 1);
+        // Column j = s - lane.  No range test around the cell update: before its first column a lane sees zeros from the
+        // lane below and the padding code (H stays 0); past its last column it computes on the padding code, which can
+        // only produce values below those already seen (the profile of padding is -128, gaps cost).  Only the hand-over
+        // store and the tracked maximum are guarded.
+        const int j = s - lane;
         int h_up = __shfl_up_sync(0xffffffffu, out_h, 1);
         int v_in = __shfl_up_sync(0xffffffffu, out_v, 1);
-        const int c0 = __shfl_sync(0xffffffffu, pre_code, s & 31);
-        const int h0 = __shfl_sync(0xffffffffu, pre_h, s & 31);
-        const int v0 = __shfl_sync(0xffffffffu, pre_v, s & 31);
-        if (lane == 0) { code = c0; h_up = h0; v_in = v0; }
-        my_code = code;
-        const int j = s - lane;
-        if (j >= 0 && j < lt) {
+        const int2 b0 = rb[s & 31];
+        if (lane == 0) { h_up = b0.x; v_in = b0.y; }
+        const unsigned w0 = lds32_ordered(pl_addr + rc[j & 63]);
+        const bool in_range = (unsigned)j < (unsigned)lt;
+        {
           int d = diag_in;
           diag_in = h_up;
           int V = v_in;
-          const unsigned w0 = lds32(pl_addr + (code & 31) * 128);
           int colbest = 0, colk = 0;
 #pragma unroll
           for (int k = 0; k < R3; ++k) {
@@ -204,11 +215,12 @@ __global__ void __launch_bounds__(K3X_WARPS * 32) k3x(const K3XParams P) {
             G[k] = __viaddmax_s32(G[k], ge, h + oe);
             if (TRACK) { if (h > colbest) { colbest = h; colk = k; } } else best = max(best, h);
           }
-          if (TRACK && k3x_better(colbest, j, row0 + colk, best, bj, bi)) { best = colbest; bj = j; bi = row0 + colk; }
+          if (TRACK && in_range && k3x_better(colbest, j, row0 + colk, best, bj, bi)) { best = colbest; bj = j; bi = row0 + colk; }
           out_h = H[R3 - 1];
           out_v = V;
-          if (lane == 31 && has_out) st_volatile_v4(&row_out[j], out_h, tag_out, out_v, tag_out);
+          if (lane == 31 && has_out && in_range) st_volatile_v4(pcol, out_h, tag_out, out_v, tag_out);
         }
+        ++pcol;
       }
       // this stripe's candidate
       if (TRACK) {
