@@ -111,6 +111,13 @@ __global__ void __launch_bounds__(K3_WARPS * 32) k3_intra(const K3Params P) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   unsigned* pl = pl_all[warp];
   const unsigned pl_addr = (unsigned)__cvta_generic_to_shared(pl) + lane * 4;
+  // per-warp rings (same scheme as k3x, sw_k3x.cuh): profile byte offset of the last 64 target columns, and the (H, V)
+  // of the stripe above for the current block of 32 columns -- one shared load each per step instead of a lane-to-lane
+  // code shuffle and three broadcast shuffles
+  __shared__ unsigned ringc_all[K3_WARPS][64];
+  __shared__ int2 ringb_all[K3_WARPS][32];
+  unsigned* rc = ringc_all[warp];
+  int2* rb = ringb_all[warp];
   int2* bnd = P.bnd + (size_t)(blockIdx.x * K3_WARPS + warp) * (size_t)P.bnd_stride;
   const int n_work = P.work_count ? (int)*P.work_count : P.n_work;
   const int oe = P.oe, ge = P.ge, lq = P.lq;
@@ -147,34 +154,37 @@ __global__ void __launch_bounds__(K3_WARPS * 32) k3_intra(const K3Params P) {
       int H[R3], G[R3];
 #pragma unroll
       for (int k = 0; k < R3; ++k) { H[k] = 0; G[k] = 0; }
-      int diag_in = 0, out_h = 0, out_v = 0, my_code = 0;
-      int pre_code = 0, pre_h = 0, pre_v = 0;
+      int diag_in = 0, out_h = 0, out_v = 0;
       const bool first = (pass == 0), last = (pass == npass - 1);
       const int nsteps = lt + 31;
+      rc[lane] = 0; rc[lane + 32] = 0;             // columns before the first one: padding code
+      int2* pcol = bnd - lane;                     // &bnd[s - lane], advanced every step
       for (int s = 0; s < nsteps; ++s) {
-        if ((s & 31) == 0) {                       // coalesced prefetch of the next 32 columns for lane 0
+        if ((s & 31) == 0) {                       // coalesced fetch of the next 32 columns
           const int j = s + lane;
-          pre_code = (j < lt) ? (int)tp[j] : 0;
           int2 b = make_int2(0, 0);
           if (!first && j < lt) b = bnd[j];
-          pre_h = b.x; pre_v = b.y;
+          __syncwarp();
+          rb[lane] = b;
+          rc[j & 63] = (j < lt) ? ((unsigned)tp[j] & 31u) * (unsigned)(W * 128) : 0u;
+          __syncwarp();
         }
-        int code = __shfl_up_sync(0xffffffffu, my_code, 1);
+        // Column j = s - lane; no range test around the cell update (see k3x): before its first column a lane sees
+        // zeros and the padding code, past its last column it computes on the padding code, which cannot raise the
+        // maximum.  Only the hand-over store is guarded.
+        const int j = s - lane;
         int h_up = __shfl_up_sync(0xffffffffu, out_h, 1);
         int v_in = __shfl_up_sync(0xffffffffu, out_v, 1);
-        const int c0 = __shfl_sync(0xffffffffu, pre_code, s & 31);
-        const int h0 = __shfl_sync(0xffffffffu, pre_h, s & 31);
-        const int v0 = __shfl_sync(0xffffffffu, pre_v, s & 31);
-        if (lane == 0) { code = c0; h_up = h0; v_in = v0; }
-        my_code = code;
-        const int j = s - lane;
-        if (j >= 0 && j < lt) {
+        const int2 b0 = rb[s & 31];
+        if (lane == 0) { h_up = b0.x; v_in = b0.y; }
+        const unsigned poff = pl_addr + rc[j & 63];
+        {
           int d = diag_in;
           diag_in = h_up;
           int V = v_in;
           unsigned wreg[W];
 #pragma unroll
-          for (int ww = 0; ww < W; ++ww) wreg[ww] = lds32(pl_addr + ((code & 31) * W + ww) * 128);
+          for (int ww = 0; ww < W; ++ww) wreg[ww] = lds32_ordered(poff + ww * 128);
 #pragma unroll
           for (int k = 0; k < R3; ++k) {
             const int t = (int)add_byte(wreg[k >> 2], 1u << (8 * (k & 3)), (unsigned)d);
@@ -188,8 +198,9 @@ __global__ void __launch_bounds__(K3_WARPS * 32) k3_intra(const K3Params P) {
           }
           out_h = H[R3 - 1];
           out_v = V;
-          if (lane == 31 && !last) bnd[j] = make_int2(out_h, out_v);
+          if (lane == 31 && !last && (unsigned)j < (unsigned)lt) *pcol = make_int2(out_h, out_v);
         }
+        ++pcol;
       }
     }
 #pragma unroll
