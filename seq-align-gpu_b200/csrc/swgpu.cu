@@ -171,6 +171,16 @@ static int pack_taper(const swgpu_pack_opts_t* opts) {
   return kDefaultTaper;
 }
 
+// Stream length when the caller does not give one: kDefaultStreamCols for a Swiss-Prot-sized database and up, shorter
+// for smaller ones so that the work queue still holds ~10 multi-stripe items (8 streams each) per resident CTA
+// (measured at 0.3 x C2, Lq = 2005: 24.1 ms with 2304-column streams, 23.1 ms with 1152; profiles/r1g_stream_cols_small_db.txt).
+static int default_stream_cols(int64_t n_residues) {
+  const int64_t want_streams = 8 * 296 * 10;
+  int64_t c = (n_residues / 2) / want_streams;
+  c = (c + 127) / 128 * 128;
+  return (int)std::max<int64_t>(1152, std::min<int64_t>(kDefaultStreamCols, c));
+}
+
 static int pick_device(int device) {
   int ndev = 0;
   CU(cudaGetDeviceCount(&ndev));
@@ -210,7 +220,8 @@ int swgpu_db_create(swgpu_db_t** out, int device, const int8_t* codes, const int
   if (n_targets > 0x7ffffff0ll) return fail(SWGPU_EINVAL, "swgpu_db_create: more than 2^31 targets per GPU; shard the database");
   *out = nullptr;
   if (int r = pick_device(device)) return r;
-  const int stream_cols = (opts && opts->stream_cols > 0) ? opts->stream_cols : kDefaultStreamCols;
+  const int stream_cols = (opts && opts->stream_cols > 0) ? opts->stream_cols
+                                                          : default_stream_cols(n_targets ? offsets[n_targets] - offsets[0] : 0);
   swpack_t pk;
   static const int64_t zero_off[1] = {0};
   if (swpack_build(&pk, codes, n_targets ? offsets : zero_off, n_targets, stream_cols, pack_taper(opts)) != 0)
@@ -230,7 +241,9 @@ int swgpu_db_create_synthetic(swgpu_db_t** out, int device, const int32_t* lengt
   if (gen->cdf[gen->n_letters - 1] != 65536u) return fail(SWGPU_EINVAL, "swgpu_db_create_synthetic: cdf must end at 65536");
   *out = nullptr;
   if (int r = pick_device(device)) return r;
-  const int stream_cols = (opts && opts->stream_cols > 0) ? opts->stream_cols : kDefaultStreamCols;
+  int64_t total_len = 0;
+  for (int64_t t = 0; t < n_targets; ++t) total_len += lengths[t] > 0 ? lengths[t] : 0;
+  const int stream_cols = (opts && opts->stream_cols > 0) ? opts->stream_cols : default_stream_cols(total_len);
   swpack_t pk;
   std::vector<int64_t> pair_col((size_t)(n_targets + 1) / 2 + 1);
   static const int32_t zero_len[1] = {0};
