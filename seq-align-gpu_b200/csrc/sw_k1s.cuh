@@ -122,6 +122,7 @@ __device__ __forceinline__ void k1s_st_release(unsigned* p, unsigned v) {
 constexpr unsigned K1S_SPIN_LIMIT = 1u << 24;
 
 constexpr int K1S_WARPS = 8;
+constexpr int K1S_RING_WORDS = 160;           // column ring per warp: (32 / g) group segments of 2 * (2g) + g words
 
 // Per-step overhead variants (A/B knobs, scripts/build_variant.sh):
 //   K1S_RING32   32-bit double-mapped column ring ([R + UR] addressing, profile offsets by IDP.2A) vs the 16-bit ring
@@ -142,7 +143,7 @@ constexpr int K1S_WARPS = 8;
 
 template <int R, bool MULTI>
 constexpr size_t k1s_smem_bytes() {
-  return (size_t)SProf<R, MULTI>::WORDS * 4 + (size_t)K1S_WARPS * (128 * 4 + 32 * 8) + 16;
+  return (size_t)SProf<R, MULTI>::WORDS * 4 + (size_t)K1S_WARPS * (K1S_RING_WORDS * 4 + 32 * 8) + 16;
 }
 
 // LANES = lanes per target pair (g), a compile-time constant (shuffle widths, ring masks and the block period fold into
@@ -158,19 +159,22 @@ __global__ void __launch_bounds__(K1S_WARPS * 32, (R <= K1S_R3CTA ? 3 : 2)) k1s(
   extern __shared__ __align__(16) unsigned smem_u32[];
   unsigned* prof_s = smem_u32;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  // Column ring: 128 words per warp.  A group's segment holds RN = 2g columns, each stored TWICE (at p and p + RN), so
+  // Column ring: K1S_RING_WORDS words per warp.  A group's segment holds RN = 2g columns, each stored TWICE (at p and p + RN), so
   // that the read index (s mod RN) - lane_g + RN never wraps: the address is a per-lane constant plus a warp-uniform
   // term, no per-lane arithmetic per step.  A ring word is (code of the low target | code of the high target << 8 |
   // first-column flag << 31): the two profile addresses come out of it with one IDP.2A each (FMA pipe).
   constexpr bool RING32 = K1S_RING32 != 0, SHFLP = K1S_SHFLP != 0;
-  unsigned* ring = smem_u32 + S::WORDS + warp * 128;
-  uint2* ring2 = reinterpret_cast<uint2*>(smem_u32 + S::WORDS + K1S_WARPS * 128) + warp * 32;
+  unsigned* ring = smem_u32 + S::WORDS + warp * K1S_RING_WORDS;
+  uint2* ring2 = reinterpret_cast<uint2*>(smem_u32 + S::WORDS + K1S_WARPS * K1S_RING_WORDS) + warp * 32;
   __shared__ unsigned cta_item;
 
   constexpr int g = LANES, g_log2 = (LANES == 8 ? 3 : LANES == 16 ? 4 : 5);
   const int lane_g = lane & (g - 1), grp = lane >> g_log2, per_warp = 32 >> g_log2;
   constexpr int RN = 2 * g;
-  unsigned* gring = ring + grp * (2 * RN);
+  // segments are g words apart modulo the 32 banks: the groups of a warp read their rings in the same instruction, each
+  // through a window of g consecutive words -- without the skew lanes of different groups would hit the same bank
+  // (ncu at 8 lanes per pair: 18 % of the shared-memory wavefronts were conflicts)
+  unsigned* gring = ring + grp * (2 * RN + g);
   const unsigned* gring_rd = gring + (RN - lane_g);
   const unsigned rd_lane = (unsigned)__cvta_generic_to_shared(gring_rd);
   constexpr int rmask = 4 * g - 1;                       // 16-bit ring: 4g columns per group
@@ -255,7 +259,7 @@ __global__ void __launch_bounds__(K1S_WARPS * 32, (R <= K1S_R3CTA ? 3 : 2)) k1s(
       unsigned out_h = BB, out_v = BBM, diag_in = BB, best = BB;
       long pair_idx = pair0 - 1;
       __syncwarp();
-      for (int i = lane; i < 128; i += 32) ring[i] = 0;
+      for (int i = lane; i < K1S_RING_WORDS; i += 32) ring[i] = 0;
       auto ring_word = [](unsigned c) { return (c & 0x1f1fu) | ((c & 0x80u) << 24); };
       unsigned pre = (lane_g < ncols) ? (unsigned)cp[lane_g] : 0u;
       uint2 pre_b = make_uint2(BB, BBM);
