@@ -138,7 +138,8 @@ constexpr int K1S_RING_WORDS = 160;           // column ring per warp: (32 / g) 
 #define K1S_RINGLD 0
 #endif
 #ifndef K1S_R3CTA
-#define K1S_R3CTA 18                         // R up to this: three CTAs per SM (<= 85 registers per thread)
+#define K1S_R3CTA 16                         // R up to this: three CTAs per SM (<= 85 registers per thread); measured: R = 18 runs
+                                             // 2-8 % faster with two CTAs of 86 registers, R = 13 and 16 1-2 % faster with three
 #endif
 
 template <int R, bool MULTI>
