@@ -39,7 +39,8 @@ typedef struct swgpu_db swgpu_db_t;   /* packed, HBM-resident database on one GP
 /* Packing knobs (0 = engine default). */
 typedef struct {
     int32_t long_threshold;   /* > 0: targets longer than this are always scored by the 32-bit kernels */
-    int32_t stream_cols;      /* length of one stream of concatenated target pairs (16-bit kernel); default 1536 */
+    int32_t stream_cols;      /* length of one stream of concatenated target pairs (16-bit kernel); default: 2304, down to
+                                 1152 for databases below ~110 M residues */
     int32_t no_taper;         /* != 0: every stream gets stream_cols columns (default: the streams of the last 1/16 of the
                                  database are half as long, those of the last 1/64 a quarter -- smaller work units at the
                                  end of the kernel's work queue) */
