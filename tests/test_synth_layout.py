@@ -166,3 +166,60 @@ def test_c5_bench_shards_partition_the_database():
     res = [int(p[0].astype(np.int64).sum()) for p in parts]
     assert max(res) - min(res) <= 35213
     assert max(int(p[0].max()) for p in parts[1:]) >= np.sort(full_lens)[-world]
+
+
+@pytest.mark.parametrize("seed", range(12))
+def test_packer_invariants_on_random_databases(seed):
+    """db_pack.c on random databases (empty targets, one giant, odd counts, any stream length and taper depth):
+    every residue of every target sits exactly once in `plain` (sorted by length, stable) and once in the streams, in
+    the half of its pair; pairs never straddle streams; streams start 64-column aligned; the long streams are a prefix."""
+    import swgpu
+    from swgpu import synth
+    L = swgpu.lib()
+    g = synth.rng(1000 + seed)
+    n = int(g.integers(1, 700))
+    lens = np.where(g.random(n) < 0.1, 0, g.integers(1, 400, size=n)).astype(np.int64)
+    if seed % 3 == 0:
+        lens[int(g.integers(0, n))] = int(g.integers(4097, 9000))
+    off = np.zeros(n + 1, dtype=np.int64); np.cumsum(lens, out=off[1:])
+    codes = g.integers(1, 32, size=int(off[-1])).astype(np.int8)
+    stream_cols, taper = int(g.choice([32, 64, 100, 777, 1536, 2304])), int(g.integers(0, 5))
+    p = SwPack()
+    assert L.swpack_build(C.byref(p), codes.ctypes.data_as(C.c_void_p), off.ctypes.data_as(C.c_void_p), C.c_int64(n),
+                          C.c_int32(stream_cols), C.c_int32(taper)) == 0
+    try:
+        order, poff = arr(p.order, n, np.int64), arr(p.plain_off, n + 1, np.int64)
+        plain = arr(p.plain, p.n_residues, np.int8)
+        assert sorted(order.tolist()) == list(range(n))
+        sl = lens[order]
+        assert np.all(np.diff(sl) <= 0)                                            # longest first ...
+        assert all(order[i] < order[i + 1] for i in range(n - 1) if sl[i] == sl[i + 1])   # ... stable
+        assert np.array_equal(np.diff(poff), sl) and p.n_residues == off[-1] and p.max_len == lens.max()
+        for s in range(n):
+            assert np.array_equal(plain[poff[s]:poff[s + 1]], codes[off[order[s]]:off[order[s] + 1]])
+        ns, npairs = int(p.n_streams), int(p.n_pairs)
+        assert npairs == (n + 1) // 2
+        soff, ncols, pair0 = arr(p.stream_off, ns + 1, np.int64), arr(p.stream_ncols, ns, np.int32), arr(p.stream_pair0, ns, np.int64)
+        scols = arr(p.scols, p.scols_len, np.uint16)
+        assert np.all(soff % 64 == 0) and pair0[0] == 0 and np.all(np.diff(pair0) > 0) and p.max_stream_cols == ncols.max()
+        nl = int(p.n_long_streams)
+        assert np.all(ncols[:nl] > 4096) and (nl == ns or ncols[nl] <= 4096)
+        q = 0
+        for st in range(ns):
+            col = soff[st]
+            q_end = pair0[st + 1] if st + 1 < ns else npairs
+            assert q == pair0[st]
+            while q < q_end:
+                la = int(sl[2 * q]); lb = int(sl[2 * q + 1]) if 2 * q + 1 < n else 0
+                w = max(la, 1)
+                seg = scols[col: col + w].astype(np.int64)
+                assert seg[0] & 0x80 and not np.any(seg[1:] & 0x80)                # one flag, on the pair's first column
+                lo, hi = seg & 0x1f, (seg >> 8) & 0x1f
+                assert np.array_equal(lo[:la], plain[poff[2 * q]: poff[2 * q] + la]) and not np.any(lo[la:])
+                assert np.array_equal(hi[:lb], plain[poff[2 * q + 1]: poff[2 * q + 1] + lb] if lb else hi[:0]) and not np.any(hi[lb:])
+                col += w; q += 1
+            assert col - soff[st] == ncols[st] and col <= soff[st + 1]
+            assert not np.any(scols[col: soff[st + 1]])                            # alignment padding is code 0
+        assert q == npairs
+    finally:
+        L.swpack_free(C.byref(p))
