@@ -94,6 +94,14 @@ def end_start(q, t, table, gap_open, gap_extend):
     return s, tuple(int(x) for x in c)
 
 
+def count_best(q, t, table, gap_open, gap_extend):
+    """Number of cells attaining the best score (1 = unique end cell)."""
+    q, t, _, table = _prep(q, t, [0], table)
+    L = oracle()
+    L.swo_count_best.restype = C.c_long
+    return int(L.swo_count_best(_p(q), C.c_long(q.size), _p(t), C.c_long(t.size), _p(table), C.c_int(gap_open), C.c_int(gap_extend)))
+
+
 def traceback(q, t, table, gap_open, gap_extend):
     """CIGAR of the forced-corner global alignment of q and t (the sub-sequences of a hit). Returns (cigar, score)."""
     q, t, _, table = _prep(q, t, [0], table)

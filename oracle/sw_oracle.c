@@ -170,6 +170,34 @@ static int32_t swo_scan_first_max(const int8_t *q, long lq, long q_step, const i
     return best;
 }
 
+/* Number of cells whose match state equals the best score (1 = the end cell of the optimum is unique): lets a test
+ * decide where an end coordinate printed by ANOTHER implementation (any tie-break) must equal this file's. */
+long swo_count_best(const int8_t *q, long lq, const int8_t *t, long lt, const int8_t *mat, int gap_open, int gap_extend)
+{
+    if (lq <= 0 || lt <= 0) return 0;
+    const int32_t oe = gap_open + gap_extend, ge = gap_extend;
+    int32_t *M = (int32_t *)calloc((size_t)(lq + 1) * 3, sizeof(int32_t));
+    int32_t *E = M + (lq + 1), *F = E + (lq + 1);
+    int32_t best = 0; long count = 0;
+    for (long j = 0; j < lt; j++) {
+        int32_t m_left = 0, e_left = 0, f_left = 0, m_ul = 0, e_ul = 0, f_ul = 0;
+        const int tc = t[j] & 31;
+        for (long i = 0; i < lq; i++) {
+            const int32_t s = mat[(q[i] & 31) * 32 + tc];
+            const int32_t m_up = M[i + 1], e_up = E[i + 1], f_up = F[i + 1];
+            int32_t m = SWO_MAX2(SWO_MAX2(m_ul + s, e_ul + s), SWO_MAX2(f_ul + s, 0));
+            if (m > best) { best = m; count = 1; } else if (m == best && m > 0) count++;
+            int32_t e = SWO_MAX2(SWO_MAX2(m_up + oe, e_up + ge), SWO_MAX2(f_up + oe, 0));
+            int32_t f = SWO_MAX2(SWO_MAX2(m_left + oe, e_left + oe), SWO_MAX2(f_left + ge, 0));
+            M[i + 1] = m; E[i + 1] = e; F[i + 1] = f;
+            m_ul = m_up; e_ul = e_up; f_ul = f_up;
+            m_left = m; e_left = e; f_left = f;
+        }
+    }
+    free(M);
+    return count;
+}
+
 int32_t swo_end_start(const int8_t *q, long lq, const int8_t *t, long lt,
                       const int8_t *mat, int gap_open, int gap_extend,
                       int32_t coords[4] /* q_start, q_end, t_start, t_end */)

@@ -17,6 +17,8 @@ def child(reps):
     for q in qs:
         db.search_resident(q, tab, -10, -1)
         out["ms"][len(q)] = round(min(db.search_resident(q, tab, -10, -1)["ms_total"] for _ in range(reps)), 3)
+    import zlib
+    out["crc"] = {len(q): zlib.crc32(db.search(q, tab, -10, -1)[0].tobytes()) for q in (qs[0], qs[3], qs[9], qs[11])}
     db.search_many(qs, tab, -10, -1, k=100, want_scores=False)
     out["many_ms"] = round(min(db.search_many(qs, tab, -10, -1, k=100, want_scores=False)[3]["ms_total"] for _ in range(2)), 2)
     out["many_gcups"] = round(sum(LQS) * int(off[-1]) / out["many_ms"] / 1e6, 1)
@@ -40,7 +42,7 @@ if __name__ == "__main__":
                 if o.returncode:
                     print(o.stderr[-2000:]); sys.exit(1)
                 d = json.loads(o.stdout.strip().splitlines()[-1]); res[l].append(d)
-                print(json.dumps({"lib": os.path.basename(l), "many_ms": d["many_ms"]}), flush=True)
+                print(json.dumps({"lib": os.path.basename(l), "many_ms": d["many_ms"], "crc": d.get("crc")}), flush=True)
         best = lambda l, lq: min(d["ms"][str(lq)] for d in res[l])
         for lq in LQS:
             base = best(libs[0], lq)

@@ -137,6 +137,14 @@ constexpr int K1S_RING_WORDS = 160;           // column ring per warp: (32 / g) 
 #ifndef K1S_RINGLD
 #define K1S_RINGLD 0
 #endif
+#ifndef K1S_BESTG
+#define K1S_BESTG 0
+#endif
+#if K1S_BESTG
+#define K1S_GINIT BB
+#else
+#define K1S_GINIT BBM
+#endif
 #ifndef K1S_R3CTA
 #define K1S_R3CTA 16                         // R up to this: three CTAs per SM (<= 85 registers per thread); measured: R = 18 runs
                                              // 2-8 % faster with two CTAs of 86 registers, R = 13 and 16 1-2 % faster with three
@@ -180,7 +188,11 @@ __global__ void __launch_bounds__(K1S_WARPS * 32, (R <= K1S_R3CTA ? 3 : 2)) k1s(
   const unsigned rd_lane = (unsigned)__cvta_generic_to_shared(gring_rd);
   constexpr int rmask = 4 * g - 1;                       // 16-bit ring: 4g columns per group
   unsigned short* gring16 = reinterpret_cast<unsigned short*>(ring) + grp * (4 * g);
+#ifdef K1S_IMM_TEST
+  constexpr unsigned BB = 140u * 0x10001u, BBM = 151u * 0x10001u, OE2 = 0xfff5fff5u, GE2 = 0xffffffffu;
+#else
   const unsigned BB = P.BB, BBM = P.BBM, OE2 = P.OE2, GE2 = P.GE2;
+#endif
   const unsigned pa_lane = (unsigned)__cvta_generic_to_shared(prof_s) + lane * (S::PAIRED ? 8 : 4);
   const unsigned pb_lane = pa_lane + 32 * S::WA * 128;
   constexpr unsigned MUL_A = (unsigned)(S::WA * 128), MUL_B = (unsigned)(S::WB * 128) << 16;
@@ -256,7 +268,7 @@ __global__ void __launch_bounds__(K1S_WARPS * 32, (R <= K1S_R3CTA ? 3 : 2)) k1s(
       };
       unsigned H[R], G[R];
 #pragma unroll
-      for (int k = 0; k < R; ++k) { H[k] = BB; G[k] = BBM; }
+      for (int k = 0; k < R; ++k) { H[k] = BB; G[k] = K1S_GINIT; }
       unsigned out_h = BB, out_v = BBM, diag_in = BB, best = BB;
       long pair_idx = pair0 - 1;
       __syncwarp();
@@ -281,6 +293,10 @@ __global__ void __launch_bounds__(K1S_WARPS * 32, (R <= K1S_R3CTA ? 3 : 2)) k1s(
         }
       };
 
+#ifdef K1S_UNROLL
+      constexpr int k1s_unroll = K1S_UNROLL;
+#pragma unroll k1s_unroll
+#endif
       for (int s = 0; s < nsteps; ++s) {
         if ((s & (g - 1)) == 0) {                  // every g steps: publish the prefetched block, fetch the next
           __syncwarp();
@@ -317,7 +333,7 @@ __global__ void __launch_bounds__(K1S_WARPS * 32, (R <= K1S_R3CTA ? 3 : 2)) k1s(
           flush();
           ++pair_idx; best = BB; diag_in = BB;
 #pragma unroll
-          for (int k = 0; k < R; ++k) { H[k] = BB; G[k] = BBM; }
+          for (int k = 0; k < R; ++k) { H[k] = BB; G[k] = K1S_GINIT; }
         }
         // pa_lane + code(low target) * WA * 128, pb_lane + code(high target) * WB * 128
         const unsigned aoff = RING32 ? mul_bytes01(MUL_A, cw, pa_lane) : pa_lane + (cw & 0x1fu) * (S::WA * 128);
@@ -354,10 +370,18 @@ __global__ void __launch_bounds__(K1S_WARPS * 32, (R <= K1S_R3CTA ? 3 : 2)) k1s(
           H[k] = h;
           G[k] = __viaddmax_u16x2(G[k], GE2, h);
           V = __viaddmax_u16x2(V, GE2, h);
+#if K1S_BESTG
+          if (k & 1) best = __vimax3_u16x2(best, G[k - 1], G[k]);
+#else
           if (k & 1) best = __vimax3_u16x2(best, hprev, h); else hprev = h;
+#endif
           t = tn;
         }
+#if K1S_BESTG
+        if (R & 1) best = __vmaxu2(best, G[R - 1]);
+#else
         if (R & 1) best = __vmaxu2(best, hprev);           // odd R: the last row has no partner
+#endif
         out_h = H[R - 1];
         out_v = V;
         if (MULTI && !last && lane == 31) {

@@ -56,3 +56,56 @@ def gather_topk(local_hits, k, dist=None, device=None):
     out = [torch.empty_like(t) for _ in range(dist.get_world_size())]
     dist.all_gather(out, t)
     return merge_topk([o.cpu().numpy() for o in out], k)
+
+
+def merge_topk_batch(lists, k):
+    """lists: int64 [world, n_queries, k, 2] (score, global entry; entry < 0 = padding).  One lexsort for all the
+    queries of a batch: key (query asc, score desc, entry asc).  Returns int64 [n_queries, k, 2], padded with -1."""
+    a = np.asarray(lists, dtype=np.int64)
+    w, nq, kk, _ = a.shape
+    rows = a.transpose(1, 0, 2, 3).reshape(nq, w * kk, 2)
+    qid = np.repeat(np.arange(nq, dtype=np.int64), w * kk)
+    flat = rows.reshape(-1, 2)
+    valid = flat[:, 1] >= 0
+    neg = np.where(valid, -flat[:, 0], np.iinfo(np.int64).max)      # padding sorts last within its query
+    order = np.lexsort((flat[:, 1], neg, qid))
+    out = flat[order].reshape(nq, w * kk, 2)[:, :k, :].copy()
+    out[out[:, :, 1] < 0] = -1
+    return out
+
+
+def gather_topk_batch(local, k, dist=None, device=None):
+    """ONE exchange for a whole batch of queries: local int64 [n_queries, <=k, 2] hit lists (padded to k with -1)
+    -> torch.distributed all_gather (NCCL on GPUs, gloo in the CPU tests) -> merge_topk_batch.  Returns
+    (merged [n_queries, k, 2], exchange_ms, merge_ms): exchange_ms is CUDA-event time around H2D + all_gather + D2H
+    when `device` is a CUDA device (else host wall clock), merge_ms the host wall clock of the lexsort."""
+    import time
+    import torch
+    loc = np.asarray(local, dtype=np.int64)
+    nq = loc.shape[0]
+    pad = np.full((nq, k, 2), -1, dtype=np.int64)
+    pad[:, : loc.shape[1], :] = loc[:, :k, :]
+    if dist is None or not dist.is_initialized() or dist.get_world_size() == 1:
+        t0 = time.perf_counter()
+        out = merge_topk_batch(pad[None], k)
+        return out, 0.0, 1e3 * (time.perf_counter() - t0)
+    world = dist.get_world_size()
+    cuda = device is not None and str(device).startswith("cuda")
+    t = torch.from_numpy(pad)
+    if cuda:
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        t = t.pin_memory().to(device, non_blocking=True)
+    else:
+        w0 = time.perf_counter()
+    buf = torch.empty((world * t.shape[0],) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device)   # ranks concatenated along dim 0
+    dist.all_gather_into_tensor(buf, t)
+    host = buf.cpu().reshape((world,) + tuple(t.shape))
+    if cuda:
+        e1.record(); e1.synchronize()
+        ex_ms = e0.elapsed_time(e1)
+    else:
+        ex_ms = 1e3 * (time.perf_counter() - w0)
+    t0 = time.perf_counter()
+    out = merge_topk_batch(host.numpy(), k)
+    return out, ex_ms, 1e3 * (time.perf_counter() - t0)

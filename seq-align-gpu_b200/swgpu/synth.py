@@ -56,6 +56,35 @@ def config2(n=570000, total=205_000_000):
     return make_db(43, n, lo=2, hi=35213, total=total, force_max=35213)
 
 
+def config3(n_each=1024, lq=6000):
+    """C3: seed 44; 16-bit overflow stress for PAM250, -10/-1.  Query of `lq` residues from a
+    low-complexity generator (W 0.4, C 0.2, Y 0.2, F 0.2: an exact copy of length L scores ~13 L and crosses 32 767
+    near L ~ 2 520).  4 x n_each targets: (A) exact substrings with L in [3 000, 6 000] -- far overflow; (B) exact
+    substrings with L in [2 300, 2 700] -- true scores straddling 32 767; (C) copies of (A)/(B) with 1-5 %
+    substitutions and one deletion; (D) C1-style background targets.  Returns (query, codes, offsets), targets
+    sorted longest first (the reference demands it)."""
+    g = rng(44)
+    lc = np.array([23, 3, 25, 6], dtype=np.int8)               # W C Y F
+    q = lc[g.choice(4, size=lq, p=[0.4, 0.2, 0.2, 0.2])]
+    parts = []
+    for _ in range(n_each):
+        L = int(g.integers(lq // 2, lq + 1)); s = int(g.integers(0, lq - L + 1)); parts.append(q[s:s + L])
+    for _ in range(n_each):
+        L = int(g.integers(2300, 2701)); s = int(g.integers(0, lq - L + 1)); parts.append(q[s:s + L])
+    for k in range(n_each):
+        src = parts[k * 2].copy()
+        mut = g.random(src.size) < g.uniform(0.01, 0.05)
+        src[mut] = residues(g, int(mut.sum()))
+        cut = int(g.integers(10, src.size - 10))
+        parts.append(np.concatenate([src[:cut], src[cut + 2:]]))
+    bg, bo = make_db(45, n_each)
+    parts += [bg[bo[i]:bo[i + 1]] for i in range(n_each)]
+    parts.sort(key=lambda p: -p.size)
+    off = np.zeros(len(parts) + 1, dtype=np.int64)
+    np.cumsum([p.size for p in parts], out=off[1:])
+    return q, np.concatenate(parts), off
+
+
 def config4(n=1024, lq=35213):
     """C4: seed 45; titin-length query; 16 targets at 35 213 aa, 48 log-uniform in [8 k, 35 k],
     the rest C1-distributed; target 1 is a 90 %-identity copy of the query (overflows 16 bits).

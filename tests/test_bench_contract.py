@@ -23,6 +23,22 @@ def test_reference_arm_prints_one_json_line():
     assert d["value"] > 0 and d["e2e"]["value"] == d["value"] and d["e2e"]["h2d_bytes_per_step"] == 0
     assert d["cpu_baseline"]["kind"] in ("reference", "port") and d["cpu_baseline"]["cores"] >= 1
     assert "C2" in d["config"]["workload"] and d["vs_baseline"] is None
+    # the arm says what it ran (a bounded sample, four query lengths incl. 5478) and times a one-thread row
+    assert "5478" in d["ran"]["sample"] and d["cpu_baseline"]["one_thread"]["cores"] == 1
+    assert d["ms_per_step"] > 0
+
+
+def test_reference_arm_ignores_torchrun_omp_num_threads():
+    """torchrun exports OMP_NUM_THREADS=1: the arm must still use every core it may run on (round-1 defect: the N > 1
+    reference values were single-threaded)."""
+    avail = len(os.sched_getaffinity(0))
+    env = dict(os.environ, OMP_NUM_THREADS="1")
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0",
+                          "--cpu-seconds", "1", "--workload", "c1"], capture_output=True, text=True, timeout=600, env=env)
+    assert out.returncode == 0, out.stderr[-2000:]
+    d = json.loads(out.stdout.strip().splitlines()[-1])
+    assert d["cpu_baseline"]["cores"] == avail and d["ran"]["omp_num_threads_env"] == "1"
+    assert "C1" in d["config"]["workload"]
 
 
 def test_reference_arm_other_ranks_stay_silent():

@@ -70,6 +70,27 @@ WORKER = textwrap.dedent("""
     oo = np.lexsort((np.arange(2000), -allsc))[:25]
     want = np.stack([allsc[oo], np.arange(2000)[oo]], axis=1)
     assert np.array_equal(merged, want), (rank, merged[:5], want[:5])
+    # the batched form bench.py uses: ONE all_gather for the hit lists of every query of a step
+    from swgpu.shard import gather_topk_batch
+    nq = 5
+    loc = np.full((nq, 25, 2), -1, dtype=np.int64)
+    wants = []
+    for qi in range(nq):
+        scq = (fake_scores(mine) * (qi + 3)) % 89
+        oq = np.lexsort((mine, -scq))[: 25 - qi]                 # ragged: fewer than k hits on some queries
+        loc[qi, : len(oq), 0] = scq[oq]; loc[qi, : len(oq), 1] = mine[oq]
+        alls = (fake_scores(np.arange(2000)) * (qi + 3)) % 89
+        parts = []
+        for r in range(world):
+            e = deal_shards(off, world)[r]; s_ = alls[e]; o_ = np.lexsort((e, -s_))[: 25 - qi]
+            parts.append(np.stack([s_[o_], e[o_]], axis=1))
+        cat = np.concatenate(parts); oo = np.lexsort((cat[:, 1], -cat[:, 0]))[:25]
+        wants.append(cat[oo])
+    got, ex_ms, mg_ms = gather_topk_batch(loc, 25, dist)
+    for qi in range(nq):
+        g = got[qi][got[qi][:, 1] >= 0]
+        assert np.array_equal(g, wants[qi]), (rank, qi, g[:4], wants[qi][:4])
+    assert ex_ms >= 0 and mg_ms >= 0
     dist.barrier(); dist.destroy_process_group()
     open(os.path.join(sys.argv[2], f"ok_{rank}"), "w").write("ok")
 """)

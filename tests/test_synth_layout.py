@@ -148,24 +148,39 @@ def test_synthetic_create_fails_loudly_without_a_device():
 
 
 def test_c5_bench_shards_partition_the_database():
-    """bench.py --workload c5 under N ranks: the shards are a partition of the global entry ids, balanced in residues
+    """bench.py --workload c5 (and c2 --sharded) under N ranks: the shards are a partition of the global entry ids, balanced in residues
     (within one target) and in length mix; the queries do not depend on the rank."""
     import importlib.util, os
     from conftest import ROOT
     spec = importlib.util.spec_from_file_location("bench_mod", os.path.join(ROOT, "bench.py"))
     bench = importlib.util.module_from_spec(spec); spec.loader.exec_module(bench)
+    import argparse
     world = 4
-    parts = [bench.make_workload_c5(r, world, 0.0005) for r in range(world)]
-    full_lens, none_entries, q1, _ = bench.make_workload_c5(0, 1, 0.0005)
-    assert none_entries is None
-    ids = np.concatenate([p[1] for p in parts])
-    assert np.array_equal(np.sort(ids), np.arange(len(full_lens)))
-    for lens, entries, qs, _ in parts:
-        assert np.array_equal(lens, full_lens[entries]) and np.all(np.diff(entries) > 0)
-        assert all(np.array_equal(a, b) for a, b in zip(qs, q1))
-    res = [int(p[0].astype(np.int64).sum()) for p in parts]
-    assert max(res) - min(res) <= 35213
-    assert max(int(p[0].max()) for p in parts[1:]) >= np.sort(full_lens)[-world]
+
+    def load(name, rank, w, **kw):
+        a = argparse.Namespace(workload=name, scale=0.0005, sharded=False, shards_total=8)
+        for k, v in kw.items():
+            setattr(a, k, v)
+        d = bench.load_workload(a, rank, w)
+        return d["lens"], d["entries"], d["queries"]
+
+    for name, kw in (("c5", {}), ("c2", {"sharded": True, "shards_total": 3, "scale": 0.002})):
+        parts = [load(name, r, world, **kw) for r in range(world)]
+        if name == "c5":
+            full_lens, none_entries, q1 = load(name, 0, 1, **kw)
+            assert none_entries is None
+        else:                                                    # --sharded deals even a single rank by global entry id
+            full_lens = bench.c2_sharded_lengths(3, 0.002)
+            l1, e1, q1 = load(name, 0, 1, **kw)
+            assert np.array_equal(e1, np.arange(len(full_lens))) and np.array_equal(l1, full_lens)
+        ids = np.concatenate([p[1] for p in parts])
+        assert np.array_equal(np.sort(ids), np.arange(len(full_lens)))
+        for lens, entries, qs in parts:
+            assert np.array_equal(lens, full_lens[entries]) and np.all(np.diff(entries) > 0)
+            assert all(np.array_equal(a, b) for a, b in zip(qs, q1))
+        res = [int(p[0].astype(np.int64).sum()) for p in parts]
+        assert max(res) - min(res) <= 35213
+        assert max(int(p[0].max()) for p in parts[1:]) >= np.sort(full_lens)[-world]
 
 
 @pytest.mark.parametrize("seed", range(12))
