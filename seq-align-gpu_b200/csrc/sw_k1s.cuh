@@ -19,6 +19,21 @@
 //     is at a different column (different residue), bank == lane, conflict-free by construction;
 //   * queries longer than 32*R rows take several passes (stripes); only then the stripe's bottom
 //     row is carried through a per-warp linear-space buffer (8 bytes per column per pass).
+//
+// Round 2 (profiles/r2a_*):
+//   * GAPSEL: the gap penalties as template constants.  VIMNMX3 / VIADDMNMX take a 32-bit immediate in their
+//     second source, so with compile-time penalties three of the four DPX instructions of a cell have TWO register
+//     sources instead of three.  That matters because a DPX instruction whose three source registers sit in the
+//     same register-file bank (even / odd register number) takes 3 issue cycles on the ALU pipe instead of 2
+//     (bench_micro/ubench_bank.cu: 1.37 vs 1.99 warp-instructions / clk / SM), ptxas cannot avoid all of them at
+//     120+ live registers, and the three constants (and their per-step LDC reloads) leave the register file.
+//     GAPSEL 0 is the generic kernel (penalties in registers), 1 = --gapopen -10 --gapextend -1, 2 = -11 / -1.
+//   * the column loop is unrolled by two where that pays (K1S_UNROLL_*): the new H of a row no longer has to be moved
+//     back into the register the next column reads it from (one IMAD.MOV per row per column before).
+//   * multi-stripe: the first lane takes the boundary values of the stripe above from a broadcast shared load that
+//     feeds the shuffle's default operand (same code for every stripe, no per-step branch), and lane 31 hands its
+//     bottom row over through a 32-column shared ring that the whole warp writes out coalesced every 32 steps
+//     (before: a bounds-checked 8-byte global store by one lane per step).
 #pragma once
 #include "sw_kernels.cuh"
 
@@ -97,19 +112,29 @@ struct K1SParams {
   long long       bnd_stride;
   unsigned*       counter;      // work queue head
   unsigned*       raw;          // [pair][g] packed biased running maxima
-  unsigned        BB, BBM, OE2, GE2;   // bias, bias - oe, packed oe, packed ge (u16 x 2)
+  unsigned        BB, BBM, OE2, GE2;   // bias, bias - oe, packed oe, packed ge (u16 x 2); a GAPSEL kernel has them as immediates
   // multi-pass only -- X items: the first n_x_streams streams (the long ones) are cut into (8 streams, ONE stripe)
   // items, so the stripes of a titin-length pair run at the same time on different CTAs instead of one after the
   // other on one warp.  Stripe p-1 -> stripe p through x_bnd (two full-length rows per stream, ping-pong by stripe
-  // parity) and one progress word per (stream, stripe): st.release.gpu by the producer's lane 31 every 32 columns,
-  // ld.acquire.gpu by the consumer's lane 0.  Items are ordered (group, stripe) ascending, so a producer always has
-  // the smaller item index and is already running when its consumer starts.
+  // parity) and one progress word per (stream, stripe): st.release.gpu by the producer's lane 31 every 32 columns
+  // (after the warp's coalesced write of those columns and a __syncwarp), ld.acquire.gpu by the consumer's lane 0.
+  // Items are ordered (group, stripe) ascending, so a producer always has the smaller item index and is already
+  // running when its consumer starts.
   int             n_x_streams;
   uint2*          x_bnd;        // per X stream two rows of its own length, at 2 * stream_off[stream]
   unsigned*       x_progress;   // [n_x_streams][npass], zeroed per search
   unsigned*       x_raw;        // [pair][npass][32] running maxima of the X pairs (one slot set per stripe)
   unsigned*       error_flag;
 };
+
+// Gap penalties known at compile time (GAPSEL > 0): oe = gap_open + gap_extend, ge = gap_extend.
+template <int GAPSEL> struct K1SGap { static constexpr int OE = 0, GE = 0; };
+template <> struct K1SGap<1> { static constexpr int OE = -11, GE = -1; };    // --gapopen -10 --gapextend -1 (the BASELINE configs)
+template <> struct K1SGap<2> { static constexpr int OE = -12, GE = -1; };    // --gapopen -11 --gapextend -1 (BLAST's BLOSUM62 default)
+constexpr int K1S_GAPSELS = 3;
+__host__ __device__ constexpr int k1s_gapsel(int oe, int ge) { return (oe == -11 && ge == -1) ? 1 : (oe == -12 && ge == -1) ? 2 : 0; }
+// bias of the unsigned 16-bit arithmetic: stored = true + B, no partial result is negative
+__host__ __device__ constexpr unsigned k1s_bias(int oe, int ge) { return 128u + (unsigned)(-oe) + (unsigned)(-ge); }
 
 __device__ __forceinline__ unsigned k1s_ld_acquire(const unsigned* p) {
   unsigned v;
@@ -124,35 +149,21 @@ constexpr unsigned K1S_SPIN_LIMIT = 1u << 24;
 constexpr int K1S_WARPS = 8;
 constexpr int K1S_RING_WORDS = 160;           // column ring per warp: (32 / g) group segments of 2 * (2g) + g words
 
-// Per-step overhead variants (A/B knobs, scripts/build_variant.sh):
-//   K1S_RING32   32-bit double-mapped column ring ([R + UR] addressing, profile offsets by IDP.2A) vs the 16-bit ring
-//   K1S_SHFLP    the shuffle's range predicate selects the first lane's default vs a separate compare
-//   K1S_RINGLD   0 = ordered inline-asm ring load, 1 = plain C++ load
-#ifndef K1S_RING32
-#define K1S_RING32 1
-#endif
-#ifndef K1S_SHFLP
-#define K1S_SHFLP 1
-#endif
-#ifndef K1S_RINGLD
-#define K1S_RINGLD 0
-#endif
-#ifndef K1S_BESTG
-#define K1S_BESTG 0
-#endif
-#if K1S_BESTG
-#define K1S_GINIT BB
-#else
-#define K1S_GINIT BBM
-#endif
 #ifndef K1S_R3CTA
 #define K1S_R3CTA 16                         // R up to this: three CTAs per SM (<= 85 registers per thread); measured: R = 18 runs
                                              // 2-8 % faster with two CTAs of 86 registers, R = 13 and 16 1-2 % faster with three
 #endif
+// columns per loop iteration (A/B knobs, scripts/build_variant.sh)
+#ifndef K1S_UNROLL_SINGLE
+#define K1S_UNROLL_SINGLE 2
+#endif
+#ifndef K1S_UNROLL_MULTI
+#define K1S_UNROLL_MULTI 1
+#endif
 
 template <int R, bool MULTI>
 constexpr size_t k1s_smem_bytes() {
-  return (size_t)SProf<R, MULTI>::WORDS * 4 + (size_t)K1S_WARPS * (K1S_RING_WORDS * 4 + 32 * 8) + 16;
+  return (size_t)SProf<R, MULTI>::WORDS * 4 + (size_t)K1S_WARPS * (K1S_RING_WORDS * 4 + (MULTI ? 2 : 1) * 32 * 8) + 16;
 }
 
 // LANES = lanes per target pair (g), a compile-time constant (shuffle widths, ring masks and the block period fold into
@@ -160,10 +171,12 @@ constexpr size_t k1s_smem_bytes() {
 // MULTI = false: the whole query fits one stripe; warps pull items independently.
 // MULTI = true : g == 32, several stripes; the CTA pulls 8 items at a time and reloads the
 //                shared profile between stripes.
-template <int R, int LANES, bool MULTI>
+// GAPSEL: see the header of this file.
+template <int R, int LANES, bool MULTI, int GAPSEL>
 __global__ void __launch_bounds__(K1S_WARPS * 32, (R <= K1S_R3CTA ? 3 : 2)) k1s(const K1SParams P) {
   static_assert(LANES == 8 || LANES == 16 || LANES == 32, "lanes per pair");
   static_assert(!MULTI || LANES == 32, "multi-stripe mode uses all 32 lanes");
+  static_assert(GAPSEL >= 0 && GAPSEL < K1S_GAPSELS, "gap specialisation");
   using S = SProf<R, MULTI>;
   extern __shared__ __align__(16) unsigned smem_u32[];
   unsigned* prof_s = smem_u32;
@@ -172,30 +185,32 @@ __global__ void __launch_bounds__(K1S_WARPS * 32, (R <= K1S_R3CTA ? 3 : 2)) k1s(
   // that the read index (s mod RN) - lane_g + RN never wraps: the address is a per-lane constant plus a warp-uniform
   // term, no per-lane arithmetic per step.  A ring word is (code of the low target | code of the high target << 8 |
   // first-column flag << 31): the two profile addresses come out of it with one IDP.2A each (FMA pipe).
-  constexpr bool RING32 = K1S_RING32 != 0, SHFLP = K1S_SHFLP != 0;
   unsigned* ring = smem_u32 + S::WORDS + warp * K1S_RING_WORDS;
-  uint2* ring2 = reinterpret_cast<uint2*>(smem_u32 + S::WORDS + K1S_WARPS * K1S_RING_WORDS) + warp * 32;
+  uint2* ring2 = reinterpret_cast<uint2*>(smem_u32 + S::WORDS + K1S_WARPS * K1S_RING_WORDS) + warp * 32;   // (H, V) of the stripe above, this block of 32 columns
+  uint2* ring3 = ring2 + K1S_WARPS * 32;                                                                     // MULTI: (H, V) of this stripe's bottom row, last 32 steps
   __shared__ unsigned cta_item;
 
   constexpr int g = LANES, g_log2 = (LANES == 8 ? 3 : LANES == 16 ? 4 : 5);
+  constexpr int UN = MULTI ? K1S_UNROLL_MULTI : K1S_UNROLL_SINGLE;
+  static_assert(UN == 1 || UN == 2, "columns per loop iteration");
   const int lane_g = lane & (g - 1), grp = lane >> g_log2, per_warp = 32 >> g_log2;
   constexpr int RN = 2 * g;
   // segments are g words apart modulo the 32 banks: the groups of a warp read their rings in the same instruction, each
   // through a window of g consecutive words -- without the skew lanes of different groups would hit the same bank
   // (ncu at 8 lanes per pair: 18 % of the shared-memory wavefronts were conflicts)
   unsigned* gring = ring + grp * (2 * RN + g);
-  const unsigned* gring_rd = gring + (RN - lane_g);
-  const unsigned rd_lane = (unsigned)__cvta_generic_to_shared(gring_rd);
-  constexpr int rmask = 4 * g - 1;                       // 16-bit ring: 4g columns per group
-  unsigned short* gring16 = reinterpret_cast<unsigned short*>(ring) + grp * (4 * g);
-#ifdef K1S_IMM_TEST
-  constexpr unsigned BB = 140u * 0x10001u, BBM = 151u * 0x10001u, OE2 = 0xfff5fff5u, GE2 = 0xffffffffu;
-#else
-  const unsigned BB = P.BB, BBM = P.BBM, OE2 = P.OE2, GE2 = P.GE2;
-#endif
+  const unsigned rd_lane = (unsigned)__cvta_generic_to_shared(gring + (RN - lane_g));
+  constexpr bool IMM = GAPSEL != 0;
+  constexpr unsigned cB = k1s_bias(K1SGap<GAPSEL>::OE, K1SGap<GAPSEL>::GE);
+  const unsigned BB = IMM ? cB * 0x10001u : P.BB;
+  const unsigned BBM = IMM ? (cB + (unsigned)(-K1SGap<GAPSEL>::OE)) * 0x10001u : P.BBM;
+  const unsigned OE2 = IMM ? ((unsigned)K1SGap<GAPSEL>::OE & 0xffffu) * 0x10001u : P.OE2;
+  const unsigned GE2 = IMM ? ((unsigned)K1SGap<GAPSEL>::GE & 0xffffu) * 0x10001u : P.GE2;
   const unsigned pa_lane = (unsigned)__cvta_generic_to_shared(prof_s) + lane * (S::PAIRED ? 8 : 4);
-  const unsigned pb_lane = pa_lane + 32 * S::WA * 128;
+  constexpr unsigned PB_OFF = 32 * S::WA * 128;         // B section: a compile-time offset in every load address
   constexpr unsigned MUL_A = (unsigned)(S::WA * 128), MUL_B = (unsigned)(S::WB * 128) << 16;
+  const unsigned r2_addr = (unsigned)__cvta_generic_to_shared(ring2);
+  const bool is31 = lane == 31;
   uint2* bnd = MULTI ? P.bnd + (size_t)(blockIdx.x * K1S_WARPS + warp) * (size_t)P.bnd_stride : nullptr;
 
   auto load_profile = [&](int pass) {
@@ -230,35 +245,34 @@ __global__ void __launch_bounds__(K1S_WARPS * 32, (R <= K1S_R3CTA ? 3 : 2)) k1s(
     const bool valid = x_item ? st_local < P.n_x_streams : st_local < P.n_streams;
     const long st = P.stream_begin + st_local;
     const int ncols = valid ? P.stream_ncols[st] : 0;
-    const long pair0 = valid ? (long)P.stream_pair0[st] : 0;
     const unsigned short* cp = P.scols + (valid ? P.stream_off[st] : 0);
     int maxcols = ncols;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) maxcols = max(maxcols, __shfl_xor_sync(0xffffffffu, maxcols, o));
-    const int nsteps = maxcols > 0 ? maxcols + g - 1 : 0;
+    // column steps of this item, rounded up to the unroll factor: a step past the end works on the padding code
+    // (score -128), which cannot raise a maximum; its hand-over column is past the end and is not written
+    const int nsteps = maxcols > 0 ? (maxcols + g - 1 + UN - 1) / UN * UN : 0;
 
     const int pass_begin = x_item ? x_pass : 0, pass_end = x_item ? x_pass + 1 : (MULTI ? P.npass : 1);
     for (int pass = pass_begin; pass < pass_end; ++pass) {
       if (MULTI) { __syncthreads(); load_profile(pass); __syncthreads(); }
       const bool first = (pass == 0), last = !MULTI || (pass == P.npass - 1);
-      // hand-over rows: own per-warp row (all stripes on this warp), or the stream's ping-pong rows (X item)
-      const uint2* bnd_in = bnd;
-      uint2* bnd_out = bnd;
-      const unsigned* prog_in = nullptr;
-      unsigned* prog_out = nullptr;
-      if (MULTI && x_item && valid) {
-        uint2* rows = P.x_bnd + 2 * (size_t)P.stream_off[st];      // two rows of ncols columns per stream
-        bnd_in = rows + (size_t)((pass + 1) & 1) * (size_t)ncols;
-        bnd_out = rows + (size_t)(pass & 1) * (size_t)ncols;
-        if (!first) prog_in = P.x_progress + (size_t)st_local * P.npass + (pass - 1);
-        if (!last) prog_out = P.x_progress + (size_t)st_local * P.npass + pass;
-      }
+      // hand-over rows: own per-warp row (all stripes on this warp), or the stream's ping-pong rows (X item: two rows of
+      // ncols columns, read from row (pass + 1) & 1, written to row pass & 1).  One base pointer is kept; the row offsets
+      // and the progress words of the X item (stripe p publishes into word p, reads word p - 1) are derived where they
+      // are used -- once per 32 steps -- so that they do not occupy registers in the cell loop.
+      const bool xv = MULTI && x_item && valid;
+      uint2* rows = xv ? P.x_bnd + 2 * (size_t)P.stream_off[st] : bnd;
+      unsigned* prog = xv ? P.x_progress + (size_t)st_local * P.npass + pass : nullptr;
+      const bool has_in = xv && !first, has_out = xv && !last;
+      auto bnd_in = [&]() -> const uint2* { return rows + (xv ? (size_t)((pass + 1) & 1) * (size_t)ncols : 0); };
+      auto bnd_out = [&]() -> uint2* { return rows + (xv ? (size_t)(pass & 1) * (size_t)ncols : 0); };
       auto wait_cols = [&](int upto) {                 // X item: the stripe above has published columns [0, upto)
-        if (prog_in) {
+        if (has_in) {
           if (lane == 0) {
             const unsigned need = (unsigned)min(upto, ncols);
             unsigned spins = 0;
-            while (k1s_ld_acquire(prog_in) < need) {
+            while (k1s_ld_acquire(prog - 1) < need) {
               __nanosleep(100);
               if (++spins > K1S_SPIN_LIMIT) { atomicExch(P.error_flag, 1u); break; }
             }
@@ -266,11 +280,16 @@ __global__ void __launch_bounds__(K1S_WARPS * 32, (R <= K1S_R3CTA ? 3 : 2)) k1s(
           __syncwarp();
         }
       };
+      // MULTI: the warp writes the hand-over columns of steps [sb, se) (lane 31 left them in ring3) in one go
+      auto flush_bnd = [&](int sb, int se) {
+        const int j = sb + lane - 31;                  // lane 31 worked on column step - 31
+        if (sb + lane < se && j >= 0 && j < ncols) bnd_out()[j] = ring3[lane];
+      };
       unsigned H[R], G[R];
 #pragma unroll
-      for (int k = 0; k < R; ++k) { H[k] = BB; G[k] = K1S_GINIT; }
+      for (int k = 0; k < R; ++k) { H[k] = BB; G[k] = BBM; }
       unsigned out_h = BB, out_v = BBM, diag_in = BB, best = BB;
-      long pair_idx = pair0 - 1;
+      int pair_rel = -1;                           // pair of the stream being scored (relative to the stream's first pair)
       __syncwarp();
       for (int i = lane; i < K1S_RING_WORDS; i += 32) ring[i] = 0;
       auto ring_word = [](unsigned c) { return (c & 0x1f1fu) | ((c & 0x80u) << 24); };
@@ -278,118 +297,110 @@ __global__ void __launch_bounds__(K1S_WARPS * 32, (R <= K1S_R3CTA ? 3 : 2)) k1s(
       uint2 pre_b = make_uint2(BB, BBM);
       if (MULTI && !first) {
         wait_cols(32);
-        if (lane < ncols) pre_b = __ldcg(&bnd_in[lane]);
+        if (lane < ncols) pre_b = __ldcg(bnd_in() + lane);
       }
       __syncwarp();
 
       auto flush = [&]() {
-        if (pair_idx >= pair0) {
+        if (pair_rel >= 0) {
+          const size_t pair_idx = (size_t)P.stream_pair0[st] + (size_t)pair_rel;
           if (MULTI && x_item) {
-            P.x_raw[(((size_t)pair_idx * P.npass + pass) << 5) + lane] = best;
+            P.x_raw[((pair_idx * P.npass + pass) << 5) + lane] = best;
           } else {
-            unsigned* slot = P.raw + ((size_t)pair_idx << g_log2) + lane_g;
+            unsigned* slot = P.raw + (pair_idx << g_log2) + lane_g;
             *slot = (MULTI && !first) ? __vmaxu2(*slot, best) : best;
           }
         }
       };
 
-#ifdef K1S_UNROLL
-      constexpr int k1s_unroll = K1S_UNROLL;
-#pragma unroll k1s_unroll
-#endif
-      for (int s = 0; s < nsteps; ++s) {
-        if ((s & (g - 1)) == 0) {                  // every g steps: publish the prefetched block, fetch the next
+      for (int s0 = 0; s0 < nsteps; s0 += UN) {
+        if ((s0 & (g - 1)) == 0) {                 // every g steps: publish the prefetched block, fetch the next
           __syncwarp();
-          if (RING32) { const int p = (s & (RN - 1)) + lane_g; const unsigned w = ring_word(pre); gring[p] = w; gring[p + RN] = w; }
-          else gring16[(s + lane_g) & rmask] = (unsigned short)pre;
-          const int c = s + g + lane_g;
+          { const int p = (s0 & (RN - 1)) + lane_g; const unsigned w = ring_word(pre); gring[p] = w; gring[p + RN] = w; }
+          const int c = s0 + g + lane_g;
           pre = (c < ncols) ? (unsigned)cp[c] : 0u;
           if (MULTI) {
+            if (!last && s0 > 0) flush_bnd(s0 - 32, s0);
             ring2[lane] = pre_b;
             pre_b = make_uint2(BB, BBM);
-            if (prog_out && lane == 31 && s > 31) k1s_st_release(prog_out, (unsigned)min(s - 31, ncols));
             if (!first) {
-              wait_cols(s + 2 * g);
-              if (c < ncols) pre_b = __ldcg(&bnd_in[c]);
+              wait_cols(s0 + 2 * g);
+              if (c < ncols) pre_b = __ldcg(bnd_in() + c);
             }
           }
           __syncwarp();
+          // columns [0, s0 - 31) of this stripe's bottom row are in memory (written by the whole warp above, ordered by the __syncwarp)
+          if (MULTI && has_out && is31 && s0 > 31) k1s_st_release(prog, (unsigned)min(s0 - 31, ncols));
         }
-        unsigned cw;
-        if (!RING32) cw = gring16[(s - lane_g) & rmask];
-        else if (K1S_RINGLD) cw = gring_rd[s & (RN - 1)];
-        else cw = lds32_ordered(rd_lane + ((unsigned)(s & (RN - 1)) << 2));
-        unsigned h_up, v_in;
-        if (SHFLP) {
-          h_up = shfl_up1_or<g>(out_h, BB);               // first lane of the group: row above the stripe = (0, no gap)
-          v_in = shfl_up1_or<g>(out_v, BBM);
-        } else {
-          h_up = __shfl_up_sync(0xffffffffu, out_h, 1, g);
-          v_in = __shfl_up_sync(0xffffffffu, out_v, 1, g);
-          if (lane_g == 0) { h_up = BB; v_in = BBM; }
-        }
-        if (MULTI && !first && lane_g == 0) { const uint2 b = ring2[s & 31]; h_up = b.x; v_in = b.y; }
-        if (RING32 ? (int)cw < 0 : (cw & 0x80u) != 0) {   // first column of a new pair: flush, reset the rows
-          flush();
-          ++pair_idx; best = BB; diag_in = BB;
 #pragma unroll
-          for (int k = 0; k < R; ++k) { H[k] = BB; G[k] = K1S_GINIT; }
-        }
-        // pa_lane + code(low target) * WA * 128, pb_lane + code(high target) * WB * 128
-        const unsigned aoff = RING32 ? mul_bytes01(MUL_A, cw, pa_lane) : pa_lane + (cw & 0x1fu) * (S::WA * 128);
-        const unsigned boff = RING32 ? mul_bytes01(MUL_B, cw, pb_lane) : pb_lane + ((cw >> 8) & 0x1fu) * (S::WB * 128);
-        // Cell update.  G and V are kept SHIFTED by -oe (Gs = G - oe, Vs = V - oe), which turns
-        //   G' = max(G + ge, H + oe)  into  Gs' = max(Gs + ge, H)          (no separate H + oe add)
-        //   H  = max(0, t, G, V)      into  H   = max(max3(Gs, Vs, 0 - oe) + oe, t)
-        // i.e. per cell pair: 2 IDP (FMA pipe) + VIMNMX3 + 3 VIADDMNMX + half a VIMNMX3 (ALU pipe).
-        // t of row k+1 is formed from H[k] of the previous column BEFORE H[k] is overwritten, so the
-        // row registers are updated in place (no register moves).
-        unsigned V = v_in;
-        unsigned wA, wB, wA2 = 0, wB2 = 0, hprev = BB;
-        if (S::PAIRED) { lds64(aoff, wA, wA2); lds64(boff, wB, wB2); }
-        else { wA = lds32(aoff); wB = lds32(boff); }
-        unsigned t = add_hi_lo(wB, add_byte(wA, 1u, diag_in));
-        diag_in = h_up;
-#pragma unroll
-        for (int k = 0; k < R; ++k) {
-          unsigned tn = 0;
-          if (k + 1 < R) {
-            const int k1 = k + 1;
-            if (S::PAIRED) {
-              if ((k1 & 7) == 0) lds64(aoff + (k1 >> 3) * 256, wA, wA2); else if ((k1 & 3) == 0) wA = wA2;
-              if ((k1 & 3) == 0) lds64(boff + (k1 >> 2) * 256, wB, wB2); else if ((k1 & 1) == 0) wB = wB2;
-            } else {
-              if ((k1 & 3) == 0) wA = lds32(aoff + (k1 >> 2) * 128);
-              if ((k1 & 1) == 0) wB = lds32(boff + (k1 >> 1) * 128);
-            }
-            tn = add_byte(wA, 1u << (8 * (k1 & 3)), H[k]);
-            tn = (k1 & 1) ? add_hi_hi(wB, tn) : add_hi_lo(wB, tn);
+        for (int u = 0; u < UN; ++u) {
+          const int s = s0 + u;
+          const unsigned cw = lds32_ordered(rd_lane + ((unsigned)(s & (RN - 1)) << 2));
+          unsigned h_up, v_in;
+          if (MULTI) {                              // first lane: the stripe above (constants in the first stripe), via the shuffle's default
+            unsigned bx, by;
+            lds64_ordered(r2_addr + ((unsigned)(s & 31) << 3), bx, by);
+            h_up = shfl_up1_or<g>(out_h, bx);
+            v_in = shfl_up1_or<g>(out_v, by);
+          } else {
+            h_up = shfl_up1_or<g>(out_h, BB);       // first lane of the group: row above the stripe = (0, no gap)
+            v_in = shfl_up1_or<g>(out_v, BBM);
           }
-          const unsigned ef = __vimax3_u16x2(G[k], V, BBM);
-          const unsigned h = __viaddmax_u16x2(ef, OE2, t);
-          H[k] = h;
-          G[k] = __viaddmax_u16x2(G[k], GE2, h);
-          V = __viaddmax_u16x2(V, GE2, h);
-#if K1S_BESTG
-          if (k & 1) best = __vimax3_u16x2(best, G[k - 1], G[k]);
-#else
-          if (k & 1) best = __vimax3_u16x2(best, hprev, h); else hprev = h;
-#endif
-          t = tn;
-        }
-#if K1S_BESTG
-        if (R & 1) best = __vmaxu2(best, G[R - 1]);
-#else
-        if (R & 1) best = __vmaxu2(best, hprev);           // odd R: the last row has no partner
-#endif
-        out_h = H[R - 1];
-        out_v = V;
-        if (MULTI && !last && lane == 31) {
-          const int j = s - 31;
-          if (j >= 0 && j < ncols) bnd_out[j] = make_uint2(out_h, out_v);
+          if ((int)cw < 0) {                        // first column of a new pair: flush, reset the rows
+            flush();
+            ++pair_rel; best = BB; diag_in = BB;
+#pragma unroll
+            for (int k = 0; k < R; ++k) { H[k] = BB; G[k] = BBM; }
+          }
+          // pa_lane + code(low target) * WA * 128, pa_lane + code(high target) * WB * 128 (+ PB_OFF in the load offsets)
+          const unsigned aoff = mul_bytes01(MUL_A, cw, pa_lane);
+          const unsigned boff = mul_bytes01(MUL_B, cw, pa_lane);
+          // Cell update.  G and V are kept SHIFTED by -oe (Gs = G - oe, Vs = V - oe), which turns
+          //   G' = max(G + ge, H + oe)  into  Gs' = max(Gs + ge, H)          (no separate H + oe add)
+          //   H  = max(0, t, G, V)      into  H   = max(max3(Gs, Vs, 0 - oe) + oe, t)
+          // i.e. per cell pair: 2 IDP (FMA pipe) + VIMNMX3 + 3 VIADDMNMX + half a VIMNMX3 (ALU pipe).
+          // t of row k+1 is formed from H[k] of the previous column BEFORE H[k] is overwritten.
+          unsigned V = v_in;
+          unsigned wA, wB, wA2 = 0, wB2 = 0, hprev = BB;
+          if (S::PAIRED) { lds64(aoff, wA, wA2); lds64(boff + PB_OFF, wB, wB2); }
+          else { wA = lds32(aoff); wB = lds32(boff + PB_OFF); }
+          unsigned t = add_hi_lo(wB, add_byte(wA, 1u, diag_in));
+          diag_in = h_up;
+#pragma unroll
+          for (int k = 0; k < R; ++k) {
+            unsigned tn = 0;
+            if (k + 1 < R) {
+              const int k1 = k + 1;
+              if (S::PAIRED) {
+                if ((k1 & 7) == 0) lds64(aoff + (k1 >> 3) * 256, wA, wA2); else if ((k1 & 3) == 0) wA = wA2;
+                if ((k1 & 3) == 0) lds64(boff + PB_OFF + (k1 >> 2) * 256, wB, wB2); else if ((k1 & 1) == 0) wB = wB2;
+              } else {
+                if ((k1 & 3) == 0) wA = lds32(aoff + (k1 >> 2) * 128);
+                if ((k1 & 1) == 0) wB = lds32(boff + PB_OFF + (k1 >> 1) * 128);
+              }
+              tn = add_byte(wA, 1u << (8 * (k1 & 3)), H[k]);
+              tn = (k1 & 1) ? add_hi_hi(wB, tn) : add_hi_lo(wB, tn);
+            }
+            const unsigned ef = __vimax3_u16x2(G[k], BBM, V);
+            const unsigned h = __viaddmax_u16x2(ef, OE2, t);
+            H[k] = h;
+            G[k] = __viaddmax_u16x2(G[k], GE2, h);
+            V = __viaddmax_u16x2(V, GE2, h);
+            if (k & 1) best = __vimax3_u16x2(best, hprev, h); else hprev = h;
+            t = tn;
+          }
+          if (R & 1) best = __vmaxu2(best, hprev);           // odd R: the last row has no partner
+          out_h = H[R - 1];
+          out_v = V;
+          if (MULTI && !last && is31) ring3[s & 31] = make_uint2(out_h, out_v);
         }
       }
-      if (MULTI && prog_out && lane == 31) k1s_st_release(prog_out, (unsigned)ncols);
+      if (MULTI && !last && nsteps > 0) {          // the columns of the last (partial) block of steps
+        __syncwarp();
+        flush_bnd((nsteps - 1) & ~31, nsteps);
+        __syncwarp();
+        if (has_out && is31) k1s_st_release(prog, (unsigned)ncols);
+      }
       flush();
     }
   }
@@ -423,5 +434,12 @@ static __global__ void k1s_finalize(const unsigned* __restrict__ raw, long pair_
     }
   }
 }
+
+// Launchers of one gap specialisation (sw_k1s_inst.cu is compiled once per GAPSEL and per ptxas option set; the
+// instantiations live in those objects, nowhere else).  cudaErrorInvalidValue for a plan that has no kernel.
+template <int GAPSEL>
+cudaError_t launch_k1s_o3(int g, int R, bool multi, const K1SParams& P, cudaStream_t stream, int grid, int device);
+template <int GAPSEL>
+cudaError_t launch_k1s_o1(int R, const K1SParams& P, cudaStream_t stream, int grid, int device);     // multi-stripe, R = 26..32
 
 }  // namespace swk

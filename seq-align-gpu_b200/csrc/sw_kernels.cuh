@@ -35,6 +35,9 @@ __device__ __forceinline__ unsigned lds32_ordered(unsigned saddr) {
 __device__ __forceinline__ void lds64(unsigned saddr, unsigned& lo, unsigned& hi) {
   asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(lo), "=r"(hi) : "r"(saddr));
 }
+__device__ __forceinline__ void lds64_ordered(unsigned saddr, unsigned& lo, unsigned& hi) {
+  asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(lo), "=r"(hi) : "r"(saddr) : "memory");
+}
 // c + (signed byte `sel` of a): IDP.4A on the FMA-heavy pipe.  sel_mask = 1 << (8*byte).
 __device__ __forceinline__ unsigned add_byte(unsigned a, unsigned sel_mask, unsigned c) {
   return (unsigned)__dp4a((int)a, (int)sel_mask, (int)c);

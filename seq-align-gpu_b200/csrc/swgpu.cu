@@ -7,8 +7,7 @@
 #include "sw_k1s.cuh"
 #include "sw_k3x.cuh"
 
-// multi-stripe K1S with R >= 28 lives in sw_k1s_o1.cu (different ptxas options)
-namespace swk { cudaError_t launch_k1s_multi_o1(int R, const K1SParams& P, cudaStream_t stream, int grid, int device); }
+// the K1S kernels themselves are instantiated in sw_k1s_inst.cu (one object per gap specialisation and ptxas option set)
 
 #include <cstdio>
 #include <cstdlib>
@@ -349,46 +348,26 @@ K1SPlan plan_k1s(int64_t lq, int64_t n_streams, int warp_slots) {
   return best;
 }
 
-template <int R, int G, bool MULTI>
-int launch_k1s_t(swgpu_db* db, const swk::K1SParams& P, cudaStream_t stream, int grid) {
-  const size_t smem = swk::k1s_smem_bytes<R, MULTI>();
-  static thread_local bool attr_done[16] = {};
-  if (!attr_done[db->device & 15]) {
-    CU(cudaFuncSetAttribute(swk::k1s<R, G, MULTI>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    attr_done[db->device & 15] = true;
-  }
-  swk::k1s<R, G, MULTI><<<grid, swk::K1S_WARPS * 32, smem, stream>>>(P);
-  CU(cudaGetLastError());
-  return SWGPU_OK;
+template <int GAPSEL>
+cudaError_t launch_k1s_sel(int g, int R, bool multi, const swk::K1SParams& P, cudaStream_t stream, int grid, int device) {
+  if (multi && R >= 26) return swk::launch_k1s_o1<GAPSEL>(R, P, stream, grid, device);
+  return swk::launch_k1s_o3<GAPSEL>(g, R, multi, P, stream, grid, device);
 }
 
-template <int G>
-int launch_k1s_g(swgpu_db* db, const swk::K1SParams& P, int R, cudaStream_t stream, int grid) {
-#define K1S_CASE(r) case r: return launch_k1s_t<r, G, false>(db, P, stream, grid);
-  switch (R) {
-    K1S_CASE(8) K1S_CASE(9) K1S_CASE(10) K1S_CASE(11) K1S_CASE(12) K1S_CASE(13) K1S_CASE(14) K1S_CASE(15) K1S_CASE(16)
-    K1S_CASE(17) K1S_CASE(18) K1S_CASE(19) K1S_CASE(20) K1S_CASE(21) K1S_CASE(22) K1S_CASE(23) K1S_CASE(24) K1S_CASE(25)
-    K1S_CASE(26) K1S_CASE(27) K1S_CASE(28) K1S_CASE(29) K1S_CASE(30) K1S_CASE(31) K1S_CASE(32)
-    default: return fail(SWGPU_EINVAL, "no k1s instantiation for g=%d R=%d", G, R);
-  }
-#undef K1S_CASE
-}
-
-int launch_k1s(swgpu_db* db, const swk::K1SParams& P, int g, int R, bool multi, cudaStream_t stream, int grid) {
+// oe / ge select the gap specialisation of the kernel (immediates instead of registers, sw_k1s.cuh); anything else runs
+// the generic kernel.  SWGPU_K1S_GENERIC=1 forces the generic kernel (A/B and test knob).
+int launch_k1s(swgpu_db* db, const swk::K1SParams& P, int g, int R, bool multi, int oe, int ge, cudaStream_t stream, int grid) {
   if (!k1s_has_plan(g, R, multi)) return fail(SWGPU_EINVAL, "no k1s instantiation for g=%d R=%d multi=%d", g, R, (int)multi);
-  if (multi) {
-#define K1S_CASEM(r) case r: return launch_k1s_t<r, 32, true>(db, P, stream, grid);
-    switch (R) { K1S_CASEM(16) K1S_CASEM(20) K1S_CASEM(24) K1S_CASEM(25) default: break; }
-#undef K1S_CASEM
-    if (R >= 26) {                                             // built with other ptxas options: sw_k1s_o1.cu
-      CU(swk::launch_k1s_multi_o1(R, P, stream, grid, db->device));
-      return SWGPU_OK;
-    }
-    return fail(SWGPU_EINVAL, "no multi-stripe k1s instantiation for R=%d", R);
+  int sel = swk::k1s_gapsel(oe, ge);
+  if (sel) { const char* ev = getenv("SWGPU_K1S_GENERIC"); if (ev && atoi(ev) > 0) sel = 0; }
+  cudaError_t e;
+  switch (sel) {
+    case 1:  e = launch_k1s_sel<1>(g, R, multi, P, stream, grid, db->device); break;
+    case 2:  e = launch_k1s_sel<2>(g, R, multi, P, stream, grid, db->device); break;
+    default: e = launch_k1s_sel<0>(g, R, multi, P, stream, grid, db->device); break;
   }
-  if (g == 8) return launch_k1s_g<8>(db, P, R, stream, grid);
-  if (g == 16) return launch_k1s_g<16>(db, P, R, stream, grid);
-  return launch_k1s_g<32>(db, P, R, stream, grid);
+  if (e != cudaSuccess) return fail(SWGPU_ECUDA, "k1s launch (g=%d R=%d multi=%d gapsel=%d) failed: %s", g, R, (int)multi, sel, cudaGetErrorString(e));
+  return SWGPU_OK;
 }
 
 // 32-bit scoring of a work list (device-side count) or of all targets (list == nullptr): k3_intra (one warp per
@@ -458,7 +437,7 @@ int enqueue_search(swgpu_db* db, swgpu_slot& S, const int8_t* query, int64_t lq,
 
   // ---- plan ----
   // 16-bit path: biased unsigned arithmetic with B = 128 + |oe| + |ge| (sw_k1s.cuh); huge gap penalties go 32-bit.
-  const unsigned B = 128u + (unsigned)(-oe) + (unsigned)(-ge);
+  const unsigned B = swk::k1s_bias(oe, ge);
   const bool use16 = (B <= 16384u) && db->n_streams > 0 && lq > 0;
   const K1SPlan plan = plan_k1s(std::max<int64_t>(lq, 1), db->n_streams, db->k1s_grid * swk::K1S_WARPS);
   // Long streams (one target pair of thousands of columns) are latency-bound on their serial column chain: when the
@@ -514,7 +493,7 @@ int enqueue_search(swgpu_db* db, swgpu_slot& S, const int8_t* query, int64_t lq,
       PL.stream_begin = 0; PL.n_streams = (int)nls; PL.n_items = (int)nls; PL.prof = S.d_sprof2; PL.npass = 1;
       PL.g = 32; PL.g_log2 = 5; PL.counter = S.d_counters + 1; PL.raw = S.d_raw_s;
       PL.active_warps = 1;                                     // one long stream per CTA: spread them over the SMs
-      if ((r = launch_k1s(db, PL, 32, plan_long.R, false, sa, (int)std::min<int64_t>(nls, db->k1s_grid)))) return r;
+      if ((r = launch_k1s(db, PL, 32, plan_long.R, false, oe, ge, sa, (int)std::min<int64_t>(nls, db->k1s_grid)))) return r;
       swk::k1s_finalize<<<std::max(1, (int)((nlp + 255) / 256)), 256, 0, sa>>>(
           S.d_raw_s, 0, (long)nlp, 32, (long)db->n, B, limit, db->d_order, db->d_plain_off, db->long_threshold,
           S.d_scores, S.d_rescore_list, S.d_counters + 2);
@@ -564,7 +543,7 @@ int enqueue_search(swgpu_db* db, swgpu_slot& S, const int8_t* query, int64_t lq,
       // every stage at the same (higher) step rate (C4: 56 -> 21 ms)
       int ctas = all_x ? 1 : plan.R <= K1S_R3CTA ? 3 : 2;
       if (const char* ev = getenv("SWGPU_K1S_CTAS")) ctas = std::max(1, std::min(3, atoi(ev)));      // A/B knob (profiling)
-      if ((r = launch_k1s(db, PS, plan.g, plan.R, multi, sm, db->sm_count * ctas))) return r;
+      if ((r = launch_k1s(db, PS, plan.g, plan.R, multi, oe, ge, sm, db->sm_count * ctas))) return r;
       if (nxp > 0) {
         swk::k1s_finalize<<<std::max(1, (int)((nxp + 255) / 256)), 256, 0, sm>>>(
             S.d_xs_raw, 0, (long)nxp, 32 * plan.npass, (long)db->n, B, limit, db->d_order, db->d_plain_off,
@@ -680,6 +659,116 @@ int run_single(swgpu_db* db, const int8_t* query, int64_t lq, const int8_t* tabl
 
 }  // namespace
 
+namespace swi {
+
+// One 16-lane batch in the reference's own layout (GPU twin of alignment_fill_matrices(aligner_t*), src/alignment.c:47).
+// The reference calls that function from every OpenMP worker at once (src/alignment_cmdline.c:504-507), thousands of times
+// per search; each host thread therefore keeps ONE context per device (stream, device buffers that only grow, pinned
+// result staging) and a call is: transpose the batch on the host, two small uploads, one k3_intra launch (one warp per
+// lane, 32-bit, exact), one 64-byte read-back.  Round 1 built and destroyed a whole swgpu_db per call.
+struct Batch16Ctx {
+  bool ready = false;
+  cudaStream_t stream = nullptr;
+  int8_t *d_query = nullptr, *d_codes = nullptr, *d_table = nullptr;  int64_t query_cap = 0, codes_cap = 0;
+  int64_t *d_off = nullptr, *d_order = nullptr;
+  int32_t* d_scores = nullptr;  unsigned* d_counter = nullptr;
+  int2* d_bnd = nullptr;  int64_t bnd_stride = 0;
+  int32_t* h_scores = nullptr;  int64_t* h_off = nullptr;  int8_t* h_codes = nullptr;  int64_t h_codes_cap = 0;
+  int8_t table_cache[1024];  bool table_valid = false;
+  ~Batch16Ctx() {
+    if (!ready) return;
+    cudaFree(d_query); cudaFree(d_codes); cudaFree(d_table); cudaFree(d_off); cudaFree(d_order); cudaFree(d_scores);
+    cudaFree(d_counter); cudaFree(d_bnd); cudaFreeHost(h_scores); cudaFreeHost(h_off); cudaFreeHost(h_codes);
+    if (stream) cudaStreamDestroy(stream);
+    cudaGetLastError();                      // at process exit the context may be gone already
+  }
+};
+
+int fill_batch16(int device, const int8_t* query, int64_t query_len, const int8_t* batch, int64_t padded_len,
+                 int lanes, const int8_t* table, int gap_open, int gap_extend, int32_t* scores16) {
+  if (lanes < 1 || lanes > 16 || padded_len < 0 || !batch || !scores16 || !table || query_len < 0 || (query_len > 0 && !query))
+    return fail(SWGPU_EINVAL, "bad batch argument");
+  if (query_len > 0x7fffffff || padded_len > 0x7ffffff0) return fail(SWGPU_EINVAL, "batch too long");
+  const int oe = gap_open + gap_extend, ge = gap_extend;
+  if (oe > 0 || ge > 0 || gap_open > 0)
+    return fail(SWGPU_EINVAL, "positive gap scores are outside the supported (and the reference-equivalent) range");
+  if (device < 0 || device >= 16) return fail(SWGPU_EINVAL, "device %d out of range", device);
+  if (int r = pick_device(device)) return r;
+  static thread_local Batch16Ctx ctxs[16];
+  Batch16Ctx& c = ctxs[device];
+  constexpr int kWarps = 16;                                 // 4 CTAs of K3_WARPS: one warp per lane of the batch
+  if (!c.ready) {
+    CU(cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking));
+    CU(cudaMalloc((void**)&c.d_table, 1024));
+    CU(cudaMalloc((void**)&c.d_off, sizeof(int64_t) * 17));
+    CU(cudaMalloc((void**)&c.d_order, sizeof(int64_t) * 16));
+    CU(cudaMalloc((void**)&c.d_scores, sizeof(int32_t) * 16));
+    CU(cudaMalloc((void**)&c.d_counter, sizeof(unsigned)));
+    CU(cudaMallocHost((void**)&c.h_scores, sizeof(int32_t) * 16));
+    CU(cudaMallocHost((void**)&c.h_off, sizeof(int64_t) * 17));
+    int64_t order[16]; for (int l = 0; l < 16; ++l) order[l] = l;
+    CU(cudaMemcpy(c.d_order, order, sizeof(order), cudaMemcpyHostToDevice));
+    c.ready = true;
+  }
+  if (query_len > c.query_cap) {
+    cudaFree(c.d_query); c.d_query = nullptr; c.query_cap = std::max<int64_t>(query_len * 2, 1024);
+    CU(cudaMalloc((void**)&c.d_query, (size_t)c.query_cap));
+  }
+  const int64_t total = (int64_t)lanes * padded_len;
+  if (total > c.codes_cap || !c.d_codes) {
+    cudaFree(c.d_codes); c.d_codes = nullptr; c.codes_cap = std::max<int64_t>(total * 2, 16 * 1024);
+    CU(cudaMalloc((void**)&c.d_codes, (size_t)c.codes_cap));
+  }
+  if (total > c.h_codes_cap || !c.h_codes) {
+    cudaFreeHost(c.h_codes); c.h_codes = nullptr; c.h_codes_cap = std::max<int64_t>(total * 2, 16 * 1024);
+    CU(cudaMallocHost((void**)&c.h_codes, (size_t)c.h_codes_cap));
+  }
+  const int64_t stride = std::max<int64_t>((padded_len + 63) & ~63ll, 64);
+  if (stride > c.bnd_stride) {
+    cudaFree(c.d_bnd); c.d_bnd = nullptr; c.bnd_stride = stride * 2;
+    CU(cudaMalloc((void**)&c.d_bnd, sizeof(int2) * (size_t)kWarps * (size_t)c.bnd_stride));
+  }
+  // The reference scores the '*' padding rows too (alignment.c:88 runs to the padded length),
+  // so every lane is handed over at its full padded length: [pos][lane] -> lane after lane.
+  for (int l = 0; l < lanes; ++l) {
+    c.h_off[l] = (int64_t)l * padded_len;
+    int8_t* dst = c.h_codes + c.h_off[l];
+    for (int64_t j = 0; j < padded_len; ++j) {
+      const int8_t v = batch[j * 16 + l];
+      if (v < 0 || v > 31) return fail(SWGPU_EINVAL, "residue code outside 0..31 in the batch");
+      dst[j] = v;
+    }
+  }
+  for (int l = lanes; l <= 16; ++l) c.h_off[l] = total;
+  for (int64_t i = 0; i < query_len; ++i) if (query[i] < 0 || query[i] > 31) return fail(SWGPU_EINVAL, "query code outside 0..31");
+  cudaStream_t st = c.stream;
+  if (query_len > 0) CU(cudaMemcpyAsync(c.d_query, query, (size_t)query_len, cudaMemcpyHostToDevice, st));
+  if (!c.table_valid || memcmp(c.table_cache, table, 1024) != 0) {
+    CU(cudaMemcpyAsync(c.d_table, table, 1024, cudaMemcpyHostToDevice, st));
+    memcpy(c.table_cache, table, 1024); c.table_valid = true;
+  }
+  if (total > 0) CU(cudaMemcpyAsync(c.d_codes, c.h_codes, (size_t)total, cudaMemcpyHostToDevice, st));
+  CU(cudaMemcpyAsync(c.d_off, c.h_off, sizeof(int64_t) * 17, cudaMemcpyHostToDevice, st));
+  CU(cudaMemsetAsync(c.d_counter, 0, sizeof(unsigned), st));
+  CU(cudaMemsetAsync(c.d_scores, 0, sizeof(int32_t) * 16, st));
+  if (query_len > 0 && padded_len > 0) {
+    swk::K3Params P; memset(&P, 0, sizeof(P));
+    P.worklist = nullptr; P.work_count = nullptr; P.n_work = lanes; P.counter = c.d_counter;
+    P.plain = c.d_codes; P.plain_off = c.d_off; P.query = c.d_query; P.lq = (int)query_len; P.table = c.d_table;
+    P.oe = oe; P.ge = ge; P.bnd = c.d_bnd; P.bnd_stride = c.bnd_stride; P.order = c.d_order;
+    P.scores_file = c.d_scores; P.one = 1u; P.max_len = 0;
+    if (query_len <= 128) swk::k3_intra<4><<<kWarps / swk::K3_WARPS, swk::K3_WARPS * 32, 0, st>>>(P);
+    else                  swk::k3_intra<8><<<kWarps / swk::K3_WARPS, swk::K3_WARPS * 32, 0, st>>>(P);
+    CU(cudaGetLastError());
+  }
+  CU(cudaMemcpyAsync(c.h_scores, c.d_scores, sizeof(int32_t) * 16, cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  for (int l = 0; l < lanes; ++l) scores16[l] = c.h_scores[l];
+  return SWGPU_OK;
+}
+
+}  // namespace swi
+
 extern "C" {
 
 int swgpu_search_resident(swgpu_db_t* db, const int8_t* query, int64_t query_len, const int8_t* table,
@@ -755,22 +844,7 @@ int swgpu_search_many(swgpu_db_t* db, int32_t n_queries, const int8_t* const* qu
 
 int swgpu_fill_batch16(int device, const int8_t* query, int64_t query_len, const int8_t* batch, int64_t padded_len,
                        int lanes, const int8_t* table, int gap_open, int gap_extend, int32_t* scores16) {
-  if (lanes < 1 || lanes > 16 || padded_len < 0 || !batch || !scores16) return fail(SWGPU_EINVAL, "bad batch argument");
-  // The reference scores the '*' padding rows too (alignment.c:88 runs to the padded length),
-  // so every lane is handed over at its full padded length.
-  std::vector<int8_t> codes((size_t)lanes * (size_t)padded_len);
-  std::vector<int64_t> off(lanes + 1);
-  for (int l = 0; l < lanes; ++l) {
-    off[l] = (int64_t)l * padded_len;
-    for (int64_t j = 0; j < padded_len; ++j) codes[(size_t)off[l] + j] = batch[j * 16 + l];
-  }
-  off[lanes] = (int64_t)lanes * padded_len;
-  swgpu_db_t* db = nullptr;
-  int r = swgpu_db_create(&db, device, codes.data(), off.data(), lanes, 0, nullptr);
-  if (r) return r;
-  r = swgpu_search(db, query, query_len, table, gap_open, gap_extend, scores16, nullptr);
-  swgpu_db_destroy(db);
-  return r;
+  return swi::fill_batch16(device, query, query_len, batch, padded_len, lanes, table, gap_open, gap_extend, scores16);
 }
 
 }  // extern "C"

@@ -105,6 +105,8 @@ void slot_release(swgpu_slot& S);
 int k3x_prepare(swgpu_db* db, swgpu_slot& S, int lq, cudaStream_t stream);   // (re)allocate + zero the k3x slot state
 int enqueue_topk(swgpu_db* db, swgpu_slot& S, int k);                  // no host synchronisation
 int collect_topk(swgpu_db* db, swgpu_slot& S, swgpu_hit_t* hits, int* n_hits);   // after S.ev[11] has completed
+int fill_batch16(int device, const int8_t* query, int64_t query_len, const int8_t* batch, int64_t padded_len, int lanes,
+                 const int8_t* table, int gap_open, int gap_extend, int32_t* scores16);   // swgpu.cu: per-thread cached context
 // swgpu_synth.cu: generate the residues of a layout-only database into d_plain, then pair them into d_scols
 cudaError_t synth_fill(swgpu_db* db, const swgpu_synth_t& gen, const int64_t* d_entry_ids, int64_t entry_base,
                        const int64_t* d_pair_col);

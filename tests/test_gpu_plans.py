@@ -8,6 +8,9 @@ instantiations the planner happens to choose.  Here SWGPU_K1S_PLAN forces each o
   * several stripes on a database big enough for ordinary items (8 streams x all stripes) next to the X items of its
     long streams, checked on a deterministic sample;
   * the same searches under different packings (stream length, taper on / off): identical scores.
+Every instantiation exists three times -- the generic kernel (gap penalties in registers) and the two gap specialisations
+(penalties as immediates: --gapopen -10 / -11 with --gapextend -1, csrc/sw_k1s.cuh) -- so every case runs under gap
+settings that select each of them; SWGPU_K1S_GENERIC=1 must give the same scores through the generic kernel.
 Bit-exact against the scalar int32 oracle (reference recurrence: src/alignment.c:117-176)."""
 import os
 
@@ -17,13 +20,16 @@ import pytest
 pytestmark = pytest.mark.gpu
 
 MULTI_R = (16, 20, 24, 25, 26, 27, 28, 29, 30, 31, 32)
+GAPS = [(-10, -1), (-11, -1), (-7, -2)]          # kernel specialisation 1, specialisation 2, generic
 
 
 @pytest.fixture()
 def plan_env():
     old = os.environ.pop("SWGPU_K1S_PLAN", None)
+    os.environ.pop("SWGPU_K1S_GENERIC", None)
     yield
     os.environ.pop("SWGPU_K1S_PLAN", None)
+    os.environ.pop("SWGPU_K1S_GENERIC", None)
     if old is not None:
         os.environ["SWGPU_K1S_PLAN"] = old
 
@@ -34,7 +40,8 @@ def small_db(synth, seed=71, n=800):
     return codes, off, lens
 
 
-def test_every_single_stripe_instantiation(oracle, matrices, plan_env):
+@pytest.mark.parametrize("go,ge", GAPS)
+def test_every_single_stripe_instantiation(oracle, matrices, plan_env, go, ge):
     import swgpu
     from swgpu import synth
     tab = matrices["BLOSUM62"]
@@ -46,15 +53,33 @@ def test_every_single_stripe_instantiation(oracle, matrices, plan_env):
             lq = g * R - (3 if R > 8 else 0)
             q = synth.make_query(9000 + lq, lq)
             if lq not in want:
-                want[lq] = oracle.search32(q, codes, off, tab, -10, -1)
+                want[lq] = oracle.search32(q, codes, off, tab, go, ge)
             os.environ["SWGPU_K1S_PLAN"] = f"{g},{R}"
-            got, st = db.search(q, tab, -10, -1)
+            got, st = db.search(q, tab, go, ge)
             assert (st["lanes_per_pair"], st["tile_rows"], st["passes"]) == (g, R, 1), (g, R, st)
             assert np.array_equal(got, want[lq]), (g, R, int((got != want[lq]).sum()))
     db.close()
 
 
-def test_every_multi_stripe_instantiation_small_database(oracle, matrices, plan_env):
+def test_generic_kernel_equals_the_gap_specialisations(oracle, matrices, plan_env):
+    """SWGPU_K1S_GENERIC=1: the -10/-1 search through the generic kernel (penalties in registers)."""
+    import swgpu
+    from swgpu import synth
+    tab = matrices["BLOSUM62"]
+    codes, off, _ = small_db(synth, seed=75, n=600)
+    db = swgpu.Database(codes, off)
+    for lq in (144, 375, 1000, 2005):
+        q = synth.make_query(9400 + lq, lq)
+        os.environ.pop("SWGPU_K1S_GENERIC", None)
+        a, _ = db.search(q, tab, -10, -1)
+        os.environ["SWGPU_K1S_GENERIC"] = "1"
+        b, _ = db.search(q, tab, -10, -1)
+        assert np.array_equal(a, b) and np.array_equal(a, oracle.search32(q, codes, off, tab, -10, -1)), lq
+    db.close()
+
+
+@pytest.mark.parametrize("go,ge", [(-12, -2), (-10, -1), (-11, -1)])
+def test_every_multi_stripe_instantiation_small_database(oracle, matrices, plan_env, go, ge):
     import swgpu
     from swgpu import synth
     tab = matrices["PAM250"]
@@ -64,15 +89,16 @@ def test_every_multi_stripe_instantiation_small_database(oracle, matrices, plan_
         for npass in (2, 3):
             lq = 32 * R * npass - 5
             q = synth.make_query(9100 + lq, lq)
-            want = oracle.search32(q, codes, off, tab, -12, -2)
+            want = oracle.search32(q, codes, off, tab, go, ge)
             os.environ["SWGPU_K1S_PLAN"] = f"32,{R}"
-            got, st = db.search(q, tab, -12, -2)
+            got, st = db.search(q, tab, go, ge)
             assert (st["lanes_per_pair"], st["tile_rows"], st["passes"]) == (32, R, npass), (R, st)
             assert np.array_equal(got, want), (R, npass, int((got != want).sum()))
     db.close()
 
 
-def test_every_multi_stripe_instantiation_ordinary_items(oracle, matrices, plan_env):
+@pytest.mark.parametrize("go,ge", GAPS)
+def test_every_multi_stripe_instantiation_ordinary_items(oracle, matrices, plan_env, go, ge):
     import swgpu
     from swgpu import synth
     tab = matrices["BLOSUM62"]
@@ -87,9 +113,9 @@ def test_every_multi_stripe_instantiation_ordinary_items(oracle, matrices, plan_
         lq = 64 * R - 7
         q = synth.make_query(9200 + lq, lq)
         os.environ["SWGPU_K1S_PLAN"] = f"32,{R}"
-        got, st = db.search(q, tab, -10, -1)
+        got, st = db.search(q, tab, go, ge)
         assert (st["tile_rows"], st["passes"]) == (R, 2), (R, st)
-        want = oracle.search32(q, sc, so, tab, -10, -1)
+        want = oracle.search32(q, sc, so, tab, go, ge)
         assert np.array_equal(got[sample], want), (R, int((got[sample] != want).sum()))
     db.close()
 
