@@ -11,8 +11,8 @@ import pytest
 
 from conftest import ROOT, SCORING, golden
 
-BIN = os.path.join(ROOT, "bin", "smith_waterman")
-HOST = os.path.join(ROOT, "seq-align-gpu_b200", "libalign.so")
+BIN = os.environ.get("SWGPU_HOST_BIN") or os.path.join(ROOT, "bin", "smith_waterman")
+HOST = os.environ.get("SWGPU_HOST_LIB") or os.path.join(ROOT, "seq-align-gpu_b200", "libalign.so")   # scripts/host_asan.sh: the ASan build
 
 
 class Scoring(C.Structure):          # include/alignment_scoring.h (== the reference's scoring_t layout)
