@@ -198,6 +198,34 @@ int swgpu_fill_batch16(int device, const int8_t *query, int64_t query_len,
                        const int8_t *batch_interleaved, int64_t padded_len, int lanes,
                        const int8_t *table, int gap_open, int gap_extend, int32_t *scores16);
 
+/*
+ * Allocation-free scoring of a small set of targets.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid allocation).  It is a variant of the 32-bit one-warp-per-target kernel (k3_intra) whose scratch
+ * memory -- the per-warp carry rows between query stripes and the work-queue counter -- lives in ONE file-scope
+ * `static __device__` array of SWGPU_NOALLOC_SCRATCH_BYTES (about 8 MiB), which every GPU that loads libswgpu.so holds
+ * until the process exits.  The call allocates and frees nothing (no cudaMalloc / cudaFree / cudaMallocHost, no
+ * allocating library routine), never synchronises, and only enqueues work on `stream`.
+ *   ALL pointers are DEVICE pointers owned by the caller:
+ *   d_query[query_len], d_targets (residue codes 0..31, targets back to back), d_offsets[n_targets + 1] (prefix offsets
+ *   into d_targets), d_table[32*32] (int8, [query code][target code]), d_scores[n_targets] (int32, written in the
+ *   order of d_offsets; exact 32-bit scores, same recurrence and results as swgpu_search()).
+ *   max_target_len  the caller's bound on the longest target; rejected with SWGPU_EINVAL if it exceeds
+ *                   SWGPU_NOALLOC_MAX_TARGET_LEN.  A target that is longer than the limit all the same is not scored:
+ *                   its d_scores entry is set to -1.
+ *   stream          a cudaStream_t passed as void* (NULL = the default stream).
+ * The scratch array is SHARED by every call on that GPU and keeps the previous call's contents; the entry point clears
+ * the part that must start at zero (the queue counter) on `stream` before the kernel.  Two calls that overlap on the
+ * GPU (different streams, or different host threads without ordering) RACE on it: order them on one stream or with
+ * events.  Gap scores must be non-positive, as for swgpu_search().
+ */
+#define SWGPU_NOALLOC_MAX_TARGET_LEN 4096
+#define SWGPU_NOALLOC_SCRATCH_BYTES  (256 + 256 * SWGPU_NOALLOC_MAX_TARGET_LEN * 8)
+int swgpu_score_targets_noalloc(int device, const int8_t *d_query, int32_t query_len,
+                                const int8_t *d_targets, const int64_t *d_offsets, int32_t n_targets,
+                                int32_t max_target_len, const int8_t *d_table, int gap_open, int gap_extend,
+                                int32_t *d_scores, void *stream);
+
 #ifdef __cplusplus
 }
 #endif
