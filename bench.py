@@ -462,13 +462,13 @@ def main():
 
     def step_serial():
         """Same queries, one at a time (nothing overlaps): the pass the per-kernel K1S time is taken from."""
-        ms, k1ms, k1cells = 0.0, 0.0, 0
+        ms, k1ms, k1cells, sms, rms = 0.0, 0.0, 0, 0.0, 0.0
         for q in serial_queries:
             st = db.search_resident(q, tab, GAP_OPEN, GAP_EXTEND)
             db.topk(TOPK)
             ms += st["ms_total"] + db.last_topk_ms
-            k1ms += st["ms_inter"]; k1cells += st["cells_inter"]
-        return ms, k1ms, k1cells
+            k1ms += st["ms_inter"]; k1cells += st["cells_inter"]; sms += st["ms_total"]; rms += st["ms_rescore"]
+        return ms, k1ms, k1cells, sms, rms
 
     want_e2e_scores = not device_db and n * nq * 4 <= (1 << 30)
     pinned = [torch.empty(n, dtype=torch.int32).pin_memory().numpy() for _ in queries] if want_e2e_scores else None
@@ -497,10 +497,10 @@ def main():
     # per-kernel time of the dominant kernel: the same queries, serially (in the pipelined region above the
     # event intervals of consecutive queries overlap, so they cannot be added up); a few steps are enough
     ser_steps = 1 if nq > 20 else min(a.steps, 5)
-    ser_ms, k1ms, k1cells = 0.0, 0.0, 0
+    ser_ms, k1ms, k1cells, search_ms, resc_ms = 0.0, 0.0, 0, 0.0, 0.0
     for _ in range(ser_steps):
         r = step_serial()
-        ser_ms += r[0]; k1ms += r[1]; k1cells += r[2]
+        ser_ms += r[0]; k1ms += r[1]; k1cells += r[2]; search_ms += r[3]; resc_ms += r[4]
     barrier()
 
     # e2e: host buffers in, host buffers out, wall clock.  Device-generated databases: 64 score vectors of 32.8 M entries
@@ -594,6 +594,11 @@ def main():
                                          f"{traffic.get('multi_stripe_lq2005', {}).get('bytes')} B; algorithmic "
                                          f"{N_RESIDUES + 4 * N_TARGETS} B per launch",
                          "hbm": {"achieved": hbm_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": hbm_gbs / hbm_peak, "peak_src": peak_src}},
+            "search_only": {"value": (k1cells / (search_ms * 1e-3) / 1e9) if search_ms > 0 else None, "unit": "GCUPS",
+                            "ms_per_step": search_ms / ser_steps, "rescore_ms_per_step": resc_ms / ser_steps,
+                            "topk_ms_per_step": (ser_ms - search_ms) / ser_steps,
+                            "what": "the serial pass split up: all per-entry scores final in HBM (16-bit pass + 32-bit rescoring), "
+                                    "WITHOUT top-100 selection and the coordinate passes that `value` also times; this rank only"},
             "cpu_baseline": cpu_line, "parity": parity,
             "merge": {"ms_per_step": merge_ms_max / a.steps, "inside_value": True,
                       "how": "one exchange per step: [queries, 100, (score, global entry)] int64 -> H2D + all_gather_into_tensor + D2H "

@@ -217,7 +217,8 @@ int swgpu_fill_batch16(int device, const int8_t *query, int64_t query_len,
  * The scratch array is SHARED by every call on that GPU and keeps the previous call's contents; the entry point clears
  * the part that must start at zero (the queue counter) on `stream` before the kernel.  Two calls that overlap on the
  * GPU (different streams, or different host threads without ordering) RACE on it: order them on one stream or with
- * events.  Gap scores must be non-positive, as for swgpu_search().
+ * events.  Gap scores must be non-positive here (this entry point carries the two-gap-state kernel only; swgpu_search()
+ * also takes positive ones).
  */
 #define SWGPU_NOALLOC_MAX_TARGET_LEN 4096
 #define SWGPU_NOALLOC_SCRATCH_BYTES  (256 + 256 * SWGPU_NOALLOC_MAX_TARGET_LEN * 8)

@@ -6,6 +6,7 @@
 #include "sw_kernels.cuh"
 #include "sw_k1s.cuh"
 #include "sw_k3x.cuh"
+#include "sw_k3s.cuh"
 
 // the K1S kernels themselves are instantiated in sw_k1s_inst.cu (one object per gap specialisation and ptxas option set)
 
@@ -80,7 +81,7 @@ int k3x_prepare(swgpu_db* db, swgpu_slot& S, int lq, cudaStream_t stream) {
 
 void slot_release(swgpu_slot& S) {
   cudaFree(S.d_scores); cudaFree(S.d_raw_s); cudaFree(S.d_rescore_list); cudaFree(S.d_counters);
-  cudaFree(S.d_bnd_s); cudaFree(S.d_bnd3); cudaFree(S.d_query); cudaFree(S.d_table);
+  cudaFree(S.d_bnd_s); cudaFree(S.d_bnd3); cudaFree(S.d_bnd3s); cudaFree(S.d_query); cudaFree(S.d_table);
   cudaFree(S.d_sprof); cudaFree(S.d_sprof2);
   cudaFree(S.d_keys); cudaFree(S.d_hit_sidx); cudaFree(S.d_sel); cudaFree(S.d_coords);
   cudaFree(S.d_xs_bnd); cudaFree(S.d_xs_progress); cudaFree(S.d_xs_raw);
@@ -400,14 +401,36 @@ int launch_32bit(swgpu_db* db, swgpu_slot& S, cudaStream_t stream, const int* li
   return SWGPU_OK;
 }
 
+// A positive gap score: the reference's three-state recurrence (sw_k3s.cuh), every target through one 32-bit kernel.
+// The two-gap-state form of the other kernels is only score-equivalent for gap_open, gap_extend <= 0.
+bool needs_three_state(int gap_open, int gap_extend) { return gap_open > 0 || gap_extend > 0 || gap_open + gap_extend > 0; }
+
+int launch_three_state(swgpu_db* db, swgpu_slot& S, cudaStream_t stream, int lq, int oe, int ge, unsigned* queue, int* launches) {
+  const int grid = db->sm_count;                                     // 4 warps per CTA, one carry row of the longest target each
+  const int64_t stride = ((int64_t)std::max<int32_t>(db->max_len, 32) + 31) & ~31ll;
+  const int64_t need = (int64_t)grid * swk::K3_WARPS * stride;
+  if (need > S.bnd3s_cap) {
+    cudaFree(S.d_bnd3s); S.d_bnd3s = nullptr; S.bnd3s_cap = need;
+    CU(cudaMalloc((void**)&S.d_bnd3s, sizeof(int2) * (size_t)need));
+  }
+  swk::K3Params P; memset(&P, 0, sizeof(P));
+  P.worklist = nullptr; P.work_count = nullptr; P.n_work = (int)db->n; P.counter = queue;
+  P.plain = db->d_plain; P.plain_off = db->d_plain_off; P.query = S.d_query; P.lq = lq; P.table = S.d_table;
+  P.oe = oe; P.ge = ge; P.bnd = S.d_bnd3s; P.bnd_stride = stride; P.order = db->d_order;
+  P.scores_file = S.d_scores; P.one = 1u; P.max_len = 0;
+  if (lq <= 128) swk::k3_three<4><<<grid, swk::K3_WARPS * 32, 0, stream>>>(P);
+  else           swk::k3_three<8><<<grid, swk::K3_WARPS * 32, 0, stream>>>(P);
+  CU(cudaGetLastError());
+  ++*launches;
+  return SWGPU_OK;
+}
+
 int check_args(swgpu_db* db, const int8_t* query, int64_t lq, const int8_t* table, int gap_open, int gap_extend) {
   if (!db) return fail(SWGPU_EINVAL, "null database handle");
   if (lq < 0 || (lq > 0 && !query) || !table) return fail(SWGPU_EINVAL, "bad query/table argument");
   if (lq > 0x7fffffff) return fail(SWGPU_EINVAL, "query too long");
   const int oe = gap_open + gap_extend, ge = gap_extend;
-  if (oe > 0 || ge > 0 || gap_open > 0)
-    return fail(SWGPU_EINVAL, "positive gap scores are outside the supported (and the reference-equivalent) range");
-  if (oe < -100000 || ge < -100000) return fail(SWGPU_EINVAL, "gap penalty out of range");
+  if (oe < -100000 || ge < -100000 || oe > 100000 || ge > 100000) return fail(SWGPU_EINVAL, "gap score out of range");
   for (int64_t i = 0; i < lq; ++i) if (query[i] < 0 || query[i] > 31) return fail(SWGPU_EINVAL, "query code outside 0..31");
   return SWGPU_OK;
 }
@@ -438,7 +461,8 @@ int enqueue_search(swgpu_db* db, swgpu_slot& S, const int8_t* query, int64_t lq,
   // ---- plan ----
   // 16-bit path: biased unsigned arithmetic with B = 128 + |oe| + |ge| (sw_k1s.cuh); huge gap penalties go 32-bit.
   const unsigned B = swk::k1s_bias(oe, ge);
-  const bool use16 = (B <= 16384u) && db->n_streams > 0 && lq > 0;
+  const bool three = needs_three_state(gap_open, gap_extend);
+  const bool use16 = !three && (B <= 16384u) && db->n_streams > 0 && lq > 0;
   const K1SPlan plan = plan_k1s(std::max<int64_t>(lq, 1), db->n_streams, db->k1s_grid * swk::K1S_WARPS);
   // Long streams (one target pair of thousands of columns) are latency-bound on their serial column chain: when the
   // bulk plan uses fewer than 32 lanes per pair they get their own launch with all 32 lanes and the fewest rows per
@@ -466,6 +490,7 @@ int enqueue_search(swgpu_db* db, swgpu_slot& S, const int8_t* query, int64_t lq,
       CU(cudaMalloc((void**)&S.d_sprof2, S.sprof2_cap * sizeof(unsigned)));
     }
   }
+  S.three_state = three;
   S.use16 = use16; S.split_long = split_long; S.n_split_pairs = split_long ? n_split_pairs : 0; S.lq = lq; S.oe = oe; S.ge = ge;
 
   // ---- timed region: first kernel -> last result resident in HBM ----
@@ -567,8 +592,9 @@ int enqueue_search(swgpu_db* db, swgpu_slot& S, const int8_t* query, int64_t lq,
     CU(cudaEventRecord(e[5], sm));
     CU(cudaStreamWaitEvent(sa, e[5], 0));
     CU(cudaEventRecord(e[1], sa));
-    if ((r = launch_32bit(db, S, sa, nullptr, nullptr, (int)db->n, (int)lq, oe, ge, S.d_counters + 5, S.d_counters + 4,
-                          &st.kernel_launches))) return r;
+    if (three) r = launch_three_state(db, S, sa, (int)lq, oe, ge, S.d_counters + 5, &st.kernel_launches);
+    else r = launch_32bit(db, S, sa, nullptr, nullptr, (int)db->n, (int)lq, oe, ge, S.d_counters + 5, S.d_counters + 4, &st.kernel_launches);
+    if (r) return r;
   }
   CU(cudaEventRecord(e[2], sa));
   S.in_flight = true;
@@ -690,8 +716,8 @@ int fill_batch16(int device, const int8_t* query, int64_t query_len, const int8_
     return fail(SWGPU_EINVAL, "bad batch argument");
   if (query_len > 0x7fffffff || padded_len > 0x7ffffff0) return fail(SWGPU_EINVAL, "batch too long");
   const int oe = gap_open + gap_extend, ge = gap_extend;
-  if (oe > 0 || ge > 0 || gap_open > 0)
-    return fail(SWGPU_EINVAL, "positive gap scores are outside the supported (and the reference-equivalent) range");
+  if (oe < -100000 || ge < -100000 || oe > 100000 || ge > 100000) return fail(SWGPU_EINVAL, "gap score out of range");
+  const bool three = needs_three_state(gap_open, gap_extend);      // a positive gap score: the reference's three-state form
   if (device < 0 || device >= 16) return fail(SWGPU_EINVAL, "device %d out of range", device);
   if (int r = pick_device(device)) return r;
   static thread_local Batch16Ctx ctxs[16];
@@ -757,8 +783,10 @@ int fill_batch16(int device, const int8_t* query, int64_t query_len, const int8_
     P.plain = c.d_codes; P.plain_off = c.d_off; P.query = c.d_query; P.lq = (int)query_len; P.table = c.d_table;
     P.oe = oe; P.ge = ge; P.bnd = c.d_bnd; P.bnd_stride = c.bnd_stride; P.order = c.d_order;
     P.scores_file = c.d_scores; P.one = 1u; P.max_len = 0;
-    if (query_len <= 128) swk::k3_intra<4><<<kWarps / swk::K3_WARPS, swk::K3_WARPS * 32, 0, st>>>(P);
-    else                  swk::k3_intra<8><<<kWarps / swk::K3_WARPS, swk::K3_WARPS * 32, 0, st>>>(P);
+    if (three && query_len <= 128) swk::k3_three<4><<<kWarps / swk::K3_WARPS, swk::K3_WARPS * 32, 0, st>>>(P);
+    else if (three)                swk::k3_three<8><<<kWarps / swk::K3_WARPS, swk::K3_WARPS * 32, 0, st>>>(P);
+    else if (query_len <= 128)     swk::k3_intra<4><<<kWarps / swk::K3_WARPS, swk::K3_WARPS * 32, 0, st>>>(P);
+    else                           swk::k3_intra<8><<<kWarps / swk::K3_WARPS, swk::K3_WARPS * 32, 0, st>>>(P);
     CU(cudaGetLastError());
   }
   CU(cudaMemcpyAsync(c.h_scores, c.d_scores, sizeof(int32_t) * 16, cudaMemcpyDeviceToHost, st));

@@ -40,6 +40,7 @@ struct swgpu_slot {
   uint2*    d_xs_bnd = nullptr;  int64_t xs_bnd_cap = 0;       // two rows per X stream (2 * its columns)
   unsigned* d_xs_progress = nullptr;  unsigned* d_xs_raw = nullptr;  int64_t xs_prog_cap = 0, xs_raw_cap = 0;
   int2*     d_bnd3 = nullptr;          // k3_intra carry rows
+  int2*     d_bnd3s = nullptr;  int64_t bnd3s_cap = 0;   // k3_three (positive gap scores) carry rows: full target length, allocated on first use
   // k3x (32-bit wavefront over many warps): target slots
   int4*     d_x_rows = nullptr;        // [K3X_SLOTS][2][x_row_stride] (H, tag, V, tag)
   int4*     d_x_partial = nullptr;  int x_stripes_cap = 0;   // [K3X_SLOTS][x_stripes_cap]
@@ -62,6 +63,7 @@ struct swgpu_slot {
   int32_t* h_scores = nullptr;  int64_t h_scores_cap = 0;   // staging when the caller's score buffer is pageable
   // host-side state of the search in flight / last finished
   bool in_flight = false, have_scores = false, use16 = false, split_long = false;
+  bool three_state = false;                    // last search ran the reference's three-state recurrence (a gap score was positive)
   int64_t n_split_pairs = 0;                   // pairs scored by the separate long-stream launch of this search
   int64_t lq = 0;  int oe = 0, ge = 0;
   int topk_k = 0, topk_launches = 0;

@@ -113,6 +113,9 @@ namespace swi {
 // Queue selection + coordinate passes + read-back of the k hits on the slot's high-priority stream, behind the
 // search queued on it.  No host synchronisation (buffers grow on first use only); 1 <= k <= min(65536, n).
 int enqueue_topk(swgpu_db* db, swgpu_slot& S, int k) {
+  if (S.three_state)
+    return fail(SWGPU_EINVAL, "top-k with coordinates is not available with positive gap scores (the coordinate passes use the "
+                "two-gap-state form); the per-entry scores are");
   cudaStream_t st = S.s_aux;
   if (k > S.topk_cap) {
     cudaFree(S.d_keys); cudaFree(S.d_hit_sidx); cudaFree(S.d_coords);

@@ -370,7 +370,12 @@ void align_from_query_and_db(const char *query_path, const char *db_path, scorin
     int g = 1;
     const char *eg = getenv("SWGPU_GPUS");
     if (eg && atoi(eg) > 0) g = atoi(eg);
-    if (g > ndev) g = ndev;
+    /* SWGPU_GPUS_SHARE_DEVICE=1: more shards than devices are allowed and share the devices round-robin (the shard /
+     * merge path on a box with fewer GPUs; the shards' searches then run concurrently on one device) */
+    const char *esh = getenv("SWGPU_GPUS_SHARE_DEVICE");
+    const int share = esh && atoi(esh) > 0;
+    if (g > ndev && !share) g = ndev;
+    if (g > 64) g = 64;
     if ((int64_t)g > d.n) g = d.n ? (int)d.n : 1;
     int topk = 0;
     const char *ek = getenv("SWGPU_TOPK");
@@ -391,7 +396,7 @@ void align_from_query_and_db(const char *query_path, const char *db_path, scorin
     pthread_t *th = (pthread_t *)calloc((size_t)g, sizeof(pthread_t));
     for (int s = 0; s < g; s++) {
         shard_job_t *j = &jobs[s];
-        j->device = s; j->nq = nq; j->queries = (const int8_t *const *)qi; j->qlens = qlen; j->sc = scoring;
+        j->device = s % ndev; j->nq = nq; j->queries = (const int8_t *const *)qi; j->qlens = qlen; j->sc = scoring;
         j->scores_file = scores;
         j->topk = topk;
         j->hits = topk ? (swgpu_hit_t *)calloc((size_t)topk * (size_t)nq, sizeof(swgpu_hit_t)) : NULL;

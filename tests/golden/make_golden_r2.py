@@ -10,6 +10,8 @@
                      (wrapped where the true score exceeds 32 767) and the int32 scalar oracle's true scores.
   c4_sample.npz      C4 (35 213-aa query x 1 024 targets): int32 scalar-oracle scores of 120 targets incl. all 16
                      titin-length ones and the 90 %-identity copy.
+  ref16_posgap.npz   positive gap scores (the reference's three-state recurrence): the unmodified kernel's scores for 272
+                     short targets x 3 query lengths x 6 gap settings, and the reference CLI's stdout for --gapopen 1 --gapextend 1.
   upstream_hits.npz  the upstream seq-align ELF the reference's own differential test drives
                      (/root/reference/test/smith_waterman, test/tests.py:58-73): `hit 0.0` of ~200 planted pairs under
                      {PAM250, default gaps -2/-1} and {BLOSUM62, -10/-1}: score, [pos; len] of both sequences and
@@ -129,8 +131,65 @@ def gen_upstream():
     print("upstream:", len(sc), "pairs; scores", int(sc.min()), "..", int(sc.max()), "; no hit:", int((sc == 0).sum()))
 
 
+POS_GAPS = [(1, -3), (2, -1), (0, 1), (1, 1), (-5, 2), (3, 0)]
+
+
+def gen_posgap():
+    """Positive gap scores: the reference accepts them (src/alignment_cmdline.c:255-267) and runs its three-state recurrence
+    on them (src/alignment.c:124-161).  With positive gap scores the reference's '*' padding rows are NOT neutral (E / F keep
+    growing across them and feed M), so its result depends on the batch a target sits in -- the same class of quirk as
+    SURVEY.md A.5.  Hence two sets:
+      equal   17 batches of 16 EQUAL-length targets (no padding): reference == per-target truth; the engine must match;
+      ragged  3 ordinary batches: the reference's padded computation, which swgpu_fill_batch16 / alignment_fill_matrices
+              (the twins of that computation) must reproduce.
+    Plus the reference CLI's stdout with --gapopen 1 --gapextend 1 on a database of two equal-length batches."""
+    import tempfile
+    tab, _ = synth.load_matrix(os.path.join(ROOT, "scoring", "BLOSUM62.txt"))
+    g = synth.rng(606)
+    q = synth.make_query(607, 300)
+
+    def related(codes, off, step):
+        for k in range(0, len(off) - 1, step):
+            L = int(off[k + 1] - off[k]); src = np.resize(q, L).copy(); mut = g.random(L) < 0.2
+            src[mut] = synth.residues(g, int(mut.sum())); codes[off[k]:off[k + 1]] = src
+
+    lens = np.repeat(np.sort(g.integers(1, 180, size=17))[::-1], 16)
+    off = np.zeros(len(lens) + 1, dtype=np.int64); np.cumsum(lens, out=off[1:])
+    codes = synth.residues(g, off[-1]); related(codes, off, 4)
+    rl = np.sort(g.integers(1, 150, size=48))[::-1]
+    roff = np.zeros(49, dtype=np.int64); np.cumsum(rl, out=roff[1:])
+    rcodes = synth.residues(g, roff[-1]); related(rcodes, roff, 3)
+    res = {}
+    for lq in (40, 130, 300):
+        for go, ge in POS_GAPS:
+            s16, _ = O.ref_search16(q[:lq], codes, off, tab, go, ge, threads=THREADS)
+            s32 = O.search32(q[:lq], codes, off, tab, go, ge, threads=THREADS)
+            assert int(s32.max()) < 32000 and np.array_equal(s16.astype(np.int32), s32), (lq, go, ge)
+            res[f"s_{lq}_{go}_{ge}"] = s16
+            r16, _ = O.ref_search16(q[:lq], rcodes, roff, tab, go, ge, threads=THREADS)
+            pad = [O.score16_wrap(q[:lq], rcodes[roff[t]:roff[t + 1]], int(rl[t // 16 * 16]), tab, go, ge) for t in range(48)]
+            assert list(r16) == pad, (lq, go, ge)               # the restatement of the padded arithmetic agrees
+            res[f"r_{lq}_{go}_{ge}"] = r16
+    print("posgap: max score", max(int(v.max()) for v in res.values()),
+          "; ragged targets whose padded score differs from the unpadded one:",
+          int(sum((res[f"r_300_{go}_{ge}"].astype(np.int32) != O.search32(q, rcodes, roff, tab, go, ge)).sum() for go, ge in POS_GAPS)))
+    cl = np.repeat([70, 41], 16)
+    coff = np.zeros(33, dtype=np.int64); np.cumsum(cl, out=coff[1:])
+    ccodes = synth.residues(g, coff[-1]); related(ccodes, coff, 5)
+    cq = q[:90]
+    with tempfile.TemporaryDirectory() as td:
+        qf, df = os.path.join(td, "q.fa"), os.path.join(td, "db.fa")
+        synth.to_fasta(qf, cq, np.array([0, len(cq)]), prefix="query"); synth.to_fasta(df, ccodes, coff, prefix="sp")
+        r = subprocess.run([O.REF_BIN, "--substitution_matrix", os.path.join(ROOT, "scoring", "BLOSUM62.txt"), "--gapopen", "1",
+                            "--gapextend", "1", "--files", qf, df], capture_output=True, text=True, env={**os.environ, "OMP_NUM_THREADS": "2"})
+        assert r.returncode == 0, r.stderr
+        cli, qtxt, dtxt = r.stdout.replace(td, "TMP"), open(qf).read(), open(df).read()
+    np.savez_compressed(os.path.join(OUT, "ref16_posgap.npz"), codes=codes, off=off, rcodes=rcodes, roff=roff, query=q, table=tab,
+                        cli_stdout=cli, cli_query_fasta=qtxt, cli_db_fasta=dtxt, **res)
+
+
 if __name__ == "__main__":
     assert O.have_ref(), "build oracle/_ref first (make -C oracle)"
-    which = sys.argv[1:] or ["c2", "c3", "c4", "upstream"]
+    which = sys.argv[1:] or ["c2", "c3", "c4", "upstream", "posgap"]
     for w in which:
-        {"c2": gen_c2, "c3": gen_c3, "c4": gen_c4, "upstream": gen_upstream}[w]()
+        {"c2": gen_c2, "c3": gen_c3, "c4": gen_c4, "upstream": gen_upstream, "posgap": gen_posgap}[w]()

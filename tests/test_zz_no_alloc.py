@@ -78,4 +78,4 @@ def test_noalloc_entry_point_rejects_sizes_beyond_the_static_scratch():
     rc = f(0, None, 10, None, None, 4, MAX_LEN + 1, None, -10, -1, None, None)
     assert rc == -3 and "SWGPU_NOALLOC_MAX_TARGET_LEN" in L.swgpu_last_error().decode()
     assert f(0, None, 10, None, None, -1, 100, None, -10, -1, None, None) == -3
-    assert f(0, None, 10, None, None, 4, 100, None, 5, -1, None, None) == -3         # positive gap score, as swgpu_search()
+    assert f(0, None, 10, None, None, 4, 100, None, 5, -1, None, None) == -3         # a positive gap score: this entry point has the two-gap-state kernel only
