@@ -147,7 +147,14 @@ static int layout_streams(swpack_t *p, int32_t stream_cols, int32_t taper, int64
     }
     p->stream_off[n_streams] = off;
     p->n_long_streams = 0;
-    while (p->n_long_streams < n_streams && p->stream_ncols[p->n_long_streams] > SWPACK_LONG_STREAM_COLS) p->n_long_streams++;
+    /* long = the stream's FIRST pair alone is longer than SWPACK_LONG_STREAM_COLS (a titin-like target, a serial chain of
+     * that many columns).  Pairs are sorted by length, so these streams are a prefix for any stream_cols; counting by
+     * stream length instead would make every stream "long" once stream_cols >= the threshold. */
+    while (p->n_long_streams < n_streams) {
+        const int64_t q0 = p->stream_pair0[p->n_long_streams];
+        if (p->plain_off[2 * q0 + 1] - p->plain_off[2 * q0] <= SWPACK_LONG_STREAM_COLS) break;
+        p->n_long_streams++;
+    }
     p->n_long_pairs = p->n_long_streams < n_streams ? p->stream_pair0[p->n_long_streams] : n_pairs;
     p->scols_len = off;
     p->max_stream_cols = maxc;

@@ -34,7 +34,7 @@ typedef struct {
     int8_t  *plain;           /* [n_residues] residues, sorted order                     */
     int64_t  n_pairs, n_streams;
     int32_t  max_stream_cols;
-    int64_t  n_long_streams;  /* leading streams with more than SWPACK_LONG_STREAM_COLS columns */
+    int64_t  n_long_streams;  /* leading streams whose first pair alone has more than SWPACK_LONG_STREAM_COLS columns */
     int64_t  n_long_pairs;    /* pairs inside those streams                              */
     uint16_t *scols;          /* [scols_len] stream columns, each stream 64-column aligned */
     int64_t  scols_len;

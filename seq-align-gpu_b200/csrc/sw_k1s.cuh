@@ -413,7 +413,7 @@ static __global__ void k1s_finalize(const unsigned* __restrict__ raw, long pair_
                                     unsigned B, unsigned limit, const int64_t* __restrict__ order,
                                     const int64_t* __restrict__ plain_off, int long_thr,
                                     int32_t* __restrict__ scores_file, int* __restrict__ rescore_list,
-                                    unsigned* __restrict__ rescore_count) {
+                                    unsigned* __restrict__ rescore_count, unsigned long long* __restrict__ rescore_residues) {
   for (long p = pair_begin + blockIdx.x * (long)blockDim.x + threadIdx.x; p < n_pairs; p += (long)gridDim.x * blockDim.x) {
     const unsigned* r = raw + (size_t)p * (size_t)slots;
     unsigned m = r[0];
@@ -428,6 +428,7 @@ static __global__ void k1s_finalize(const unsigned* __restrict__ raw, long pair_
       if (sat || force) {
         const unsigned slot = atomicAdd(rescore_count, 1u);
         rescore_list[slot] = (int)s;
+        atomicAdd(rescore_residues, (unsigned long long)(plain_off[s + 1] - plain_off[s]));      // statistics: cells of the 32-bit pass
       } else {
         scores_file[order[s]] = (int32_t)((h ? hi : lo) - B);
       }

@@ -10,8 +10,8 @@
 //   * stripe s-1 -> stripe s: the bottom row goes through a full-length row in global memory (two rows per target
 //     slot, ping-pong by stripe parity).  Every column is ONE aligned 16-byte store (H, tag, V, tag) by the
 //     producer's lane 31 and one 16-byte volatile load by the consumer, which simply re-reads until both tags are
-//     the producer's (tag = f(item, launch epoch), so neither an older stripe of the same parity nor an earlier
-//     launch can be mistaken for it).  The flag travels with the data: no fence, no separate progress word
+//     the producer's (two item-specific tag words, see k3x_tag_a / k3x_tag_b: neither an older stripe of the same parity
+//     nor an earlier launch nor a torn record can be mistaken for it).  The flag travels with the data: no fence, no separate progress word
 //     (the first version published a counter with st.release.gpu every 32 columns and polled it with
 //     ld.acquire.gpu: the MEMBAR and the L1 invalidate were the two hottest instructions in ncu);
 //   * target slots (rows, per-stripe results) are reused round-robin: a warp starts an item of
@@ -67,9 +67,13 @@ __device__ __forceinline__ int4 ld_volatile_v4(const int4* p) {
 __device__ __forceinline__ void st_volatile_v4(int4* p, int a, int b, int c, int d) {
   asm volatile("st.volatile.global.v4.s32 [%0], {%1, %2, %3, %4};" :: "l"(p), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
-__device__ __forceinline__ int k3x_tag(long long item, unsigned epoch) {
-  return (int)((((unsigned)(item + 1) * 2654435761u) ^ (epoch * 40503u + 0x5bd1e995u)) | 1u);   // never 0 (zeroed rows)
-}
+// Hand-over tags of a column: TWO words, one in each 8-byte half of the 16-byte (H, tagA, V, tagB) record, both specific
+// to the item, so a half that is stale (an older stripe of the same parity, an earlier launch) or torn cannot pass:
+//   tagA = item + 1                     (items are numbered below 2^32 - 1, checked by the host: never 0 = a zeroed row)
+//   tagB = tagA ^ (epoch * odd + 1)     (injective in the launch epoch for a given item)
+// Equality on both is exact -- no hash, no collision (round 1 used one 31-bit hash in both words).
+__device__ __forceinline__ int k3x_tag_a(long long item) { return (int)(unsigned)(item + 1); }
+__device__ __forceinline__ int k3x_tag_b(long long item, unsigned epoch) { return (int)((unsigned)(item + 1) ^ (epoch * 0x9E3779B9u + 1u)); }
 __device__ __forceinline__ unsigned ld_acquire_u32(const unsigned* p) {
   unsigned v;
   asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
@@ -161,7 +165,8 @@ __global__ void __launch_bounds__(K3X_WARPS * 32) k3x(const K3XParams P) {
       const bool has_in = stripe > 0, has_out = stripe + 1 < nstripes;
       const int4* row_in = P.rows + ((size_t)slot * 2 + ((stripe + 1) & 1)) * (size_t)P.row_stride;
       int4* row_out = P.rows + ((size_t)slot * 2 + (stripe & 1)) * (size_t)P.row_stride;
-      const int tag_in = k3x_tag(item - 1, P.epoch), tag_out = k3x_tag(item, P.epoch);
+      const int tag_in_a = k3x_tag_a(item - 1), tag_in_b = k3x_tag_b(item - 1, P.epoch);
+      const int tag_out_a = k3x_tag_a(item), tag_out_b = k3x_tag_b(item, P.epoch);
       int H[R3], G[R3];
 #pragma unroll
       for (int k = 0; k < R3; ++k) { H[k] = 0; G[k] = 0; }
@@ -178,7 +183,7 @@ __global__ void __launch_bounds__(K3X_WARPS * 32) k3x(const K3XParams P) {
             unsigned spins = 0;
             for (;;) {
               b = ld_volatile_v4(&row_in[j]);
-              if (b.y == tag_in && b.w == tag_in) break;
+              if (b.y == tag_in_a && b.w == tag_in_b) break;
               __nanosleep(40);
               if (++spins > K3X_SPIN_LIMIT) { atomicExch(P.error_flag, 1u); break; }
             }
@@ -218,7 +223,7 @@ __global__ void __launch_bounds__(K3X_WARPS * 32) k3x(const K3XParams P) {
           if (TRACK && in_range && k3x_better(colbest, j, row0 + colk, best, bj, bi)) { best = colbest; bj = j; bi = row0 + colk; }
           out_h = H[R3 - 1];
           out_v = V;
-          if (lane == 31 && has_out && in_range) st_volatile_v4(pcol, out_h, tag_out, out_v, tag_out);
+          if (lane == 31 && has_out && in_range) st_volatile_v4(pcol, out_h, tag_out_a, out_v, tag_out_b);
         }
         ++pcol;
       }

@@ -521,7 +521,7 @@ int enqueue_search(swgpu_db* db, swgpu_slot& S, const int8_t* query, int64_t lq,
       if ((r = launch_k1s(db, PL, 32, plan_long.R, false, oe, ge, sa, (int)std::min<int64_t>(nls, db->k1s_grid)))) return r;
       swk::k1s_finalize<<<std::max(1, (int)((nlp + 255) / 256)), 256, 0, sa>>>(
           S.d_raw_s, 0, (long)nlp, 32, (long)db->n, B, limit, db->d_order, db->d_plain_off, db->long_threshold,
-          S.d_scores, S.d_rescore_list, S.d_counters + 2);
+          S.d_scores, S.d_rescore_list, S.d_counters + 2, reinterpret_cast<unsigned long long*>(S.d_counters + 12));
       CU(cudaGetLastError()); st.kernel_launches += 3;
     }
     CU(cudaEventRecord(e[4], sa));
@@ -572,14 +572,14 @@ int enqueue_search(swgpu_db* db, swgpu_slot& S, const int8_t* query, int64_t lq,
       if (nxp > 0) {
         swk::k1s_finalize<<<std::max(1, (int)((nxp + 255) / 256)), 256, 0, sm>>>(
             S.d_xs_raw, 0, (long)nxp, 32 * plan.npass, (long)db->n, B, limit, db->d_order, db->d_plain_off,
-            db->long_threshold, S.d_scores, S.d_rescore_list, S.d_counters + 2);
+            db->long_threshold, S.d_scores, S.d_rescore_list, S.d_counters + 2, reinterpret_cast<unsigned long long*>(S.d_counters + 12));
         st.kernel_launches++;
       }
       const int64_t pb = nlp + nxp;                            // first pair scored by the bulk items
       if (db->n_pairs > pb)
         swk::k1s_finalize<<<(int)std::min<int64_t>((db->n_pairs - pb + 255) / 256, 4096), 256, 0, sm>>>(
             PS.raw, (long)pb, (long)db->n_pairs, 1 << plan.g_log2, (long)db->n, B, limit, db->d_order, db->d_plain_off,
-            db->long_threshold, S.d_scores, S.d_rescore_list, S.d_counters + 2);
+            db->long_threshold, S.d_scores, S.d_rescore_list, S.d_counters + 2, reinterpret_cast<unsigned long long*>(S.d_counters + 12));
       CU(cudaGetLastError()); st.kernel_launches += 2;
     }
     CU(cudaEventRecord(e[5], sm));
@@ -656,13 +656,9 @@ int collect_search(swgpu_db* db, swgpu_slot& S, swgpu_stats_t* stats) {
       if (S.split_long) { CU(cudaEventElapsedTime(&ms, e[3], e[4])); st.ms_intra = ms; st.n_long = 2 * S.n_split_pairs; }
       st.cells_inter = st.cells;
       st.n_rescored = ctr[2];
-      if (ctr[2]) {
-        std::vector<int> lst(ctr[2]);
-        CU(cudaMemcpy(lst.data(), S.d_rescore_list, sizeof(int) * ctr[2], cudaMemcpyDeviceToHost));
-        int64_t res = 0;
-        for (int s : lst) res += db->h_len_sorted_prefix[s + 1] - db->h_len_sorted_prefix[s];
-        st.cells_rescore = lq * res;
-      }
+      // residues of the rescored targets: summed on the device by k1s_finalize (counters 12..13, one 64-bit word), read back
+      // with the other counters -- no extra copy, nothing blocking inside the pipelined swgpu_search_many()
+      st.cells_rescore = lq * (int64_t)(((unsigned long long)ctr[13] << 32) | ctr[12]);
     } else {
       st.ms_rescore = st.ms_total; st.n_rescored = db->n; st.cells_rescore = st.cells;
     }

@@ -34,7 +34,7 @@ struct swgpu_slot {
   int*      d_rescore_list = nullptr;  // up to n
   unsigned* d_counters = nullptr;      // [0] k1s queue, [1] k1s long queue, [2] rescore count, [3] k3 queue, [4] k3x queue,
                                        // [5] k3 all-targets queue, [6] k3x error flag, [7] top-k error flag,
-                                       // [8] top-k coordinate queue phase 0, [9] phase 1
+                                       // [8] top-k coordinate queue phase 0, [9] phase 1, [12..13] residues of the rescored targets (u64)
   uint2*    d_bnd_s = nullptr;         // k1s multi-stripe carry rows
   // k1s X items (long streams, one stripe per item): ping-pong rows, progress words, per-stripe maxima
   uint2*    d_xs_bnd = nullptr;  int64_t xs_bnd_cap = 0;       // two rows per X stream (2 * its columns)

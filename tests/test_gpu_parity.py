@@ -205,7 +205,7 @@ def test_32bit_kernels_on_everything(swgpu_mod, oracle, matrices):
     codes = np.concatenate(parts)
     for lq in (2700, 100, 129):
         got, st = check(swgpu_mod, oracle, q[:lq], codes, off, matrices["BLOSUM45"], -12, -2, long_threshold=1)
-        assert st["n_rescored"] == len(parts)
+        assert st["n_rescored"] == len(parts) and st["cells_rescore"] == st["cells"] == lq * int(off[-1])   # summed on the device
     # huge gap penalties: the 16-bit bias does not fit -> the 32-bit kernels score the whole database directly
     got, st = check(swgpu_mod, oracle, q[:300], codes, off, matrices["BLOSUM62"], -20000, -1)
     assert st["tile_rows"] == 0

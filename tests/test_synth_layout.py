@@ -218,7 +218,8 @@ def test_packer_invariants_on_random_databases(seed):
         scols = arr(p.scols, p.scols_len, np.uint16)
         assert np.all(soff % 64 == 0) and pair0[0] == 0 and np.all(np.diff(pair0) > 0) and p.max_stream_cols == ncols.max()
         nl = int(p.n_long_streams)
-        assert np.all(ncols[:nl] > 4096) and (nl == ns or ncols[nl] <= 4096)
+        first_pair = np.array([int(sl[2 * q0]) for q0 in pair0])              # a long stream = its FIRST pair alone exceeds 4096 columns
+        assert np.all(first_pair[:nl] > 4096) and (nl == ns or first_pair[nl] <= 4096), (nl, first_pair[:nl + 1])
         q = 0
         for st in range(ns):
             col = soff[st]
