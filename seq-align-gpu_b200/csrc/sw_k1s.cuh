@@ -155,10 +155,16 @@ constexpr int K1S_RING_WORDS = 160;           // column ring per warp: (32 / g) 
 #endif
 // columns per loop iteration (A/B knobs, scripts/build_variant.sh)
 #ifndef K1S_UNROLL_SINGLE
-#define K1S_UNROLL_SINGLE 2
-#endif
+#define K1S_UNROLL_SINGLE 4                  // four columns: 0.23 register moves per row left (two columns: 0.47, one: 1.03); 1-4 % faster at
+#endif                                       // every single-stripe length of the C2 sweep (profiles/r2d_ab_unroll4.txt)
 #ifndef K1S_UNROLL_MULTI
 #define K1S_UNROLL_MULTI 1
+#endif
+// 1: single-stripe kernels load the ring word of step s + 1 at the end of step s, so that the shared-memory latency is not at
+// the head of every step's dependency chain (1-2 % at most single-stripe lengths; the multi-stripe kernel, which would also
+// prefetch the boundary pair of the stripe above, measured 0.2-1.8 % SLOWER with it and keeps the direct loads)
+#ifndef K1S_PREFETCH
+#define K1S_PREFETCH 1
 #endif
 
 template <int R, bool MULTI>
@@ -192,7 +198,8 @@ __global__ void __launch_bounds__(K1S_WARPS * 32, (R <= K1S_R3CTA ? 3 : 2)) k1s(
 
   constexpr int g = LANES, g_log2 = (LANES == 8 ? 3 : LANES == 16 ? 4 : 5);
   constexpr int UN = MULTI ? K1S_UNROLL_MULTI : K1S_UNROLL_SINGLE;
-  static_assert(UN == 1 || UN == 2, "columns per loop iteration");
+  constexpr bool PF = K1S_PREFETCH != 0 && !MULTI;       // single-stripe only (measured: the multi-stripe kernel is 0.2-1.8 % slower with it)
+  static_assert(UN == 1 || UN == 2 || UN == 4, "columns per loop iteration");
   const int lane_g = lane & (g - 1), grp = lane >> g_log2, per_warp = 32 >> g_log2;
   constexpr int RN = 2 * g;
   // segments are g words apart modulo the 32 banks: the groups of a warp read their rings in the same instruction, each
@@ -313,6 +320,7 @@ __global__ void __launch_bounds__(K1S_WARPS * 32, (R <= K1S_R3CTA ? 3 : 2)) k1s(
         }
       };
 
+      unsigned cw_next = 0;
       for (int s0 = 0; s0 < nsteps; s0 += UN) {
         if ((s0 & (g - 1)) == 0) {                 // every g steps: publish the prefetched block, fetch the next
           __syncwarp();
@@ -331,11 +339,12 @@ __global__ void __launch_bounds__(K1S_WARPS * 32, (R <= K1S_R3CTA ? 3 : 2)) k1s(
           __syncwarp();
           // columns [0, s0 - 31) of this stripe's bottom row are in memory (written by the whole warp above, ordered by the __syncwarp)
           if (MULTI && has_out && is31 && s0 > 31) k1s_st_release(prog, (unsigned)min(s0 - 31, ncols));
+          if (PF) cw_next = lds32_ordered(rd_lane + ((unsigned)(s0 & (RN - 1)) << 2));   // the word prefetched for this step predates the publish
         }
 #pragma unroll
         for (int u = 0; u < UN; ++u) {
           const int s = s0 + u;
-          const unsigned cw = lds32_ordered(rd_lane + ((unsigned)(s & (RN - 1)) << 2));
+          const unsigned cw = PF ? cw_next : lds32_ordered(rd_lane + ((unsigned)(s & (RN - 1)) << 2));
           unsigned h_up, v_in;
           if (MULTI) {                              // first lane: the stripe above (constants in the first stripe), via the shuffle's default
             unsigned bx, by;
@@ -393,6 +402,7 @@ __global__ void __launch_bounds__(K1S_WARPS * 32, (R <= K1S_R3CTA ? 3 : 2)) k1s(
           out_h = H[R - 1];
           out_v = V;
           if (MULTI && !last && is31) ring3[s & 31] = make_uint2(out_h, out_v);
+          if (PF) cw_next = lds32_ordered(rd_lane + ((unsigned)((s + 1) & (RN - 1)) << 2));   // next step's ring word (re-loaded after a publish, above)
         }
       }
       if (MULTI && !last && nsteps > 0) {          // the columns of the last (partial) block of steps
