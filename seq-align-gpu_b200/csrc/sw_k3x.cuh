@@ -55,6 +55,15 @@ struct K3XParams {
   int4*           coords;       // TRACK: per target (q_start, q_end, t_start, t_end)
   int*            best_out;     // TRACK phase 0: score found
   int             phase;        // TRACK: 0 = forward (end cell), 1 = reversed prefixes (start cell)
+  // TRACK, early stop: the hit's score S is known (hit_keys[t] >> 32), so a pass is over as soon as every column up to the
+  // first column that holds a cell with H == S has been evaluated -- later columns cannot win the tie-break (SURVEY.md A.7:
+  // smallest target position first).  stop_col[t] (initialised to a huge value) is lowered with atomicMin by whichever
+  // stripe sees S; a warp leaves when all its remaining columns lie beyond it, a lane stops waiting for an input column
+  // beyond it (it computes on zeros instead: the recurrence is monotone in its boundary values, so such cells can only come out
+  // LOWER than the truth, never above S), and candidates beyond it are ignored.  The reversed pass
+  // typically ends after the ~100 columns of the alignment itself instead of the whole prefix.
+  const unsigned long long* hit_keys;   // TRACK: sorted keys of the hits (score << 32 | ~entry); nullptr = no early stop
+  int*            stop_col;     // TRACK: [n_targets] for this phase
   unsigned*       error_flag;
   int             min_len;      // !TRACK: targets shorter than this are left to k3_intra
 };
@@ -77,6 +86,12 @@ __device__ __forceinline__ int k3x_tag_b(long long item, unsigned epoch) { retur
 __device__ __forceinline__ unsigned ld_acquire_u32(const unsigned* p) {
   unsigned v;
   asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+__device__ __forceinline__ int ld_volatile_s32(const int* p) {
+  int v;
+  asm volatile("ld.volatile.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
 
@@ -147,6 +162,10 @@ __global__ void __launch_bounds__(K3X_WARPS * 32) k3x(const K3XParams P) {
     if (!TRACK && lt < P.min_len) skip = true;             // this target belongs to k3_intra
     const int nstripes = skip ? 0 : (lq + 32 * R3 - 1) / (32 * R3);
     int best = 0, bj = 0x7fffffff, bi = 0x7fffffff;
+    const bool early = TRACK && P.hit_keys != nullptr;
+    const int known = early ? (int)(P.hit_keys[t] >> 32) : 0x7fffffff;      // the hit's score
+    int* stop_p = early ? P.stop_col + t : nullptr;
+    int stop = 0x7fffffff;                                  // this lane's view of stop_col[t] (only ever decreases)
 
     if (stripe < nstripes) {
       const int row0 = stripe * 32 * R3 + lane * R3;
@@ -179,11 +198,20 @@ __global__ void __launch_bounds__(K3X_WARPS * 32) k3x(const K3XParams P) {
         if ((s & 31) == 0) {
           const int j = s + lane;
           int4 b = make_int4(0, 0, 0, 0);
+          if (early) {
+            stop = min(stop, ld_volatile_s32(stop_p));
+            stop = __reduce_min_sync(0xffffffffu, stop);   // one view per warp: the exit below must be uniform
+            if (s - 31 > stop) break;                      // every column this warp still has lies beyond the stop column
+          }
           if (has_in && j < lt) {                          // my column of the stripe above: re-read until it carries its tag
             unsigned spins = 0;
             for (;;) {
               b = ld_volatile_v4(&row_in[j]);
               if (b.y == tag_in_a && b.w == tag_in_b) break;
+              if (early) {                                 // the producer may have left already: columns beyond the stop column never come
+                stop = min(stop, ld_volatile_s32(stop_p));
+                if (j > stop) { b = make_int4(0, 0, 0, 0); break; }
+              }
               __nanosleep(40);
               if (++spins > K3X_SPIN_LIMIT) { atomicExch(P.error_flag, 1u); break; }
             }
@@ -220,7 +248,10 @@ __global__ void __launch_bounds__(K3X_WARPS * 32) k3x(const K3XParams P) {
             G[k] = __viaddmax_s32(G[k], ge, h + oe);
             if (TRACK) { if (h > colbest) { colbest = h; colk = k; } } else best = max(best, h);
           }
-          if (TRACK && in_range && k3x_better(colbest, j, row0 + colk, best, bj, bi)) { best = colbest; bj = j; bi = row0 + colk; }
+          if (TRACK && in_range && j <= stop && k3x_better(colbest, j, row0 + colk, best, bj, bi)) {
+            best = colbest; bj = j; bi = row0 + colk;
+            if (early && colbest == known) { atomicMin(stop_p, j); stop = j; }      // nothing right of this column can win any more
+          }
           out_h = H[R3 - 1];
           out_v = V;
           if (lane == 31 && has_out && in_range) st_volatile_v4(pcol, out_h, tag_out_a, out_v, tag_out_b);

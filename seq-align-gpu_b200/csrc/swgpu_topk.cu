@@ -122,7 +122,7 @@ int enqueue_topk(swgpu_db* db, swgpu_slot& S, int k) {
     S.d_keys = nullptr; S.d_hit_sidx = nullptr; S.d_coords = nullptr; S.topk_cap = 0;
     const int cap = std::max(k, 128);
     CU(cudaMalloc((void**)&S.d_keys, sizeof(unsigned long long) * 2 * (size_t)cap));
-    CU(cudaMalloc((void**)&S.d_hit_sidx, sizeof(int) * 3 * (size_t)cap));       // unsorted, sorted, best_out
+    CU(cudaMalloc((void**)&S.d_hit_sidx, sizeof(int) * 5 * (size_t)cap));       // unsorted, sorted, best_out, stop columns of the two coordinate passes
     CU(cudaMalloc((void**)&S.d_coords, sizeof(int4) * (size_t)cap));
     S.topk_cap = cap;
   }
@@ -164,12 +164,14 @@ int enqueue_topk(swgpu_db* db, swgpu_slot& S, int k) {
     P.lq = (int)S.lq; P.nstripes_max = ((int)S.lq + 127) / 128; P.table = S.d_table; P.oe = S.oe; P.ge = S.ge;
     P.rows = S.d_x_rows; P.row_stride = db->x_row_stride; P.coords = S.d_coords; P.best_out = best_out;
     P.error_flag = S.d_counters + 7;
+    P.hit_keys = getenv("SWGPU_TOPK_NO_EARLY_STOP") ? nullptr : keys_s;     // A/B knob: the coordinate passes scan their whole rectangles
+    CU(cudaMemsetAsync(S.d_hit_sidx + 3 * cap, 0x7f, sizeof(int) * 2 * (size_t)cap, st));        // stop columns: 0x7f7f7f7f = none yet
     const int grid = std::min(db->sm_count * 2, std::max(1, (k * P.nstripes_max + swk::K3X_WARPS - 1) / swk::K3X_WARPS));
     for (int phase = 0; phase < 2; ++phase) {
       int r = swi::k3x_prepare(db, S, (int)S.lq, st);
       if (r) return r;
       P.epoch = S.x_epoch; P.done = S.d_x_done; P.partial = S.d_x_partial; P.rows = S.d_x_rows;
-      P.phase = phase; P.counter = S.d_counters + 8 + phase;
+      P.phase = phase; P.counter = S.d_counters + 8 + phase; P.stop_col = S.d_hit_sidx + (3 + phase) * cap;
       swk::k3x<true><<<grid, swk::K3X_WARPS * 32, 0, st>>>(P);
     }
     launches += 2;

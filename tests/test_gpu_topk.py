@@ -61,3 +61,45 @@ def test_topk_long_query_multi_stripe_and_zero_scores(oracle, matrices):
         s, c = oracle.end_start(q, codes[off[i]:off[i + 1]], tab, -12, -2)
         assert (h["score"], h["q_start"], h["q_end"], h["t_start"], h["t_end"]) == (s, *c), h
     assert hits[-1]["score"] == 0 and hits[-1]["q_end"] == -1
+
+
+def test_topk_coordinates_with_ties_and_early_stop(oracle, matrices):
+    """The coordinate passes stop at the first column that holds the hit's (known) score.  Ties are the dangerous case: the
+    same maximal score at several columns and in several stripes of query rows -- the FIRST column in the reference's scan
+    order must win, whichever stripe gets there first.  Targets hold two or three exact copies of query
+    segments (equal maxima far apart, in different 128-row stripes), a copy at the very first and at the very last column,
+    and long background; the same hits come out with the early stop switched off (SWGPU_TOPK_NO_EARLY_STOP)."""
+    import os
+    import swgpu
+    from swgpu import synth
+    tab = matrices["BLOSUM62"]
+    g = synth.rng(170)
+    q = synth.make_query(171, 900)                           # 8 stripes of 128 rows in the coordinate kernel
+    bgr = lambda n: synth.residues(g, int(n))
+    parts = [
+        np.concatenate([bgr(700), q[100:300], bgr(1500), q[100:300], bgr(900)]),               # the same segment twice: equal maxima
+        np.concatenate([bgr(300), q[600:850], bgr(50), q[20:270], bgr(2000), q[600:850]]),     # equal-length copies from different stripes
+        np.concatenate([q[400:700], bgr(5000)]),                                               # hit at the first columns of a long target
+        np.concatenate([bgr(6000), q[0:250]]),                                                 # hit at the last columns
+        np.concatenate([q[300:420]] * 5),                                                      # five abutting copies
+        bgr(9000), bgr(40), q.copy(), q[::-1].copy(),
+    ] + [bgr(L) for L in g.integers(1, 1200, size=40)]
+    off = np.zeros(len(parts) + 1, np.int64); np.cumsum([p.size for p in parts], out=off[1:])
+    codes = np.concatenate(parts)
+    db = swgpu.Database(codes, off)
+    results = []
+    for env in (None, "1"):
+        if env: os.environ["SWGPU_TOPK_NO_EARLY_STOP"] = env
+        else: os.environ.pop("SWGPU_TOPK_NO_EARLY_STOP", None)
+        for lq in (900, 130):
+            db.search(q[:lq], tab, -10, -1)
+            hits = db.topk(len(parts))
+            results.append((env, lq, hits, db.last_topk_ms))
+            for h in hits:
+                i = h["entry"]
+                s, c = oracle.end_start(q[:lq], codes[off[i]:off[i + 1]], tab, -10, -1)
+                assert (h["score"], h["q_start"], h["q_end"], h["t_start"], h["t_end"]) == (s, *c), (env, lq, h, c)
+    os.environ.pop("SWGPU_TOPK_NO_EARLY_STOP", None)
+    assert results[0][2] == results[2][2] and results[1][2] == results[3][2]
+    print(f"top-{len(parts)} coordinates, Lq=900: {results[0][3]:.2f} ms with the early stop, {results[2][3]:.2f} ms without")
+    db.close()
