@@ -28,8 +28,10 @@
 
 namespace swk {
 
-constexpr int K3X_WARPS = 8;
-constexpr int K3X_R = 4;                       // rows per lane: 128 rows per stripe
+constexpr int K3X_WARPS = 4;                   // 36 KB of static shared memory per CTA (a lane-private profile of 8 KB per warp)
+constexpr int K3X_CTAS_PER_SM = 4;             // 16 warps per SM
+constexpr int K3X_R = 8;                       // rows per lane
+constexpr int K3X_ROWS = 32 * K3X_R;           // 256 rows per stripe
 constexpr int K3X_SLOTS = 128;                 // targets in flight
 constexpr unsigned K3X_SPIN_LIMIT = 1u << 24;  // polls (with back-off) before the error flag is raised instead of hanging
 
@@ -42,7 +44,7 @@ struct K3XParams {
   const int64_t*  plain_off;
   const int8_t*   query;
   int             lq;
-  int             nstripes_max; // ceil(lq / 128)
+  int             nstripes_max; // ceil(lq / K3X_ROWS)
   const int8_t*   table;
   int             oe, ge;
   int4*           rows;         // [K3X_SLOTS][2][row_stride] (H, tag, V, tag)
@@ -102,31 +104,36 @@ __device__ __forceinline__ bool k3x_better(int s, int j, int i, int bs, int bj, 
 template <bool TRACK>
 __global__ void __launch_bounds__(K3X_WARPS * 32) k3x(const K3XParams P) {
   constexpr int R3 = K3X_R;
+  static_assert(R3 == 8, "profile layout: two int8x4 words per (code, lane)");
   __shared__ int8_t tab[32 * 32];
-  __shared__ unsigned pl_all[K3X_WARPS][32 * 32];          // [code][lane], one int8x4 word (R3 == 4)
-  static_assert(R3 == 4, "profile layout assumes 4 rows per lane");
+  __shared__ uint2 pl_all[K3X_WARPS][32 * 32];             // [code][lane]: int8 x 8 = s(own row k, code), k = 0..7
   for (int i = threadIdx.x; i < 1024; i += blockDim.x) tab[i] = P.table[i];
   __syncthreads();
   // lane id through a volatile shared-memory round trip: ptxas otherwise re-derives it from the special register with an
-  // S2R (tens of cycles) twice per column step, on the critical path of the step's range test and first-lane select;
-  // a volatile load cannot be re-materialised, so the value stays in a register
+  // S2R (tens of cycles) on the critical path of the step's first-lane select; a volatile load cannot be re-materialised
   __shared__ unsigned lane_ids[K3X_WARPS * 32];
   lane_ids[threadIdx.x] = threadIdx.x & 31;
   unsigned lane_v;
   asm volatile("ld.volatile.shared.u32 %0, [%1];" : "=r"(lane_v) : "r"((unsigned)__cvta_generic_to_shared(&lane_ids[threadIdx.x])) : "memory");
   const int warp = threadIdx.x >> 5, lane = (int)lane_v;
-  unsigned* pl = pl_all[warp];
-  const unsigned pl_addr = (unsigned)__cvta_generic_to_shared(pl) + lane * 4;
-  // per-warp rings: the profile byte offset (code * 128) of the last 64 target columns, and the (H, V) of the stripe
-  // above for the current block of 32 columns.  A lane reads its column's code and the first lane its boundary inputs
-  // with one shared load each, instead of passing the code from lane to lane and broadcasting three values by shuffle.
-  __shared__ unsigned ringc_all[K3X_WARPS][64];
+  uint2* pl = pl_all[warp];
+  const unsigned pl_addr = (unsigned)__cvta_generic_to_shared(pl) + lane * 8;
+  // per-warp rings: the profile byte offset (code * 256) of 128 consecutive target columns -- written ONE BLOCK of 32
+  // columns ahead, so a lane can fetch its profile words a step early and the residue load from global memory is a
+  // whole block off the critical path -- and the (H, Vs) of the stripe above for the current block of 32 columns.
+  __shared__ unsigned ringc_all[K3X_WARPS][128];
   __shared__ int2 ringb_all[K3X_WARPS][32];
   unsigned* rc = ringc_all[warp];
   int2* rb = ringb_all[warp];
+  const unsigned rc_addr = (unsigned)__cvta_generic_to_shared(rc);
+  const unsigned rb_addr = (unsigned)__cvta_generic_to_shared(rb);
   const int n_targets = P.work_count ? (int)*P.work_count : P.n_targets;
   const long long n_items = (long long)n_targets * P.nstripes_max;
-  const int oe = P.oe, ge = P.ge;
+  // opaque copies: the penalties stay in registers (as uniform-register operands they were re-loaded from the
+  // constant bank inside every step)
+  int oe, ge;
+  asm volatile("mov.s32 %0, %1;" : "=r"(oe) : "r"(P.oe));
+  asm volatile("mov.s32 %0, %1;" : "=r"(ge) : "r"(P.ge));
 
   for (;;) {
     long long item = 0;
@@ -160,7 +167,7 @@ __global__ void __launch_bounds__(K3X_WARPS * 32) k3x(const K3XParams P) {
       else { lq = c.y + 1; lt = c.w + 1; qp += c.y; tp += c.w; qstep = -1; tstep = -1; }
     }
     if (!TRACK && lt < P.min_len) skip = true;             // this target belongs to k3_intra
-    const int nstripes = skip ? 0 : (lq + 32 * R3 - 1) / (32 * R3);
+    const int nstripes = skip ? 0 : (lq + K3X_ROWS - 1) / K3X_ROWS;
     int best = 0, bj = 0x7fffffff, bi = 0x7fffffff;
     const bool early = TRACK && P.hit_keys != nullptr;
     const int known = early ? (int)(P.hit_keys[t] >> 32) : 0x7fffffff;      // the hit's score
@@ -168,42 +175,59 @@ __global__ void __launch_bounds__(K3X_WARPS * 32) k3x(const K3XParams P) {
     int stop = 0x7fffffff;                                  // this lane's view of stop_col[t] (only ever decreases)
 
     if (stripe < nstripes) {
-      const int row0 = stripe * 32 * R3 + lane * R3;
-      __syncwarp();
-      for (int c = 0; c < 32; ++c) {
-        unsigned word = 0;
+      const int row0 = stripe * K3X_ROWS + lane * R3;
+      {
+        int qc[R3];
 #pragma unroll
-        for (int b = 0; b < 4; ++b) {
-          const int i = row0 + b;
-          const int s = (c == 0 || i >= lq) ? -128 : (int)tab[(qp[(long)i * qstep] & 31) * 32 + c];
-          word |= (unsigned)(s & 0xff) << (8 * b);
+        for (int b = 0; b < R3; ++b) { const int i = row0 + b; qc[b] = (i < lq) ? ((int)qp[(long)i * qstep] & 31) : -1; }
+        __syncwarp();                                        // the previous item of this warp is done with pl and the rings
+        for (int c = 0; c < 32; ++c) {
+          unsigned w[2] = {0u, 0u};
+#pragma unroll
+          for (int b = 0; b < R3; ++b) {
+            const int sc = (c == 0 || qc[b] < 0) ? -128 : (int)tab[qc[b] * 32 + c];
+            w[b >> 2] |= (unsigned)(sc & 0xff) << (8 * (b & 3));
+          }
+          pl[c * 32 + lane] = make_uint2(w[0], w[1]);
         }
-        pl[c * 32 + lane] = word;
       }
-      __syncwarp();
       const bool has_in = stripe > 0, has_out = stripe + 1 < nstripes;
       const int4* row_in = P.rows + ((size_t)slot * 2 + ((stripe + 1) & 1)) * (size_t)P.row_stride;
       int4* row_out = P.rows + ((size_t)slot * 2 + (stripe & 1)) * (size_t)P.row_stride;
       const int tag_in_a = k3x_tag_a(item - 1), tag_in_b = k3x_tag_b(item - 1, P.epoch);
       const int tag_out_a = k3x_tag_a(item), tag_out_b = k3x_tag_b(item, P.epoch);
-      int H[R3], G[R3];
+      // State of the lane's 8 rows.  Gs = G - oe and Vs = V - oe are kept SHIFTED, which leaves one add per operation:
+      //   Hx = max(0, t, G)          = max(Gs + oe, t, 0)     VIADDMNMX.RELU   (independent of V: off the row-to-row chain)
+      //   H  = max(Hx, V)            = max(Vs + oe, Hx)       VIADDMNMX
+      //   V' = max(V + ge, Hx + oe)  : Vs' = max(Vs + ge, Hx) VIADDMNMX        (the chain: one operation per row; oe <= ge)
+      //   G' = max(G + ge, H + oe)   : Gs' = max(Gs + ge, H)  VIADDMNMX
+      // i.e. 4 ALU-pipe operations + 1 IDP per cell.  A boundary value of 0 for Gs / Vs stands for G = V = oe <= 0: as good as
+      // "no gap" (H >= 0 everywhere).  The hand-over rows carry (H, Vs).
+      int H[R3], Gs[R3];
 #pragma unroll
-      for (int k = 0; k < R3; ++k) { H[k] = 0; G[k] = 0; }
+      for (int k = 0; k < R3; ++k) { H[k] = 0; Gs[k] = 0; }
       int diag_in = 0, out_h = 0, out_v = 0;
-      rc[lane] = 0; rc[lane + 32] = 0;                      // columns before the first one: padding code
+      // code ring: columns < 0 and >= lt are the padding code 0 (profile -128); columns [0, 32) now, [32, 64) in `creg`
+      auto code_of = [&](int j) -> unsigned { return (j < lt) ? ((unsigned)tp[(long)j * tstep] & 31u) * 256u : 0u; };
+      rc[lane] = code_of(lane); rc[lane + 32] = 0; rc[lane + 64] = 0; rc[lane + 96] = 0;
+      unsigned creg = code_of(32 + lane);
+      __syncwarp();
       const int nsteps = lt + 31;
-      int4* pcol = row_out - lane;                          // &row_out[s - lane], advanced every step (a loop-carried pointer
-                                                            // is not re-derived from the slot/stripe arithmetic each step)
-      for (int s = 0; s < nsteps; ++s) {
-        if ((s & 31) == 0) {
-          const int j = s + lane;
+      int4* pcol = row_out - lane;                          // &row_out[s - lane], advanced every step
+      // software pipeline: the profile words of step s are fetched during step s - 1, their ring entry during step s - 2
+      unsigned w0, w1, cn;
+      lds64(pl_addr + lds32_ordered(rc_addr + (((unsigned)(0 - lane) & 127u) << 2)), w0, w1);
+      cn = lds32_ordered(rc_addr + (((unsigned)(1 - lane) & 127u) << 2));
+      for (int s0 = 0; s0 < nsteps; s0 += 32) {
+        {
+          const int j = s0 + lane;
           int4 b = make_int4(0, 0, 0, 0);
           if (early) {
             stop = min(stop, ld_volatile_s32(stop_p));
             stop = __reduce_min_sync(0xffffffffu, stop);   // one view per warp: the exit below must be uniform
-            if (s - 31 > stop) break;                      // every column this warp still has lies beyond the stop column
+            if (s0 - 31 > stop) break;                     // every column this warp still has lies beyond the stop column
           }
-          if (has_in && j < lt) {                          // my column of the stripe above: re-read until it carries its tag
+          if (has_in && j < lt) {                          // my column of the stripe above: re-read until it carries its tags
             unsigned spins = 0;
             for (;;) {
               b = ld_volatile_v4(&row_in[j]);
@@ -218,45 +242,67 @@ __global__ void __launch_bounds__(K3X_WARPS * 32) k3x(const K3XParams P) {
           }
           __syncwarp();                                    // the previous block's rb has been read by the first lane
           rb[lane] = make_int2(b.x, b.z);
-          rc[j & 63] = (j < lt) ? ((unsigned)tp[(long)j * tstep] & 31u) * 128u : 0u;
+          rc[(s0 + 32 + lane) & 127] = creg;               // the NEXT block's codes (this block's went in a block ago)
+          creg = code_of(s0 + 64 + lane);                  // in flight during the 32 steps below
           __syncwarp();
         }
-        // Column j = s - lane.  No range test around the cell update: before its first column a lane sees zeros from the
-        // lane below and the padding code (H stays 0); past its last column it computes on the padding code, which can
-        // only produce values below those already seen (the profile of padding is -128, gaps cost).  Only the hand-over
-        // store and the tracked maximum are guarded.
-        const int j = s - lane;
-        int h_up = __shfl_up_sync(0xffffffffu, out_h, 1);
-        int v_in = __shfl_up_sync(0xffffffffu, out_v, 1);
-        const int2 b0 = rb[s & 31];
-        if (lane == 0) { h_up = b0.x; v_in = b0.y; }
-        const unsigned w0 = lds32_ordered(pl_addr + rc[j & 63]);
-        const bool in_range = (unsigned)j < (unsigned)lt;
-        {
+        unsigned bx, by;
+        lds64_ordered(rb_addr, bx, by);                     // the first lane's boundary pair of this block's first column
+        const int send = min(32, nsteps - s0);
+        for (int u = 0; u < send; ++u) {
+          const int s = s0 + u;
+          const int j = s - lane;                           // this lane's column
+          int h_up = __shfl_up_sync(0xffffffffu, out_h, 1);
+          int v_in = __shfl_up_sync(0xffffffffu, out_v, 1);
+          if (lane == 0) { h_up = (int)bx; v_in = (int)by; }
+          // fetches for the next steps (nothing below depends on them)
+          unsigned wn0, wn1;
+          lds64(pl_addr + cn, wn0, wn1);
+          const unsigned cnn = lds32_ordered(rc_addr + (((unsigned)(j + 2) & 127u) << 2));
+          lds64_ordered(rb_addr + (((unsigned)(s + 1) & 31u) << 3), bx, by);   // (stale in a block's last step: re-read above)
+          // No range test around the cell update: before its first column a lane sees zeros from the lane below and the
+          // padding code (H stays 0); past its last column it computes on the padding code, which can only produce values
+          // below those already seen.  Only the hand-over store and the tracked maximum are guarded.
           int d = diag_in;
           diag_in = h_up;
-          int V = v_in;
-          int colbest = 0, colk = 0;
+          int Vs = v_in;
 #pragma unroll
           for (int k = 0; k < R3; ++k) {
-            const int tt = (int)add_byte(w0, 1u << (8 * k), (unsigned)d);
-            const int hx = __vimax3_s32_relu(tt, G[k], 0);   // max(0, t, G): independent of V
-            const int h = max(hx, V);
-            V = __viaddmax_s32(V, ge, hx + oe);              // the row-to-row chain: one op
+            const int tt = (int)add_byte(k < 4 ? w0 : w1, 1u << (8 * (k & 3)), (unsigned)d);
+            const int hx = __viaddmax_s32_relu(Gs[k], oe, tt);
+            const int h = __viaddmax_s32(Vs, oe, hx);
+            Vs = __viaddmax_s32(Vs, ge, hx);                 // the row-to-row chain: one operation
+            Gs[k] = __viaddmax_s32(Gs[k], ge, h);
             d = H[k];
             H[k] = h;
-            G[k] = __viaddmax_s32(G[k], ge, h + oe);
-            if (TRACK) { if (h > colbest) { colbest = h; colk = k; } } else best = max(best, h);
-          }
-          if (TRACK && in_range && j <= stop && k3x_better(colbest, j, row0 + colk, best, bj, bi)) {
-            best = colbest; bj = j; bi = row0 + colk;
-            if (early && colbest == known) { atomicMin(stop_p, j); stop = j; }      // nothing right of this column can win any more
           }
           out_h = H[R3 - 1];
-          out_v = V;
+          out_v = Vs;
+          const bool in_range = (unsigned)j < (unsigned)lt;
+          if (TRACK) {
+            int cb = __vimax3_s32(H[0], H[1], H[2]);
+            cb = __vimax3_s32(cb, H[3], H[4]);
+            cb = __vimax3_s32(cb, H[5], H[6]);
+            cb = max(cb, H[7]);
+            // a lane's columns come in increasing order: a later column wins only with a strictly higher score; within the
+            // column the smallest row wins
+            if (cb > best && in_range && j <= stop) {
+              int kk = R3 - 1;
+#pragma unroll
+              for (int k = R3 - 2; k >= 0; --k) if (H[k] == cb) kk = k;
+              best = cb; bj = j; bi = row0 + kk;
+              if (early && cb == known) { atomicMin(stop_p, j); stop = j; }   // nothing right of this column can win any more
+            }
+          } else {
+            best = __vimax3_s32(best, H[0], H[1]);
+            best = __vimax3_s32(best, H[2], H[3]);
+            best = __vimax3_s32(best, H[4], H[5]);
+            best = __vimax3_s32(best, H[6], H[7]);
+          }
           if (lane == 31 && has_out && in_range) st_volatile_v4(pcol, out_h, tag_out_a, out_v, tag_out_b);
+          ++pcol;
+          w0 = wn0; w1 = wn1; cn = cnn;
         }
-        ++pcol;
       }
       // this stripe's candidate
       if (TRACK) {

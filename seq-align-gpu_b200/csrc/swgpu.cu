@@ -63,7 +63,7 @@ int slot_prepare(swgpu_db* db, swgpu_slot& S) {
 // k3x slot state for a query of lq rows: the per-stripe partial results grow with the query; the completion
 // counters are zeroed on `stream` and the tag epoch advances before every k3x launch.
 int k3x_prepare(swgpu_db* db, swgpu_slot& S, int lq, cudaStream_t stream) {
-  const int ns = std::max(1, (lq + 127) / 128);
+  const int ns = std::max(1, (lq + swk::K3X_ROWS - 1) / swk::K3X_ROWS);
   if (!S.d_x_rows) {                                       // top-k coordinates on a database without long targets
     CU(cudaMalloc((void**)&S.d_x_rows, sizeof(int4) * (size_t)swk::K3X_SLOTS * 2 * (size_t)db->x_row_stride));
     CU(cudaMemsetAsync(S.d_x_rows, 0, sizeof(int4) * (size_t)swk::K3X_SLOTS * 2 * (size_t)db->x_row_stride, stream));
@@ -389,12 +389,12 @@ int launch_32bit(swgpu_db* db, swgpu_slot& S, cudaStream_t stream, const int* li
     if (r) return r;
     swk::K3XParams W; memset(&W, 0, sizeof(W));
     W.sidx_list = list; W.work_count = list_count; W.n_targets = n_all; W.counter = q_k3x;
-    W.plain = db->d_plain; W.plain_off = db->d_plain_off; W.query = S.d_query; W.lq = lq; W.nstripes_max = (lq + 127) / 128;
+    W.plain = db->d_plain; W.plain_off = db->d_plain_off; W.query = S.d_query; W.lq = lq; W.nstripes_max = (lq + swk::K3X_ROWS - 1) / swk::K3X_ROWS;
     W.table = S.d_table; W.oe = oe; W.ge = ge; W.rows = S.d_x_rows; W.row_stride = db->x_row_stride;
     W.epoch = S.x_epoch; W.done = S.d_x_done; W.partial = S.d_x_partial;
     W.order = db->d_order; W.scores_file = S.d_scores; W.error_flag = S.d_counters + 6; W.min_len = kWaveMinLen;
     if ((double)db->n * W.nstripes_max >= 4.0e9) return fail(SWGPU_EINVAL, "query too long for this database size (32-bit path)");
-    swk::k3x<false><<<db->sm_count * 2, swk::K3X_WARPS * 32, 0, stream>>>(W);
+    swk::k3x<false><<<db->sm_count * swk::K3X_CTAS_PER_SM, swk::K3X_WARPS * 32, 0, stream>>>(W);
     CU(cudaGetLastError());
     ++*launches;
   }

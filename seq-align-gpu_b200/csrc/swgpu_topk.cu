@@ -161,12 +161,12 @@ int enqueue_topk(swgpu_db* db, swgpu_slot& S, int k) {
     // coordinates of the k hits against the query of this slot's search (hits with score 0 come out as -1)
     swk::K3XParams P; memset(&P, 0, sizeof(P));
     P.sidx_list = sidx_s; P.n_targets = k; P.plain = db->d_plain; P.plain_off = db->d_plain_off; P.query = S.d_query;
-    P.lq = (int)S.lq; P.nstripes_max = ((int)S.lq + 127) / 128; P.table = S.d_table; P.oe = S.oe; P.ge = S.ge;
+    P.lq = (int)S.lq; P.nstripes_max = ((int)S.lq + swk::K3X_ROWS - 1) / swk::K3X_ROWS; P.table = S.d_table; P.oe = S.oe; P.ge = S.ge;
     P.rows = S.d_x_rows; P.row_stride = db->x_row_stride; P.coords = S.d_coords; P.best_out = best_out;
     P.error_flag = S.d_counters + 7;
     P.hit_keys = getenv("SWGPU_TOPK_NO_EARLY_STOP") ? nullptr : keys_s;     // A/B knob: the coordinate passes scan their whole rectangles
     CU(cudaMemsetAsync(S.d_hit_sidx + 3 * cap, 0x7f, sizeof(int) * 2 * (size_t)cap, st));        // stop columns: 0x7f7f7f7f = none yet
-    const int grid = std::min(db->sm_count * 2, std::max(1, (k * P.nstripes_max + swk::K3X_WARPS - 1) / swk::K3X_WARPS));
+    const int grid = std::min(db->sm_count * swk::K3X_CTAS_PER_SM, std::max(1, (k * P.nstripes_max + swk::K3X_WARPS - 1) / swk::K3X_WARPS));
     for (int phase = 0; phase < 2; ++phase) {
       int r = swi::k3x_prepare(db, S, (int)S.lq, st);
       if (r) return r;
