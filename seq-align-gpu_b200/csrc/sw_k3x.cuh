@@ -32,6 +32,7 @@ constexpr int K3X_WARPS = 4;                   // 36 KB of static shared memory 
 constexpr int K3X_CTAS_PER_SM = 4;             // 16 warps per SM
 constexpr int K3X_R = 8;                       // rows per lane
 constexpr int K3X_ROWS = 32 * K3X_R;           // 256 rows per stripe
+constexpr int K3X_PREFETCH_AT = 24;            // step of a 32-step block at which the next block's input columns are requested
 constexpr int K3X_SLOTS = 128;                 // targets in flight
 constexpr unsigned K3X_SPIN_LIMIT = 1u << 24;  // polls (with back-off) before the error flag is raised instead of hanging
 
@@ -67,7 +68,12 @@ struct K3XParams {
   const unsigned long long* hit_keys;   // TRACK: sorted keys of the hits (score << 32 | ~entry); nullptr = no early stop
   int*            stop_col;     // TRACK: [n_targets] for this phase
   unsigned*       error_flag;
+  unsigned*       sm_slots;     // [256], zero at launch: CTAs that have started on each SM (a CTA's level = its arrival number there)
+  int             level_ctas;   // CTAs per level = number of SMs
   int             min_len;      // !TRACK: targets shorter than this are left to k3_intra
+#ifdef K3X_TRACE
+  int4*           trace;        // profiling build only: per item (begin, end, time spent waiting for input; 0.1 us units, SM id)
+#endif
 };
 
 __device__ __forceinline__ int4 ld_volatile_v4(const int4* p) {
@@ -107,8 +113,25 @@ __global__ void __launch_bounds__(K3X_WARPS * 32) k3x(const K3XParams P) {
   static_assert(R3 == 8, "profile layout: two int8x4 words per (code, lane)");
   __shared__ int8_t tab[32 * 32];
   __shared__ uint2 pl_all[K3X_WARPS][32 * 32];             // [code][lane]: int8 x 8 = s(own row k, code), k = 0..7
+  // Placement.  The grid is the whole machine (K3X_CTAS_PER_SM CTAs on every SM) but a job may have far fewer items than
+  // warps (ONE 35 213 x 35 213 pair is 138 stripes), and the queue hands consecutive items to whichever warps ask first:
+  // left alone, 138 items landed on 31 SMs, up to four per scheduler, and the whole chain ran at the pace of the most
+  // crowded scheduler.  So CTAs are numbered per SM in arrival order (their level); level L only takes part when the
+  // levels below cannot give every item a warp of its own, and waits a moment so that the lower levels ask first.
+  // Items still come from the one queue, in order, whoever asks: the no-deadlock argument above is untouched.
+  __shared__ int cta_level;
+  if (threadIdx.x == 0) {
+    unsigned smid; asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    cta_level = (int)atomicAdd(P.sm_slots + (smid & 255u), 1u);
+  }
   for (int i = threadIdx.x; i < 1024; i += blockDim.x) tab[i] = P.table[i];
   __syncthreads();
+  {
+    const long long items = (long long)(P.work_count ? (int)*P.work_count : P.n_targets) * P.nstripes_max;
+    const long long per_level = (long long)P.level_ctas * K3X_WARPS;
+    if (items <= (long long)cta_level * per_level) return;
+    if (cta_level > 0 && items < (long long)gridDim.x * K3X_WARPS) __nanosleep(3000u * (unsigned)min(cta_level, 8));
+  }
   // lane id through a volatile shared-memory round trip: ptxas otherwise re-derives it from the special register with an
   // S2R (tens of cycles) on the critical path of the step's first-lane select; a volatile load cannot be re-materialised
   __shared__ unsigned lane_ids[K3X_WARPS * 32];
@@ -135,6 +158,9 @@ __global__ void __launch_bounds__(K3X_WARPS * 32) k3x(const K3XParams P) {
   asm volatile("mov.s32 %0, %1;" : "=r"(oe) : "r"(P.oe));
   asm volatile("mov.s32 %0, %1;" : "=r"(ge) : "r"(P.ge));
 
+#ifdef K3X_TRACE
+  unsigned long long tr_entry; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tr_entry));
+#endif
   for (;;) {
     long long item = 0;
     if (lane == 0) item = (long long)atomicAdd(P.counter, 1u);
@@ -214,8 +240,12 @@ __global__ void __launch_bounds__(K3X_WARPS * 32) k3x(const K3XParams P) {
       __syncwarp();
       const int nsteps = lt + 31;
       int4* pcol = row_out - lane;                          // &row_out[s - lane], advanced every step
+#ifdef K3X_TRACE
+      unsigned long long tr_begin, tr_wait = 0, tr_m0 = 0, tr_m1 = 0, tr_m2 = 0; unsigned tr_miss = 0; int tr_b[16]; for (int q = 0; q < 16; ++q) tr_b[q] = 0; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tr_begin));
+#endif
       // software pipeline: the profile words of step s are fetched during step s - 1, their ring entry during step s - 2
       unsigned w0, w1, cn;
+      int4 bpre = make_int4(0, 0, 0, 0);                    // tag 0 is nobody's: the first block polls
       lds64(pl_addr + lds32_ordered(rc_addr + (((unsigned)(0 - lane) & 127u) << 2)), w0, w1);
       cn = lds32_ordered(rc_addr + (((unsigned)(1 - lane) & 127u) << 2));
       for (int s0 = 0; s0 < nsteps; s0 += 32) {
@@ -227,20 +257,57 @@ __global__ void __launch_bounds__(K3X_WARPS * 32) k3x(const K3XParams P) {
             stop = __reduce_min_sync(0xffffffffu, stop);   // one view per warp: the exit below must be uniform
             if (s0 - 31 > stop) break;                     // every column this warp still has lies beyond the stop column
           }
-          if (has_in && j < lt) {                          // my column of the stripe above: re-read until it carries its tags
+#ifdef K3X_TRACE
+          unsigned long long tr_w0; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tr_w0));
+#endif
+          const bool want = has_in && j < lt;                // my column of the stripe above
+          if (want) b = bpre;                                // requested during the previous block (nothing before the first one)
+          bool ok = !want || (b.y == tag_in_a && b.w == tag_in_b);
+          if (!__all_sync(0xffffffffu, ok)) {
+            // Not there yet.  Both waits below are loops the WHOLE warp leaves together: with per-lane exits the lanes came out
+            // of the wait on different paths and ran the block that followed un-converged, every shuffle on its slow path
+            // (measured: 12.5 us for a stripe's first 32 steps instead of 2.5, i.e. 15 us per stripe for a long pair to get going).
+            // First the block's LAST column, one 16-byte record read by all lanes, with a growing pause: while a long pair starts
+            // up every stripe below the front waits for its first block, on the same few lines of the two rows.  Then every lane
+            // re-reads its own column until it carries its tags (normally the first read; the order in which the producer's
+            // stores become visible is not relied upon).
+            {
+              const int jl = min(s0 + 31, lt - 1);
+              unsigned spins = 0;
+              for (;;) {
+                const int4 l = ld_volatile_v4(&row_in[jl]);
+                bool seen = (l.y == tag_in_a && l.w == tag_in_b);
+                if (early) { stop = min(stop, ld_volatile_s32(stop_p)); seen |= jl > stop; }   // may never come: decided per lane below
+                if (++spins > K3X_SPIN_LIMIT) { atomicExch(P.error_flag, 1u); seen = true; }
+                if (__any_sync(0xffffffffu, seen)) break;
+                __nanosleep(64u << min(spins, 4u));
+              }
+            }
+#ifdef K3X_TRACE
+            if (s0 > 0) ++tr_miss;
+#endif
             unsigned spins = 0;
             for (;;) {
-              b = ld_volatile_v4(&row_in[j]);
-              if (b.y == tag_in_a && b.w == tag_in_b) break;
-              if (early) {                                 // the producer may have left already: columns beyond the stop column never come
-                stop = min(stop, ld_volatile_s32(stop_p));
-                if (j > stop) { b = make_int4(0, 0, 0, 0); break; }
+              if (!ok) {
+                b = ld_volatile_v4(&row_in[j]);
+                ok = (b.y == tag_in_a && b.w == tag_in_b);
+                if (!ok && early) {                        // the producer may have left already: columns beyond the stop column never come
+                  stop = min(stop, ld_volatile_s32(stop_p));
+                  if (j > stop) { b = make_int4(0, 0, 0, 0); ok = true; }
+                }
               }
+              if (__all_sync(0xffffffffu, ok)) break;
               __nanosleep(40);
               if (++spins > K3X_SPIN_LIMIT) { atomicExch(P.error_flag, 1u); break; }
             }
           }
           __syncwarp();                                    // the previous block's rb has been read by the first lane
+#ifdef K3X_TRACE
+          { unsigned long long tr_w1; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tr_w1)); tr_wait += tr_w1 - tr_w0;
+            if (s0 == 0) tr_m0 = tr_w1; if (s0 == 64) tr_m1 = tr_w1; if (s0 == 1024) tr_m2 = tr_w1;
+#pragma unroll
+            for (int q = 0; q < 8; ++q) if (s0 == 32 * q) { tr_b[2 * q] = (int)((tr_w0 - tr_begin) / 10); tr_b[2 * q + 1] = (int)((tr_w1 - tr_begin) / 10); } }
+#endif
           rb[lane] = make_int2(b.x, b.z);
           rc[(s0 + 32 + lane) & 127] = creg;               // the NEXT block's codes (this block's went in a block ago)
           creg = code_of(s0 + 64 + lane);                  // in flight during the 32 steps below
@@ -249,7 +316,7 @@ __global__ void __launch_bounds__(K3X_WARPS * 32) k3x(const K3XParams P) {
         unsigned bx, by;
         lds64_ordered(rb_addr, bx, by);                     // the first lane's boundary pair of this block's first column
         const int send = min(32, nsteps - s0);
-        for (int u = 0; u < send; ++u) {
+        auto step = [&](const int u) {
           const int s = s0 + u;
           const int j = s - lane;                           // this lane's column
           int h_up = __shfl_up_sync(0xffffffffu, out_h, 1);
@@ -302,7 +369,18 @@ __global__ void __launch_bounds__(K3X_WARPS * 32) k3x(const K3XParams P) {
           if (lane == 31 && has_out && in_range) st_volatile_v4(pcol, out_h, tag_out_a, out_v, tag_out_b);
           ++pcol;
           w0 = wn0; w1 = wn1; cn = cnn;
+        };
+        const int upre = min(send, K3X_PREFETCH_AT);
+        for (int u = 0; u < upre; ++u) step(u);
+        // The next block's input columns are requested a few steps before they are needed: a consumer that is not right on
+        // its producer's heels finds them complete and pays no load latency at the block boundary (a stripe that failed the
+        // check once has fallen behind by the re-poll and succeeds from then on); an incomplete record is re-polled above.
+        if (has_in) {
+          const int jn = s0 + 32 + lane;
+          bpre = make_int4(0, 0, 0, 0);
+          if (jn < lt) bpre = ld_volatile_v4(&row_in[jn]);
         }
+        for (int u = upre; u < send; ++u) step(u);
       }
       // this stripe's candidate
       if (TRACK) {
@@ -318,6 +396,16 @@ __global__ void __launch_bounds__(K3X_WARPS * 32) k3x(const K3XParams P) {
         for (int o = 16; o > 0; o >>= 1) best = max(best, __shfl_xor_sync(0xffffffffu, best, o));
       }
       if (lane == 0) P.partial[(size_t)slot * P.nstripes_max + stripe] = make_int4(best, bj, bi, 0);
+#ifdef K3X_TRACE
+      if (lane == 0 && P.trace) {
+        unsigned long long tr_end; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tr_end));
+        unsigned smid; asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+        P.trace[6 * item] = make_int4((int)((tr_begin - tr_entry) / 100), (int)((tr_end - tr_entry) / 100), (int)(tr_wait / 100), (int)smid);
+        P.trace[6 * item + 1] = make_int4((int)((tr_m0 - tr_entry) / 100), (int)((tr_m1 - tr_entry) / 100), (int)((tr_m2 - tr_entry) / 100), (int)tr_miss);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) P.trace[6 * item + 2 + q] = make_int4(tr_b[4 * q], tr_b[4 * q + 1], tr_b[4 * q + 2], tr_b[4 * q + 3]);
+      }
+#endif
     }
 
     // completion: the last item of this target reduces the per-stripe candidates and writes the result
@@ -360,6 +448,20 @@ __global__ void __launch_bounds__(K3X_WARPS * 32) k3x(const K3XParams P) {
       }
     }
   }
+}
+
+// CTAs of k3x<TRACK> that fit an SM of `device` (the current device), at most K3X_CTAS_PER_SM: the launch grid is
+// sm_count times this, so that every CTA of the grid is resident at once when the GPU is otherwise idle.
+template <bool TRACK>
+inline int k3x_ctas_per_sm(int device) {
+  static int cached[64] = {0};
+  if (device >= 0 && device < 64 && cached[device]) return cached[device];
+  cudaFuncSetAttribute(k3x<TRACK>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+  int n = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k3x<TRACK>, K3X_WARPS * 32, 0) != cudaSuccess || n < 1) n = 1;
+  if (n > K3X_CTAS_PER_SM) n = K3X_CTAS_PER_SM;
+  if (device >= 0 && device < 64) cached[device] = n;
+  return n;
 }
 
 }  // namespace swk

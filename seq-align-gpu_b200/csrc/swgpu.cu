@@ -53,7 +53,7 @@ int slot_prepare(swgpu_db* db, swgpu_slot& S) {
   if (db->max_len >= kWaveMinLen) {
     if ((r = dalloc(db, &S.d_x_rows, (size_t)swk::K3X_SLOTS * 2 * (size_t)db->x_row_stride))) return r;
     CU(cudaMemset(S.d_x_rows, 0, sizeof(int4) * (size_t)swk::K3X_SLOTS * 2 * (size_t)db->x_row_stride));
-    if ((r = dalloc(db, &S.d_x_done, (size_t)swk::K3X_SLOTS))) return r;
+    if ((r = dalloc(db, &S.d_x_done, (size_t)swk::K3X_SLOTS + 256))) return r;      // + the per-SM CTA counters of k3x
   }
   CU(cudaMallocHost((void**)&S.h_ctr, 16 * sizeof(unsigned)));
   S.ready = true;
@@ -67,14 +67,14 @@ int k3x_prepare(swgpu_db* db, swgpu_slot& S, int lq, cudaStream_t stream) {
   if (!S.d_x_rows) {                                       // top-k coordinates on a database without long targets
     CU(cudaMalloc((void**)&S.d_x_rows, sizeof(int4) * (size_t)swk::K3X_SLOTS * 2 * (size_t)db->x_row_stride));
     CU(cudaMemsetAsync(S.d_x_rows, 0, sizeof(int4) * (size_t)swk::K3X_SLOTS * 2 * (size_t)db->x_row_stride, stream));
-    CU(cudaMalloc((void**)&S.d_x_done, sizeof(unsigned) * swk::K3X_SLOTS));
+    CU(cudaMalloc((void**)&S.d_x_done, sizeof(unsigned) * (swk::K3X_SLOTS + 256)));
   }
   if (ns > S.x_stripes_cap) {
     cudaFree(S.d_x_partial); S.d_x_partial = nullptr;
     S.x_stripes_cap = ns + ns / 2;
     CU(cudaMalloc((void**)&S.d_x_partial, sizeof(int4) * (size_t)swk::K3X_SLOTS * S.x_stripes_cap));
   }
-  CU(cudaMemsetAsync(S.d_x_done, 0, sizeof(unsigned) * swk::K3X_SLOTS, stream));
+  CU(cudaMemsetAsync(S.d_x_done, 0, sizeof(unsigned) * (swk::K3X_SLOTS + 256), stream));
   ++S.x_epoch;
   return SWGPU_OK;
 }
@@ -391,12 +391,31 @@ int launch_32bit(swgpu_db* db, swgpu_slot& S, cudaStream_t stream, const int* li
     W.sidx_list = list; W.work_count = list_count; W.n_targets = n_all; W.counter = q_k3x;
     W.plain = db->d_plain; W.plain_off = db->d_plain_off; W.query = S.d_query; W.lq = lq; W.nstripes_max = (lq + swk::K3X_ROWS - 1) / swk::K3X_ROWS;
     W.table = S.d_table; W.oe = oe; W.ge = ge; W.rows = S.d_x_rows; W.row_stride = db->x_row_stride;
-    W.epoch = S.x_epoch; W.done = S.d_x_done; W.partial = S.d_x_partial;
+    W.epoch = S.x_epoch; W.done = S.d_x_done; W.partial = S.d_x_partial; W.sm_slots = S.d_x_done + swk::K3X_SLOTS; W.level_ctas = db->sm_count;
     W.order = db->d_order; W.scores_file = S.d_scores; W.error_flag = S.d_counters + 6; W.min_len = kWaveMinLen;
     if ((double)db->n * W.nstripes_max >= 4.0e9) return fail(SWGPU_EINVAL, "query too long for this database size (32-bit path)");
-    swk::k3x<false><<<db->sm_count * swk::K3X_CTAS_PER_SM, swk::K3X_WARPS * 32, 0, stream>>>(W);
+#ifdef K3X_TRACE
+    int4* d_trace = nullptr;
+    const size_t n_trace = 6 * (size_t)(n_all > 0 ? n_all : 8) * W.nstripes_max;     // device-side list: room for 8 targets
+    if (getenv("SWGPU_K3X_TRACE")) { CU(cudaMalloc((void**)&d_trace, sizeof(int4) * n_trace)); CU(cudaMemset(d_trace, 0, sizeof(int4) * n_trace)); }
+    W.trace = d_trace;
+#endif
+    swk::k3x<false><<<db->sm_count * swk::k3x_ctas_per_sm<false>(db->device), swk::K3X_WARPS * 32, 0, stream>>>(W);
     CU(cudaGetLastError());
     ++*launches;
+#ifdef K3X_TRACE
+    if (d_trace) {                                            // profiling build: (begin, end, waiting; 0.1 us) and SM of every item, appended as text
+      CU(cudaStreamSynchronize(stream));
+      std::vector<int4> h(n_trace);
+      CU(cudaMemcpy(h.data(), d_trace, sizeof(int4) * n_trace, cudaMemcpyDeviceToHost));
+      cudaFree(d_trace);
+      if (FILE* f = fopen(getenv("SWGPU_K3X_TRACE"), "a")) {
+        fprintf(f, "# lq %d stripes %d items %zu\n", lq, W.nstripes_max, n_trace);
+        for (size_t i = 0; i + 5 < n_trace; i += 6) { fprintf(f, "%zu", i / 6); for (int q = 0; q < 6; ++q) fprintf(f, " %d %d %d %d", h[i + q].x, h[i + q].y, h[i + q].z, h[i + q].w); fprintf(f, "\n"); }
+        fclose(f);
+      }
+    }
+#endif
   }
   return SWGPU_OK;
 }

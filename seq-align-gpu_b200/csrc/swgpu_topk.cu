@@ -166,11 +166,12 @@ int enqueue_topk(swgpu_db* db, swgpu_slot& S, int k) {
     P.error_flag = S.d_counters + 7;
     P.hit_keys = getenv("SWGPU_TOPK_NO_EARLY_STOP") ? nullptr : keys_s;     // A/B knob: the coordinate passes scan their whole rectangles
     CU(cudaMemsetAsync(S.d_hit_sidx + 3 * cap, 0x7f, sizeof(int) * 2 * (size_t)cap, st));        // stop columns: 0x7f7f7f7f = none yet
-    const int grid = std::min(db->sm_count * swk::K3X_CTAS_PER_SM, std::max(1, (k * P.nstripes_max + swk::K3X_WARPS - 1) / swk::K3X_WARPS));
+    const int grid = db->sm_count * swk::k3x_ctas_per_sm<true>(db->device);    // the whole machine: CTAs beyond the levels the items need leave at once (sw_k3x.cuh)
     for (int phase = 0; phase < 2; ++phase) {
       int r = swi::k3x_prepare(db, S, (int)S.lq, st);
       if (r) return r;
       P.epoch = S.x_epoch; P.done = S.d_x_done; P.partial = S.d_x_partial; P.rows = S.d_x_rows;
+      P.sm_slots = S.d_x_done + swk::K3X_SLOTS; P.level_ctas = db->sm_count;
       P.phase = phase; P.counter = S.d_counters + 8 + phase; P.stop_col = S.d_hit_sidx + (3 + phase) * cap;
       swk::k3x<true><<<grid, swk::K3X_WARPS * 32, 0, st>>>(P);
     }
