@@ -2,11 +2,11 @@
 // warps (from any CTA) on the same target at the same time.
 //
 // Same recurrence as k3_intra (sw_kernels.cuh; reference src/alignment.c:117-176).  A single (query, target)
-// pair is a chain of Lt dependent column steps per stripe of query rows; a 35 213 x 35 213 pair has 276 stripes
-// of 128 rows.  Here every stripe is a work item of its own:
-//   * items = (target, stripe), enumerated target-major / stripe-ascending and pulled from one atomic queue, so
-//     the producer of an item's input row always has a smaller item index: it is already running (or done) when
-//     the consumer starts -- no deadlock whatever the number of resident warps;
+// pair is a chain of Lt dependent column steps per stripe of query rows; a 35 213 x 35 213 pair has 138 stripes
+// of 256 rows.  Here every stripe is a work item of its own:
+//   * items = (target, stripe), enumerated stripe-ascending per target (stripe-major inside a generation of K3X_SLOTS
+//     targets) and pulled from one atomic queue, so the producer of an item's input row always has a smaller item
+//     index: it is already running (or done) when the consumer starts -- no deadlock whatever the number of resident warps;
 //   * stripe s-1 -> stripe s: the bottom row goes through a full-length row in global memory (two rows per target
 //     slot, ping-pong by stripe parity).  Every column is ONE aligned 16-byte store (H, tag, V, tag) by the
 //     producer's lane 31 and one 16-byte volatile load by the consumer, which simply re-reads until both tags are
@@ -29,7 +29,10 @@
 namespace swk {
 
 constexpr int K3X_WARPS = 4;                   // 36 KB of static shared memory per CTA (a lane-private profile of 8 KB per warp)
-constexpr int K3X_CTAS_PER_SM = 4;             // 16 warps per SM
+#ifndef K3X_CTAS
+#define K3X_CTAS 4
+#endif
+constexpr int K3X_CTAS_PER_SM = K3X_CTAS;      // 16 warps per SM (at most: the launch asks the occupancy calculator)
 constexpr int K3X_R = 8;                       // rows per lane
 constexpr int K3X_ROWS = 32 * K3X_R;           // 256 rows per stripe
 constexpr int K3X_PREFETCH_AT = 24;            // step of a 32-step block at which the next block's input columns are requested
@@ -166,8 +169,17 @@ __global__ void __launch_bounds__(K3X_WARPS * 32) k3x(const K3XParams P) {
     if (lane == 0) item = (long long)atomicAdd(P.counter, 1u);
     item = __shfl_sync(0xffffffffu, item, 0);
     if (item >= n_items) break;
-    const int t = (int)(item / P.nstripes_max), stripe = (int)(item - (long long)t * P.nstripes_max);
-    const int slot = t % K3X_SLOTS, gen = t / K3X_SLOTS;
+    // item -> (target, stripe): targets in generations of K3X_SLOTS, and inside a generation STRIPE-major (stripe 0 of all its
+    // targets, then stripe 1, ...): the warps of the machine then work on the leading stripes of many targets, not on all
+    // 138 stripes of a few, most of which would only wait for their turn.  The producer of (t, stripe) is (t, stripe - 1),
+    // n_in_gen items earlier: still a smaller item number.
+    const long long per_gen = (long long)K3X_SLOTS * P.nstripes_max;
+    const int gen = (int)(item / per_gen);
+    const int in_gen = (int)(item - (long long)gen * per_gen);
+    const int n_in_gen = min(K3X_SLOTS, n_targets - gen * K3X_SLOTS);
+    const int stripe = in_gen / n_in_gen;
+    const int slot = in_gen - stripe * n_in_gen;
+    const int t = gen * K3X_SLOTS + slot;
     // the slot's previous user (target t - K3X_SLOTS) must be completely done before its rows are touched
     if (gen > 0) {
       if (lane == 0) {
@@ -220,7 +232,7 @@ __global__ void __launch_bounds__(K3X_WARPS * 32) k3x(const K3XParams P) {
       const bool has_in = stripe > 0, has_out = stripe + 1 < nstripes;
       const int4* row_in = P.rows + ((size_t)slot * 2 + ((stripe + 1) & 1)) * (size_t)P.row_stride;
       int4* row_out = P.rows + ((size_t)slot * 2 + (stripe & 1)) * (size_t)P.row_stride;
-      const int tag_in_a = k3x_tag_a(item - 1), tag_in_b = k3x_tag_b(item - 1, P.epoch);
+      const int tag_in_a = k3x_tag_a(item - n_in_gen), tag_in_b = k3x_tag_b(item - n_in_gen, P.epoch);
       const int tag_out_a = k3x_tag_a(item), tag_out_b = k3x_tag_b(item, P.epoch);
       // State of the lane's 8 rows.  Gs = G - oe and Vs = V - oe are kept SHIFTED, which leaves one add per operation:
       //   Hx = max(0, t, G)          = max(Gs + oe, t, 0)     VIADDMNMX.RELU   (independent of V: off the row-to-row chain)

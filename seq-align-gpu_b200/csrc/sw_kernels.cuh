@@ -12,7 +12,7 @@
 // K1S (sw_k1s.cuh)  inter-sequence, packed 2 x u16, the dominant kernel
 // K3  k3_intra<R3>  32-bit, one warp per target: rescoring of targets whose 16-bit result
 //                   saturated -- the reference's 16-bit / 32-bit split, README.md:11
-// K3X (sw_k3x.cuh)  32-bit wavefront, one warp per 128-row stripe: long targets, top-k coordinates
+// K3X (sw_k3x.cuh)  32-bit wavefront, one warp per 256-row stripe: long targets, top-k coordinates
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>

@@ -22,7 +22,7 @@ using swi::fail;
 
 constexpr int kDefaultStreamCols = 2304;
 constexpr int kDefaultTaper = 3;             // stream lengths halve at the last 1/16, 1/64 and 1/256 of the database (scripts/ab_taper.py)
-constexpr int kWaveMinLen = 4096;          // 32-bit path: targets at least this long take k3x (one warp per 128-row stripe)
+constexpr int kWaveMinLen = 4096;          // 32-bit path: targets at least this long take k3x (one warp per 256-row stripe)
 
 template <typename T>
 int dalloc(swgpu_db* db, T** p, size_t count) {

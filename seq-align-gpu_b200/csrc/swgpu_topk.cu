@@ -95,7 +95,7 @@ __global__ void topk_ranksort(const unsigned long long* __restrict__ keys, const
   if (i < k) { keys_out[rank] = mine; sidx_out[rank] = sidx[i]; }
 }
 
-// Coordinates: the wavefront kernel k3x<TRACK> (sw_k3x.cuh), one warp per 128-row stripe of a hit; phase 0 =
+// Coordinates: the wavefront kernel k3x<TRACK> (sw_k3x.cuh), one warp per 256-row stripe of a hit; phase 0 =
 // forward (end cell), phase 1 = the reversed prefixes (start cell).
 
 }  // namespace swk
