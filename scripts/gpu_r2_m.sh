@@ -1,10 +1,9 @@
 #!/bin/bash
-# round 2, A/B m: k3x CTAs per SM (4 / 5 / 6): 64-target throughput case and the C4 line
+# round 2, A/B m: k3x CTAs per SM: C4 line (top-100 coordinates on long targets), 64-target throughput case, C2 top-k
 mkdir -p gpurun_out
-for v in "" _vctas5 _vctas6; do
+for v in "" _vctas1 _vctas2 _vctas3; do
   echo "== libswgpu$v.so"
-  SWGPU_LIB=seq-align-gpu_b200/libswgpu$v.so timeout 300 python scripts/k3x_steps.py --targets 64 --lqs 4096,35213 --reps 2 2>/dev/null | grep ms_rescore | cut -c1-140
-  SWGPU_LIB=seq-align-gpu_b200/libswgpu$v.so timeout 300 python scripts/k3x_steps.py --lqs 35213 --reps 3 2>/dev/null | grep ms_rescore | cut -c1-140
+  SWGPU_LIB=seq-align-gpu_b200/libswgpu$v.so timeout 300 python scripts/k3x_steps.py --targets 64 --lqs 35213 --reps 2 2>/dev/null | grep ms_rescore | cut -c1-140
   SWGPU_LIB=seq-align-gpu_b200/libswgpu$v.so timeout 600 python bench.py --workload c4 --steps 3 --warmup 3 --no-cpu 2>/dev/null | python -c "
 import json,sys
 d=json.loads(sys.stdin.read())

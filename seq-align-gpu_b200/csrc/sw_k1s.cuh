@@ -423,25 +423,35 @@ static __global__ void k1s_finalize(const unsigned* __restrict__ raw, long pair_
                                     unsigned B, unsigned limit, const int64_t* __restrict__ order,
                                     const int64_t* __restrict__ plain_off, int long_thr,
                                     int32_t* __restrict__ scores_file, int* __restrict__ rescore_list,
-                                    unsigned* __restrict__ rescore_count, unsigned long long* __restrict__ rescore_residues) {
+                                    unsigned* __restrict__ rescore_count, unsigned long long* __restrict__ rescore_residues,
+                                    int slot_rows, int lq, int* __restrict__ row_bound) {
   for (long p = pair_begin + blockIdx.x * (long)blockDim.x + threadIdx.x; p < n_pairs; p += (long)gridDim.x * blockDim.x) {
     const unsigned* r = raw + (size_t)p * (size_t)slots;
-    unsigned m = r[0];
-    for (int i = 1; i < slots; ++i) m = __vmaxu2(m, r[i]);
-    const unsigned lo = m & 0xffffu, hi = m >> 16;
+    // maximum of each half and the LAST slot that holds it.  Slot i of a launch whose slots are not merged over the stripes
+    // covers the query rows [i * slot_rows, (i + 1) * slot_rows): no row below that slot's last one holds the target's score,
+    // which is all the forward coordinate pass of a reported hit has to look at (swgpu_topk.cu).
+    unsigned lo = 0, hi = 0; int ilo = 0, ihi = 0;
+    for (int i = 0; i < slots; ++i) {
+      const unsigned v = r[i], l = v & 0xffffu, h = v >> 16;
+      if (l >= lo) { lo = l; ilo = i; }
+      if (h >= hi) { hi = h; ihi = i; }
+    }
     const bool sat = (lo >= limit) || (hi >= limit);
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
       const long s = 2 * p + h;
       if (s >= n_sorted) continue;
       const bool force = long_thr > 0 && (plain_off[s + 1] - plain_off[s]) > long_thr;
+      int bound = lq - 1;
       if (sat || force) {
         const unsigned slot = atomicAdd(rescore_count, 1u);
         rescore_list[slot] = (int)s;
         atomicAdd(rescore_residues, (unsigned long long)(plain_off[s + 1] - plain_off[s]));      // statistics: cells of the 32-bit pass
       } else {
         scores_file[order[s]] = (int32_t)((h ? hi : lo) - B);
+        if (slot_rows > 0) bound = min(bound, ((h ? ihi : ilo) + 1) * slot_rows - 1);
       }
+      if (row_bound) row_bound[s] = bound;
     }
   }
 }

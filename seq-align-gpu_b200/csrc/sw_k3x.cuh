@@ -70,6 +70,7 @@ struct K3XParams {
   // typically ends after the ~100 columns of the alignment itself instead of the whole prefix.
   const unsigned long long* hit_keys;   // TRACK: sorted keys of the hits (score << 32 | ~entry); nullptr = no early stop
   int*            stop_col;     // TRACK: [n_targets] for this phase
+  const int*      row_bound;    // TRACK phase 0: by sorted position, the last query row that can hold the hit's score (nullptr: none)
   unsigned*       error_flag;
   unsigned*       sm_slots;     // [256], zero at launch: CTAs that have started on each SM (a CTA's level = its arrival number there)
   int             level_ctas;   // CTAs per level = number of SMs
@@ -199,6 +200,7 @@ __global__ void __launch_bounds__(K3X_WARPS * 32) k3x(const K3XParams P) {
     const int8_t* qp = P.query;
     int qstep = 1, tstep = 1;
     bool skip = false;
+    if (TRACK && P.phase == 0 && P.row_bound) lq = min(lq, P.row_bound[sidx] + 1);   // rows below hold lower scores: not needed
     if (TRACK && P.phase == 1) {
       const int4 c = P.coords[t];
       if (c.y < 0) skip = true;

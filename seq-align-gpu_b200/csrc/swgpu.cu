@@ -46,6 +46,7 @@ int slot_prepare(swgpu_db* db, swgpu_slot& S) {
   if ((r = dalloc(db, &S.d_scores, (size_t)db->n))) return r;
   if ((r = dalloc(db, &S.d_raw_s, (size_t)db->n_pairs * 32))) return r;
   if ((r = dalloc(db, &S.d_rescore_list, (size_t)db->n))) return r;
+  if ((r = dalloc(db, &S.d_row_bound, (size_t)db->n))) return r;
   if ((r = dalloc(db, &S.d_counters, 16))) return r;
   if ((r = dalloc(db, &S.d_table, 1024))) return r;
   if ((r = dalloc(db, &S.d_bnd_s, (size_t)db->k1s_grid * swk::K1S_WARPS * (size_t)db->bnd_s_stride))) return r;
@@ -80,7 +81,7 @@ int k3x_prepare(swgpu_db* db, swgpu_slot& S, int lq, cudaStream_t stream) {
 }
 
 void slot_release(swgpu_slot& S) {
-  cudaFree(S.d_scores); cudaFree(S.d_raw_s); cudaFree(S.d_rescore_list); cudaFree(S.d_counters);
+  cudaFree(S.d_scores); cudaFree(S.d_raw_s); cudaFree(S.d_rescore_list); cudaFree(S.d_row_bound); cudaFree(S.d_counters);
   cudaFree(S.d_bnd_s); cudaFree(S.d_bnd3); cudaFree(S.d_bnd3s); cudaFree(S.d_query); cudaFree(S.d_table);
   cudaFree(S.d_sprof); cudaFree(S.d_sprof2);
   cudaFree(S.d_keys); cudaFree(S.d_hit_sidx); cudaFree(S.d_sel); cudaFree(S.d_coords);
@@ -540,7 +541,8 @@ int enqueue_search(swgpu_db* db, swgpu_slot& S, const int8_t* query, int64_t lq,
       if ((r = launch_k1s(db, PL, 32, plan_long.R, false, oe, ge, sa, (int)std::min<int64_t>(nls, db->k1s_grid)))) return r;
       swk::k1s_finalize<<<std::max(1, (int)((nlp + 255) / 256)), 256, 0, sa>>>(
           S.d_raw_s, 0, (long)nlp, 32, (long)db->n, B, limit, db->d_order, db->d_plain_off, db->long_threshold,
-          S.d_scores, S.d_rescore_list, S.d_counters + 2, reinterpret_cast<unsigned long long*>(S.d_counters + 12));
+          S.d_scores, S.d_rescore_list, S.d_counters + 2, reinterpret_cast<unsigned long long*>(S.d_counters + 12),
+          plan_long.R, (int)lq, S.d_row_bound);
       CU(cudaGetLastError()); st.kernel_launches += 3;
     }
     CU(cudaEventRecord(e[4], sa));
@@ -591,14 +593,16 @@ int enqueue_search(swgpu_db* db, swgpu_slot& S, const int8_t* query, int64_t lq,
       if (nxp > 0) {
         swk::k1s_finalize<<<std::max(1, (int)((nxp + 255) / 256)), 256, 0, sm>>>(
             S.d_xs_raw, 0, (long)nxp, 32 * plan.npass, (long)db->n, B, limit, db->d_order, db->d_plain_off,
-            db->long_threshold, S.d_scores, S.d_rescore_list, S.d_counters + 2, reinterpret_cast<unsigned long long*>(S.d_counters + 12));
+            db->long_threshold, S.d_scores, S.d_rescore_list, S.d_counters + 2, reinterpret_cast<unsigned long long*>(S.d_counters + 12),
+            plan.R, (int)lq, S.d_row_bound);
         st.kernel_launches++;
       }
       const int64_t pb = nlp + nxp;                            // first pair scored by the bulk items
       if (db->n_pairs > pb)
         swk::k1s_finalize<<<(int)std::min<int64_t>((db->n_pairs - pb + 255) / 256, 4096), 256, 0, sm>>>(
             PS.raw, (long)pb, (long)db->n_pairs, 1 << plan.g_log2, (long)db->n, B, limit, db->d_order, db->d_plain_off,
-            db->long_threshold, S.d_scores, S.d_rescore_list, S.d_counters + 2, reinterpret_cast<unsigned long long*>(S.d_counters + 12));
+            db->long_threshold, S.d_scores, S.d_rescore_list, S.d_counters + 2, reinterpret_cast<unsigned long long*>(S.d_counters + 12),
+            multi ? 0 : plan.R, (int)lq, S.d_row_bound);                   // a multi-stripe bulk slot is the maximum over the stripes: no bound
       CU(cudaGetLastError()); st.kernel_launches += 2;
     }
     CU(cudaEventRecord(e[5], sm));
@@ -608,6 +612,7 @@ int enqueue_search(swgpu_db* db, swgpu_slot& S, const int8_t* query, int64_t lq,
     if ((r = launch_32bit(db, S, sa, S.d_rescore_list, S.d_counters + 2, 0, (int)lq, oe, ge, S.d_counters + 3,
                           S.d_counters + 4, &st.kernel_launches))) return r;
   } else {
+    if (db->n) CU(cudaMemsetAsync(S.d_row_bound, 0x7f, sizeof(int) * (size_t)db->n, sm));     // no 16-bit pass: no row bounds
     CU(cudaEventRecord(e[5], sm));
     CU(cudaStreamWaitEvent(sa, e[5], 0));
     CU(cudaEventRecord(e[1], sa));

@@ -32,6 +32,7 @@ struct swgpu_slot {
   int32_t*  d_scores = nullptr;        // file order
   unsigned* d_raw_s = nullptr;         // n_pairs * 32 packed running maxima
   int*      d_rescore_list = nullptr;  // up to n
+  int*      d_row_bound = nullptr;     // [n] by sorted position: last query row that can hold the target's score (k1s_finalize)
   unsigned* d_counters = nullptr;      // [0] k1s queue, [1] k1s long queue, [2] rescore count, [3] k3 queue, [4] k3x queue,
                                        // [5] k3 all-targets queue, [6] k3x error flag, [7] top-k error flag,
                                        // [8] top-k coordinate queue phase 0, [9] phase 1, [12..13] residues of the rescored targets (u64)

@@ -164,6 +164,7 @@ int enqueue_topk(swgpu_db* db, swgpu_slot& S, int k) {
     P.lq = (int)S.lq; P.nstripes_max = ((int)S.lq + swk::K3X_ROWS - 1) / swk::K3X_ROWS; P.table = S.d_table; P.oe = S.oe; P.ge = S.ge;
     P.rows = S.d_x_rows; P.row_stride = db->x_row_stride; P.coords = S.d_coords; P.best_out = best_out;
     P.error_flag = S.d_counters + 7;
+    P.row_bound = (S.use16 && !getenv("SWGPU_TOPK_NO_ROW_BOUND")) ? S.d_row_bound : nullptr;      // A/B knob
     P.hit_keys = getenv("SWGPU_TOPK_NO_EARLY_STOP") ? nullptr : keys_s;     // A/B knob: the coordinate passes scan their whole rectangles
     CU(cudaMemsetAsync(S.d_hit_sidx + 3 * cap, 0x7f, sizeof(int) * 2 * (size_t)cap, st));        // stop columns: 0x7f7f7f7f = none yet
     const int grid = db->sm_count * swk::k3x_ctas_per_sm<true>(db->device);    // the whole machine: CTAs beyond the levels the items need leave at once (sw_k3x.cuh)
