@@ -99,6 +99,33 @@ void slot_release(swgpu_slot& S) {
 
 namespace {
 
+// Host -> device copy of a large pageable array through two pinned staging buffers: the host memcpy into one buffer
+// overlaps the DMA out of the other (north_star (1): "pinned, HBM-resident batches"; a plain cudaMemcpy from pageable
+// memory stages through the driver's own buffer synchronously, chunk after chunk).
+static int upload_staged(void* dst, const void* src, size_t bytes) {
+  constexpr size_t CHUNK = 16u << 20;
+  if (bytes <= CHUNK) { CU(cudaMemcpy(dst, src, bytes, cudaMemcpyHostToDevice)); return SWGPU_OK; }
+  void* stage[2] = {nullptr, nullptr}; cudaEvent_t ev[2] = {nullptr, nullptr}; cudaStream_t st = nullptr;
+  auto body = [&]() -> int {
+    CU(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+    for (int i = 0; i < 2; ++i) { CU(cudaMallocHost(&stage[i], CHUNK)); CU(cudaEventCreateWithFlags(&ev[i], cudaEventDisableTiming)); }
+    int b = 0;
+    for (size_t o = 0; o < bytes; o += CHUNK, b ^= 1) {
+      const size_t n = std::min(CHUNK, bytes - o);
+      CU(cudaEventSynchronize(ev[b]));                       // the DMA that last used this buffer is done (no-op the first time)
+      memcpy(stage[b], (const char*)src + o, n);
+      CU(cudaMemcpyAsync((char*)dst + o, stage[b], n, cudaMemcpyHostToDevice, st));
+      CU(cudaEventRecord(ev[b], st));
+    }
+    CU(cudaStreamSynchronize(st));
+    return SWGPU_OK;
+  };
+  const int rc = body();
+  for (int i = 0; i < 2; ++i) { if (stage[i]) cudaFreeHost(stage[i]); if (ev[i]) cudaEventDestroy(ev[i]); }
+  if (st) cudaStreamDestroy(st);
+  return rc;
+}
+
 // Host tables + device buffers of a packed database.  With pk.plain / pk.scols present they are uploaded; without
 // (layout only, swgpu_db_create_synthetic) the two buffers are allocated and `fill` generates them on the device.
 template <typename Fill>
@@ -145,8 +172,8 @@ static int db_from_pack(swgpu_db_t** out, int device, swpack_t& pk, int64_t entr
     CU(cudaMemcpy(db->d_stream_ncols, pk.stream_ncols, sizeof(int32_t) * (size_t)pk.n_streams, cudaMemcpyHostToDevice));
     CU(cudaMemcpy(db->d_stream_pair0, pk.stream_pair0, sizeof(int64_t) * (size_t)pk.n_streams, cudaMemcpyHostToDevice));
     if (pk.plain && pk.scols) {
-      CU(cudaMemcpy(db->d_plain, pk.plain, (size_t)pk.n_residues, cudaMemcpyHostToDevice));
-      CU(cudaMemcpy(db->d_scols, pk.scols, sizeof(uint16_t) * (size_t)pk.scols_len, cudaMemcpyHostToDevice));
+      if ((r = upload_staged(db->d_plain, pk.plain, (size_t)pk.n_residues))) return r;
+      if ((r = upload_staged(db->d_scols, pk.scols, sizeof(uint16_t) * (size_t)pk.scols_len))) return r;
     } else if ((r = fill(db))) {
       return r;
     }
