@@ -103,3 +103,46 @@ def test_topk_coordinates_with_ties_and_early_stop(oracle, matrices):
     assert results[0][2] == results[2][2] and results[1][2] == results[3][2]
     print(f"top-{len(parts)} coordinates, Lq=900: {results[0][3]:.2f} ms with the early stop, {results[2][3]:.2f} ms without")
     db.close()
+
+
+def test_topk_row_bound_of_the_forward_pass_with_ties_across_stripes(oracle, matrices):
+    """The forward coordinate pass stops at the last query row that can hold the hit's score (k1s_finalize records the last
+    lane slot holding the maximum; X pairs keep one set of slots per stripe).  The query carries the same 200-residue segment
+    twice, 1 100 rows apart -- in different stripes of the two-stripe 16-bit plan -- so a target holding it once has two equal
+    maxima in different row bands: the bound must keep both, the first one in scan order must win, and the hits must be the
+    same with the bound switched off (SWGPU_TOPK_NO_ROW_BOUND).  The database is small: every stream is an X item."""
+    import os
+    import swgpu
+    from swgpu import synth
+    tab = matrices["BLOSUM62"]
+    g = synth.rng(270)
+    q0 = synth.make_query(271, 900)
+    bgr = lambda n: synth.residues(g, int(n))
+    q = np.concatenate([q0, bgr(300), q0[100:300], bgr(700)])           # 2 100 rows: q0[100:300] at rows 100.. and 1 200..
+    parts = [
+        np.concatenate([bgr(500), q0[100:300], bgr(800)]),              # one copy: equal maxima in both stripes' bands
+        np.concatenate([bgr(200), q0[100:300], bgr(900), q0[100:300], bgr(100)]),
+        np.concatenate([bgr(1200), q[1900:2090], bgr(30)]),             # a hit in the last rows
+        np.concatenate([q0[0:150], bgr(2000)]),                         # a hit in the first rows
+        bgr(3000), q0[100:300].copy(),
+    ] + [bgr(L) for L in g.integers(1, 900, size=30)]
+    off = np.zeros(len(parts) + 1, np.int64); np.cumsum([p.size for p in parts], out=off[1:])
+    codes = np.concatenate(parts)
+    db = swgpu.Database(codes, off)
+    out = []
+    for env in (None, "1"):
+        if env: os.environ["SWGPU_TOPK_NO_ROW_BOUND"] = env
+        else: os.environ.pop("SWGPU_TOPK_NO_ROW_BOUND", None)
+        _, st = db.search(q, tab, -10, -1)
+        assert st["passes"] >= 2
+        hits = db.topk(len(parts))
+        out.append(hits)
+        for h in hits:
+            i = h["entry"]
+            s, c = oracle.end_start(q, codes[off[i]:off[i + 1]], tab, -10, -1)
+            assert (h["score"], h["q_start"], h["q_end"], h["t_start"], h["t_end"]) == (s, *c), (env, h, c)
+    os.environ.pop("SWGPU_TOPK_NO_ROW_BOUND", None)
+    assert out[0] == out[1]
+    first = [h for h in out[0] if h["entry"] == 0][0]
+    assert first["q_end"] < 400                                          # of the two equal maxima the one in the upper rows wins
+    db.close()
