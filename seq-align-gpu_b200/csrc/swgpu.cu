@@ -335,7 +335,7 @@ struct K1SPlan { int g, g_log2, R, npass; };
 // Measured deviations of single instantiations from the smooth model (scripts/tune_plan.py on the C2 database,
 // profiles/r1f_tune_plan_odd.jsonl): the planner may take one or two rows per lane more than needed to avoid them.
 double k1s_penalty(int g, int R) {
-  if (R == 21) return 1.09;                        // unpaired profile loads, 95 registers
+  if (R == 21 && g < 32) return 1.09;              // unpaired profile loads, 95 registers (g = 32: no deviation with the round-2 kernel)
   if (R == 11) return 1.06;
   if (R == 8 && g == 8) return 1.25;
   if (R == 25 && g < 32) return 1.05;
@@ -357,9 +357,16 @@ K1SPlan plan_k1s(int64_t lq, int64_t n_streams, int warp_slots) {
     }
   }
   if (best_cost < 0) {
-    // multi-stripe: measured time per padded query row on the C2 database (scripts/tune_plan.py, us per row)
-    static const struct { int R; double us_per_row; } kMulti[] = {{16, 44.2}, {20, 39.7}, {24, 37.63}, {25, 37.96}, {26, 36.94}, {27, 36.85},
-                                                                  {28, 36.3}, {29, 36.55}, {30, 36.8}, {31, 37.8}, {32, 36.72}};
+    // multi-stripe: measured time per padded query row on the C2 database (scripts/tune_plan.py, us per row; round-2 kernels:
+    // profiles/r2c_tune_plan.jsonl).  A database too small to fill the GPU runs every stream as X items on one CTA per SM, a
+    // latency regime with its own ranking (profiles/r1f_c4_plans.txt): it keeps the table measured there.
+    struct MultiCost { int R; double us_per_row; };
+    static const MultiCost kBulk[] = {{16, 41.3}, {20, 35.45}, {24, 35.33}, {25, 35.2}, {26, 33.2}, {27, 34.2},
+                                      {28, 33.85}, {29, 34.15}, {30, 34.95}, {31, 33.43}, {32, 34.24}};
+    static const MultiCost kFew[] = {{16, 44.2}, {20, 39.7}, {24, 37.63}, {25, 37.96}, {26, 36.94}, {27, 36.85},
+                                     {28, 36.3}, {29, 36.55}, {30, 36.8}, {31, 37.8}, {32, 36.72}};
+    const bool few = n_streams < 2 * (int64_t)warp_slots;
+    const MultiCost (&kMulti)[11] = few ? kFew : kBulk;
     for (const auto& m : kMulti) {
       const int np = (int)((lq + 32 * m.R - 1) / (32 * m.R));
       const double cost = (double)np * 32 * m.R * m.us_per_row;
