@@ -321,8 +321,8 @@ __global__ void __launch_bounds__(K1S_WARPS * 32, (R <= K1S_R3CTA ? 3 : 2)) k1s(
       };
 
       unsigned cw_next = 0;
-      for (int s0 = 0; s0 < nsteps; s0 += UN) {
-        if ((s0 & (g - 1)) == 0) {                 // every g steps: publish the prefetched block, fetch the next
+      // every g steps: publish the prefetched block, fetch the next
+      auto boundary = [&](const int s0) {
           __syncwarp();
           { const int p = (s0 & (RN - 1)) + lane_g; const unsigned w = ring_word(pre); gring[p] = w; gring[p + RN] = w; }
           const int c = s0 + g + lane_g;
@@ -340,10 +340,8 @@ __global__ void __launch_bounds__(K1S_WARPS * 32, (R <= K1S_R3CTA ? 3 : 2)) k1s(
           // columns [0, s0 - 31) of this stripe's bottom row are in memory (written by the whole warp above, ordered by the __syncwarp)
           if (MULTI && has_out && is31 && s0 > 31) k1s_st_release(prog, (unsigned)min(s0 - 31, ncols));
           if (PF) cw_next = lds32_ordered(rd_lane + ((unsigned)(s0 & (RN - 1)) << 2));   // the word prefetched for this step predates the publish
-        }
-#pragma unroll
-        for (int u = 0; u < UN; ++u) {
-          const int s = s0 + u;
+      };
+      auto step = [&](const int s) {
           const unsigned cw = PF ? cw_next : lds32_ordered(rd_lane + ((unsigned)(s & (RN - 1)) << 2));
           unsigned h_up, v_in;
           if (MULTI) {                              // first lane: the stripe above (constants in the first stripe), via the shuffle's default
@@ -403,6 +401,27 @@ __global__ void __launch_bounds__(K1S_WARPS * 32, (R <= K1S_R3CTA ? 3 : 2)) k1s(
           out_v = V;
           if (MULTI && !last && is31) ring3[s & 31] = make_uint2(out_h, out_v);
           if (PF) cw_next = lds32_ordered(rd_lane + ((unsigned)((s + 1) & (RN - 1)) << 2));   // next step's ring word (re-loaded after a publish, above)
+      };
+      // Multi-stripe kernels: blocks of 32 steps without the per-step block test, for the rows-per-lane values where that is
+      // faster (every multi-stripe plan timed both ways on the C2 database, profiles/r2w_ab_nested_per_R.txt: R = 16, 24, 28,
+      // 29, 30, 32: 0.7-2.7 % faster; 20, 31: the same; 25, 26, 27: 1.4-2.3 % slower).  -DK1S_NESTED=0 / 1 forces one form.
+#ifndef K1S_NESTED
+#define K1S_NESTED (-1)
+#endif
+      constexpr bool NEST = MULTI && (K1S_NESTED >= 0 ? K1S_NESTED != 0
+                                                      : (R == 16 || R == 24 || R == 28 || R == 29 || R == 30 || R == 32));
+      if (NEST) {
+        for (int s0 = 0; s0 < nsteps; s0 += 32) {
+          boundary(s0);
+          const int se = min(s0 + 32, nsteps);
+#pragma unroll 1
+          for (int s = s0; s < se; ++s) step(s);
+        }
+      } else {
+        for (int s0 = 0; s0 < nsteps; s0 += UN) {
+          if ((s0 & (g - 1)) == 0) boundary(s0);
+#pragma unroll
+          for (int u = 0; u < UN; ++u) step(s0 + u);
         }
       }
       if (MULTI && !last && nsteps > 0) {          // the columns of the last (partial) block of steps

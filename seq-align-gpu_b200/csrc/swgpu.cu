@@ -358,11 +358,11 @@ K1SPlan plan_k1s(int64_t lq, int64_t n_streams, int warp_slots) {
   }
   if (best_cost < 0) {
     // multi-stripe: measured time per padded query row on the C2 database (scripts/tune_plan.py, us per row; round-2 kernels:
-    // profiles/r2c_tune_plan.jsonl).  A database too small to fill the GPU runs every stream as X items on one CTA per SM, a
+    // profiles/r2c_tune_plan.jsonl, r2w_ab_nested_per_R.txt).  A database too small to fill the GPU runs every stream as X items on one CTA per SM, a
     // latency regime with its own ranking (profiles/r1f_c4_plans.txt): it keeps the table measured there.
     struct MultiCost { int R; double us_per_row; };
-    static const MultiCost kBulk[] = {{16, 41.3}, {20, 35.45}, {24, 35.33}, {25, 35.2}, {26, 33.2}, {27, 34.2},
-                                      {28, 33.85}, {29, 34.15}, {30, 34.95}, {31, 33.43}, {32, 34.24}};
+    static const MultiCost kBulk[] = {{16, 40.6}, {20, 35.54}, {24, 34.6}, {25, 35.2}, {26, 33.5}, {27, 34.24},
+                                      {28, 33.68}, {29, 33.67}, {30, 34.05}, {31, 33.43}, {32, 33.37}};   // profiles/r2w_ab_nested_per_R.txt
     static const MultiCost kFew[] = {{16, 44.2}, {20, 39.7}, {24, 37.63}, {25, 37.96}, {26, 36.94}, {27, 36.85},
                                      {28, 36.3}, {29, 36.55}, {30, 36.8}, {31, 37.8}, {32, 36.72}};
     const bool few = n_streams < 2 * (int64_t)warp_slots;
