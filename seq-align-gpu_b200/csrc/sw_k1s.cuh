@@ -308,14 +308,36 @@ __global__ void __launch_bounds__(K1S_WARPS * 32, (R <= K1S_R3CTA ? 3 : 2)) k1s(
       }
       __syncwarp();
 
+      // where this lane's maxima go: slot of the stream's first pair and the distance to the next pair's, in registers -- the
+      // flush (once per pair) then touches no kernel parameter (its constant-bank loads sat in the column loop's body).
+      // A/B per plan on the C2 database (profiles/r2y_ab_slot_ptr.txt): 1.1-1.7 % faster for the multi-stripe kernels except
+      // R = 24 and 28 (1.2-1.4 % slower), within +-0.7 % for the single-stripe ones except g x R = 32 x 32 (1.8 % slower).
+      // Also tried there: the four IDP byte selectors in registers instead of re-materialised uniform registers (4 UMOV per
+      // column step): 2-4 % SLOWER in the multi-stripe kernels, not kept.
+#ifndef K1S_SLOT_PTR
+#define K1S_SLOT_PTR (-1)
+#endif
+      constexpr bool SLOTP = K1S_SLOT_PTR >= 0 ? K1S_SLOT_PTR != 0 : (MULTI ? (R != 24 && R != 28) : !(R == 32 && g == 32));
+      unsigned* slot0 = nullptr; int slot_stride = 0;
+      if (SLOTP && valid) {
+        const size_t p0 = (size_t)P.stream_pair0[st];
+        if (MULTI && x_item) { slot0 = P.x_raw + (((p0 * P.npass + pass) << 5) + lane); slot_stride = P.npass << 5; }
+        else { slot0 = P.raw + ((p0 << g_log2) + lane_g); slot_stride = 1 << g_log2; }
+      }
       auto flush = [&]() {
         if (pair_rel >= 0) {
-          const size_t pair_idx = (size_t)P.stream_pair0[st] + (size_t)pair_rel;
-          if (MULTI && x_item) {
-            P.x_raw[((pair_idx * P.npass + pass) << 5) + lane] = best;
+          if (SLOTP) {
+            unsigned* slot = slot0 + (size_t)pair_rel * (size_t)slot_stride;
+            if (MULTI && x_item) *slot = best;
+            else *slot = (MULTI && !first) ? __vmaxu2(*slot, best) : best;
           } else {
-            unsigned* slot = P.raw + (pair_idx << g_log2) + lane_g;
-            *slot = (MULTI && !first) ? __vmaxu2(*slot, best) : best;
+            const size_t pair_idx = (size_t)P.stream_pair0[st] + (size_t)pair_rel;
+            if (MULTI && x_item) {
+              P.x_raw[((pair_idx * P.npass + pass) << 5) + lane] = best;
+            } else {
+              unsigned* slot = P.raw + (pair_idx << g_log2) + lane_g;
+              *slot = (MULTI && !first) ? __vmaxu2(*slot, best) : best;
+            }
           }
         }
       };
