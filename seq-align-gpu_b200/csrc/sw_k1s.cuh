@@ -198,7 +198,7 @@ __global__ void __launch_bounds__(K1S_WARPS * 32, (R <= K1S_R3CTA ? 3 : 2)) k1s(
 
   constexpr int g = LANES, g_log2 = (LANES == 8 ? 3 : LANES == 16 ? 4 : 5);
   constexpr int UN = MULTI ? K1S_UNROLL_MULTI : K1S_UNROLL_SINGLE;
-  constexpr bool PF = K1S_PREFETCH != 0 && !MULTI;       // single-stripe only (measured: the multi-stripe kernel is 0.2-1.8 % slower with it)
+  constexpr bool PF = K1S_PREFETCH != 0 && (!MULTI || K1S_PREFETCH == 2);       // single-stripe only (measured: the multi-stripe kernel is 0.2-1.8 % slower with it; -DK1S_PREFETCH=2 turns it on there)
   static_assert(UN == 1 || UN == 2 || UN == 4, "columns per loop iteration");
   const int lane_g = lane & (g - 1), grp = lane >> g_log2, per_warp = 32 >> g_log2;
   constexpr int RN = 2 * g;
@@ -502,6 +502,6 @@ static __global__ void k1s_finalize(const unsigned* __restrict__ raw, long pair_
 template <int GAPSEL>
 cudaError_t launch_k1s_o3(int g, int R, bool multi, const K1SParams& P, cudaStream_t stream, int grid, int device);
 template <int GAPSEL>
-cudaError_t launch_k1s_o1(int R, const K1SParams& P, cudaStream_t stream, int grid, int device);     // multi-stripe, R = 26..32
+cudaError_t launch_k1s_o1(int R, const K1SParams& P, cudaStream_t stream, int grid, int device);     // multi-stripe, R = 24..32
 
 }  // namespace swk

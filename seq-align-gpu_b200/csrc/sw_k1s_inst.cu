@@ -1,11 +1,13 @@
 // sw_k1s_inst.cu -- the K1S instantiations of ONE gap specialisation (-DK1S_GAPSEL=0|1|2) and ONE ptxas option set
-// (-DK1S_PART=0: everything built at -O3; -DK1S_PART=1: the multi-stripe kernels with 26..32 rows per lane, built at
+// (-DK1S_PART=0: everything built at -O3; -DK1S_PART=1: the multi-stripe kernels with 24..32 rows per lane, built at
 // ptxas -O1).  The Makefile compiles this file six times, in parallel.
 //
 // Why a part of its own at -O1: at -O3 the multi-stripe kernels with the most rows per lane sit on the 128-register
 // ceiling of two CTAs per SM and spill 24-56 bytes in the cell loop; at -O1 they take 120-126 registers and do not
 // spill (round 1: 4.5-5.5 % faster at R = 30, 32; re-checked with the round-2 kernel by `nvcc -Xptxas -v`).  Every
-// other instantiation is as fast or faster at -O3 (scripts/ab_lib.py, two builds interleaved on one box).
+// other instantiation is as fast or faster at -O3 (scripts/ab_lib.py, two builds interleaved on one box).  Round 2, every
+// multi-stripe plan timed at both levels (profiles/r2y_ab_ptxas_levels.txt): R = 26..32 are 1.4-5.8 % faster at -O1, R = 24, 25
+// 1.0-1.8 % (moved here), R = 16, 20 and the single-stripe kernels are faster at -O3.
 #include "sw_k1s.cuh"
 
 #ifndef K1S_GAPSEL
@@ -48,15 +50,13 @@ cudaError_t launch_single(int R, const K1SParams& P, cudaStream_t stream, int gr
 }  // namespace
 
 #if K1S_PART == 0
-// Instantiated: every R in 8..32 for g = 8, 16, 32; multi-stripe (g = 32) with R in {16, 20, 24, 25} (26..32: part 1).
+// Instantiated: every R in 8..32 for g = 8, 16, 32; multi-stripe (g = 32) with R in {16, 20} (24..32: part 1).
 template <>
 cudaError_t launch_k1s_o3<K1S_GAPSEL>(int g, int R, bool multi, const K1SParams& P, cudaStream_t stream, int grid, int device) {
   if (multi) {
     switch (R) {
       case 16: return launch_t<16, 32, true>(P, stream, grid, device);
       case 20: return launch_t<20, 32, true>(P, stream, grid, device);
-      case 24: return launch_t<24, 32, true>(P, stream, grid, device);
-      case 25: return launch_t<25, 32, true>(P, stream, grid, device);
       default: return cudaErrorInvalidValue;
     }
   }
@@ -69,6 +69,8 @@ cudaError_t launch_k1s_o3<K1S_GAPSEL>(int g, int R, bool multi, const K1SParams&
 template <>
 cudaError_t launch_k1s_o1<K1S_GAPSEL>(int R, const K1SParams& P, cudaStream_t stream, int grid, int device) {
   switch (R) {
+    case 24: return launch_t<24, 32, true>(P, stream, grid, device);
+    case 25: return launch_t<25, 32, true>(P, stream, grid, device);
     case 26: return launch_t<26, 32, true>(P, stream, grid, device);
     case 27: return launch_t<27, 32, true>(P, stream, grid, device);
     case 28: return launch_t<28, 32, true>(P, stream, grid, device);

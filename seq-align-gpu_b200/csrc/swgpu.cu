@@ -386,7 +386,7 @@ K1SPlan plan_k1s(int64_t lq, int64_t n_streams, int warp_slots) {
 
 template <int GAPSEL>
 cudaError_t launch_k1s_sel(int g, int R, bool multi, const swk::K1SParams& P, cudaStream_t stream, int grid, int device) {
-  if (multi && R >= 26) return swk::launch_k1s_o1<GAPSEL>(R, P, stream, grid, device);
+  if (multi && R >= 24) return swk::launch_k1s_o1<GAPSEL>(R, P, stream, grid, device);
   return swk::launch_k1s_o3<GAPSEL>(g, R, multi, P, stream, grid, device);
 }
 
