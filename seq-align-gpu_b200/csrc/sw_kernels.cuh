@@ -99,6 +99,8 @@ struct K3Params {
   int32_t*       scores_file;
   unsigned       one;
   int            max_len;      // targets longer than this are left to the wavefront kernel k3x (0 = no limit)
+  unsigned*      sm_slots;     // [256], zero at launch, or nullptr: CTAs started per SM (placement by level, as in k3x)
+  int            level_ctas;   // CTAs per level = number of SMs
 };
 
 constexpr int K3_WARPS = 4;
@@ -109,8 +111,23 @@ __global__ void __launch_bounds__(K3_WARPS * 32) k3_intra(const K3Params P) {
   constexpr int W = R3 / 4;                        // profile words per (lane, code)
   __shared__ unsigned pl_all[K3_WARPS][32 * W * 32];
   __shared__ int8_t tab[32 * 32];
+  // Placement by level (see k3x): a rescoring list is often far shorter than the grid has warps, and the queue hands the
+  // items to whichever warps ask first -- a few SMs with four busy warps per scheduler while the rest of the machine idles.
+  // CTAs number themselves per SM in arrival order; level L takes part only when the levels below cannot give every item
+  // a warp of its own, and lets them ask first.
+  __shared__ int cta_level;
+  if (P.sm_slots && threadIdx.x == 0) {
+    unsigned smid; asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    cta_level = (int)atomicAdd(P.sm_slots + (smid & 255u), 1u);
+  }
   for (int i = threadIdx.x; i < 1024; i += blockDim.x) tab[i] = P.table[i];
   __syncthreads();
+  if (P.sm_slots) {
+    const long long items = P.work_count ? (long long)*P.work_count : (long long)P.n_work;
+    const long long per_level = (long long)P.level_ctas * K3_WARPS;
+    if (items <= (long long)cta_level * per_level) return;
+    if (cta_level > 0 && items < (long long)gridDim.x * K3_WARPS) __nanosleep(3000u * (unsigned)min(cta_level, 8));
+  }
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   unsigned* pl = pl_all[warp];
   const unsigned pl_addr = (unsigned)__cvta_generic_to_shared(pl) + lane * 4;
@@ -190,14 +207,16 @@ __global__ void __launch_bounds__(K3_WARPS * 32) k3_intra(const K3Params P) {
           for (int ww = 0; ww < W; ++ww) wreg[ww] = lds32_ordered(poff + ww * 128);
 #pragma unroll
           for (int k = 0; k < R3; ++k) {
+            // gap states shifted by -oe (G holds G - oe, V holds V - oe): one add per operation and a row-to-row chain of ONE
+            // operation (V' from Hx, which does not depend on V; valid for oe <= ge) -- see sw_k3x.cuh
             const int t = (int)add_byte(wreg[k >> 2], 1u << (8 * (k & 3)), (unsigned)d);
-            const int h = __vimax3_s32_relu(t, G[k], V);
+            const int hx = __viaddmax_s32_relu(G[k], oe, t);
+            const int h = __viaddmax_s32(V, oe, hx);
+            V = __viaddmax_s32(V, ge, hx);
+            G[k] = __viaddmax_s32(G[k], ge, h);
             d = H[k];
             H[k] = h;
-            const int u = (int)add_fma((unsigned)h, P.one, (unsigned)oe);
-            G[k] = __viaddmax_s32(G[k], ge, u);
-            V = __viaddmax_s32(V, ge, u);
-            best = max(best, h);
+            if (k & 1) best = __vimax3_s32(best, H[k - 1], h);
           }
           out_h = H[R3 - 1];
           out_v = V;

@@ -47,7 +47,7 @@ int slot_prepare(swgpu_db* db, swgpu_slot& S) {
   if ((r = dalloc(db, &S.d_raw_s, (size_t)db->n_pairs * 32))) return r;
   if ((r = dalloc(db, &S.d_rescore_list, (size_t)db->n))) return r;
   if ((r = dalloc(db, &S.d_row_bound, (size_t)db->n))) return r;
-  if ((r = dalloc(db, &S.d_counters, 16))) return r;
+  if ((r = dalloc(db, &S.d_counters, 16 + 256))) return r;           // 16 counters + the per-SM CTA counters of k3_intra's placement
   if ((r = dalloc(db, &S.d_table, 1024))) return r;
   if ((r = dalloc(db, &S.d_bnd_s, (size_t)db->k1s_grid * swk::K1S_WARPS * (size_t)db->bnd_s_stride))) return r;
   if ((r = dalloc(db, &S.d_bnd3, (size_t)db->k3_grid * swk::K3_WARPS * (size_t)db->bnd3_stride))) return r;
@@ -407,19 +407,27 @@ int launch_k1s(swgpu_db* db, const swk::K1SParams& P, int g, int R, bool multi, 
 }
 
 // 32-bit scoring of a work list (device-side count) or of all targets (list == nullptr): k3_intra (one warp per
-// target) takes the targets shorter than kWaveMinLen, the wavefront kernel k3x (one warp per stripe, many warps per target) the rest.
+// target) takes the short targets, the wavefront kernel k3x (one warp per stripe, many warps per target) the rest (wave_min below).
 int launch_32bit(swgpu_db* db, swgpu_slot& S, cudaStream_t stream, const int* list, const unsigned* list_count,
                  int n_all, int lq, int oe, int ge, unsigned* q_k3, unsigned* q_k3x, int* launches) {
   swk::K3Params P; memset(&P, 0, sizeof(P));
   P.worklist = list; P.work_count = list_count; P.n_work = n_all; P.counter = q_k3;
   P.plain = db->d_plain; P.plain_off = db->d_plain_off; P.query = S.d_query; P.lq = lq; P.table = S.d_table;
   P.oe = oe; P.ge = ge; P.bnd = S.d_bnd3; P.bnd_stride = db->bnd3_stride; P.order = db->d_order;
-  P.scores_file = S.d_scores; P.one = 1u; P.max_len = kWaveMinLen - 1;
+  // Who takes a target: k3_intra runs a target's stripes one after the other on ONE warp (npass x lt column steps in a row),
+  // k3x runs them as a pipeline on npass warps (lt steps + 6 us per stripe).  The longer the query, the shorter the targets
+  // that are worth the pipeline: targets whose serial chain would exceed kWaveMinLen steps go to k3x (Lq <= 256: one stripe,
+  // lt >= 4096 as before; Lq = 6 000: 24 stripes, lt >= 171).  SWGPU_WAVE_MIN=<len> overrides it (A/B knob).
+  const int npass8 = std::max(1, (lq + swk::K3X_ROWS - 1) / swk::K3X_ROWS);
+  int wave_min = std::max(128, kWaveMinLen / npass8);
+  if (const char* ev = getenv("SWGPU_WAVE_MIN")) wave_min = std::max(32, std::min(kWaveMinLen, atoi(ev)));
+  P.scores_file = S.d_scores; P.one = 1u; P.max_len = wave_min - 1;
+  P.sm_slots = S.d_counters + 16; P.level_ctas = db->sm_count;
   if (lq <= 128) swk::k3_intra<4><<<db->k3_grid, swk::K3_WARPS * 32, 0, stream>>>(P);
   else           swk::k3_intra<8><<<db->k3_grid, swk::K3_WARPS * 32, 0, stream>>>(P);
   CU(cudaGetLastError());
   ++*launches;
-  if (db->max_len >= kWaveMinLen) {
+  if (db->max_len >= wave_min) {
     int r = swi::k3x_prepare(db, S, lq, stream);
     if (r) return r;
     swk::K3XParams W; memset(&W, 0, sizeof(W));
@@ -427,7 +435,7 @@ int launch_32bit(swgpu_db* db, swgpu_slot& S, cudaStream_t stream, const int* li
     W.plain = db->d_plain; W.plain_off = db->d_plain_off; W.query = S.d_query; W.lq = lq; W.nstripes_max = (lq + swk::K3X_ROWS - 1) / swk::K3X_ROWS;
     W.table = S.d_table; W.oe = oe; W.ge = ge; W.rows = S.d_x_rows; W.row_stride = db->x_row_stride;
     W.epoch = S.x_epoch; W.done = S.d_x_done; W.partial = S.d_x_partial; W.sm_slots = S.d_x_done + swk::K3X_SLOTS; W.level_ctas = db->sm_count;
-    W.order = db->d_order; W.scores_file = S.d_scores; W.error_flag = S.d_counters + 6; W.min_len = kWaveMinLen;
+    W.order = db->d_order; W.scores_file = S.d_scores; W.error_flag = S.d_counters + 6; W.min_len = wave_min;
     if ((double)db->n * W.nstripes_max >= 4.0e9) return fail(SWGPU_EINVAL, "query too long for this database size (32-bit path)");
 #ifdef K3X_TRACE
     int4* d_trace = nullptr;
@@ -549,7 +557,7 @@ int enqueue_search(swgpu_db* db, swgpu_slot& S, const int8_t* query, int64_t lq,
 
   // ---- timed region: first kernel -> last result resident in HBM ----
   CU(cudaEventRecord(e[0], sm));
-  CU(cudaMemsetAsync(S.d_counters, 0, 16 * sizeof(unsigned), sm));
+  CU(cudaMemsetAsync(S.d_counters, 0, (16 + 256) * sizeof(unsigned), sm));
   int r;
   if (lq == 0 || db->n == 0) {
     if (db->n) CU(cudaMemsetAsync(S.d_scores, 0, sizeof(int32_t) * (size_t)db->n, sm));
