@@ -131,7 +131,23 @@ __global__ void __launch_bounds__(K3X_WARPS * 32) k3x(const K3XParams P) {
   for (int i = threadIdx.x; i < 1024; i += blockDim.x) tab[i] = P.table[i];
   __syncthreads();
   {
-    const long long items = (long long)(P.work_count ? (int)*P.work_count : P.n_targets) * P.nstripes_max;
+    long long items = (long long)(P.work_count ? (int)*P.work_count : P.n_targets) * P.nstripes_max;
+    if (TRACK && P.phase == 1 && P.hit_keys) {
+      // The reversed pass stops at the alignment's start, so most of a hit's stripes leave after one block; what stays busy
+      // is about one stripe per 256 rows of the alignment, i.e. per ~1 024 score units (4 per aligned row, a low estimate
+      // of the score density), plus two.  The levels are sized for THAT: with 100 unrelated hits and one full-length
+      // alignment (C4) the pass is a single long chain that wants a scheduler per stripe, with 100 long alignments (C3) it is
+      // throughput work that wants every warp.
+      __shared__ unsigned long long busy_est;
+      if (threadIdx.x == 0) busy_est = 0ull;
+      __syncthreads();
+      unsigned long long mine = 0;
+      const int nt = P.n_targets;
+      for (int h = threadIdx.x; h < nt; h += blockDim.x) mine += (unsigned long long)((unsigned)(P.hit_keys[h] >> 32) >> 10) + 2ull;
+      atomicAdd(&busy_est, mine);
+      __syncthreads();
+      items = min(items, (long long)busy_est);
+    }
     const long long per_level = (long long)P.level_ctas * K3X_WARPS;
     if (items <= (long long)cta_level * per_level) return;
     if (cta_level > 0 && items < (long long)gridDim.x * K3X_WARPS) __nanosleep(3000u * (unsigned)min(cta_level, 8));

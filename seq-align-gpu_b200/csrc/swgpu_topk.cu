@@ -174,15 +174,8 @@ int enqueue_topk(swgpu_db* db, swgpu_slot& S, int k) {
       P.epoch = S.x_epoch; P.done = S.d_x_done; P.partial = S.d_x_partial; P.rows = S.d_x_rows;
       P.sm_slots = S.d_x_done + swk::K3X_SLOTS; P.level_ctas = db->sm_count;
       P.phase = phase; P.counter = S.d_counters + 8 + phase; P.stop_col = S.d_hit_sidx + (3 + phase) * cap;
-      // The reversed pass stops at the alignment's start: little work, but a hit whose alignment spans a whole long target is a
-      // full-length chain of stripes, and that chain runs at the pace of its most crowded scheduler: one CTA per SM
-      // (one warp per scheduler) for this pass (C4 top-100: 23.3 -> 21.2 ms; SWGPU_K3X_REV_CTAS=<1..4> overrides).
-      int g2 = grid;
-      if (phase == 1) {
-        int c = 1;
-        if (const char* ev = getenv("SWGPU_K3X_REV_CTAS")) c = std::max(1, std::min(4, atoi(ev)));
-        g2 = std::min(grid, db->sm_count * c);
-      }
+      int g2 = grid;                                       // the reversed pass sizes its levels from the hits' scores (sw_k3x.cuh)
+      if (phase == 1) { if (const char* ev = getenv("SWGPU_K3X_REV_CTAS")) g2 = std::min(grid, db->sm_count * std::max(1, std::min(4, atoi(ev)))); }   // A/B knob
       swk::k3x<true><<<g2, swk::K3X_WARPS * 32, 0, st>>>(P);
     }
     launches += 2;
