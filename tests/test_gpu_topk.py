@@ -67,14 +67,14 @@ def test_topk_coordinates_with_ties_and_early_stop(oracle, matrices):
     """The coordinate passes stop at the first column that holds the hit's (known) score.  Ties are the dangerous case: the
     same maximal score at several columns and in several stripes of query rows -- the FIRST column in the reference's scan
     order must win, whichever stripe gets there first.  Targets hold two or three exact copies of query
-    segments (equal maxima far apart, in different 128-row stripes), a copy at the very first and at the very last column,
+    segments (equal maxima far apart, in different 256-row stripes), a copy at the very first and at the very last column,
     and long background; the same hits come out with the early stop switched off (SWGPU_TOPK_NO_EARLY_STOP)."""
     import os
     import swgpu
     from swgpu import synth
     tab = matrices["BLOSUM62"]
     g = synth.rng(170)
-    q = synth.make_query(171, 900)                           # 8 stripes of 128 rows in the coordinate kernel
+    q = synth.make_query(171, 900)                           # 4 stripes of 256 rows in the coordinate kernel
     bgr = lambda n: synth.residues(g, int(n))
     parts = [
         np.concatenate([bgr(700), q[100:300], bgr(1500), q[100:300], bgr(900)]),               # the same segment twice: equal maxima
