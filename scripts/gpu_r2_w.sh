@@ -1,15 +1,16 @@
 #!/bin/bash
-# round 2, A/B w: every multi-stripe plan (rows per lane) with and without the nested column loop, two query lengths
+# round 2, A/B w2: every multi-stripe plan under the four combinations of (nested column loop, slot pointer in registers)
 mkdir -p gpurun_out
-for v in "" _vnested; do
-  SWGPU_LIB=seq-align-gpu_b200/libswgpu$v.so timeout 900 python scripts/tune_plan.py --lqs 2005,4743 > gpurun_out/r2w_tune$v.jsonl 2>&1; echo "rc=$?"
+for v in n0s0 n0s1 n1s0 n1s1; do
+  SWGPU_LIB=seq-align-gpu_b200/libswgpu_v$v.so timeout 900 python scripts/tune_plan.py --lqs 2005 > gpurun_out/r2w2_tune_$v.jsonl 2>&1; echo "$v rc=$?"
 done
+SWGPU_LIB=seq-align-gpu_b200/libswgpu.so timeout 900 python scripts/tune_plan.py --lqs 2005 > gpurun_out/r2w2_tune_intree.jsonl 2>&1
 python - <<'PY'
 import json
-a=[json.loads(l) for l in open('gpurun_out/r2w_tune.jsonl') if l.startswith('{')]
-b=[json.loads(l) for l in open('gpurun_out/r2w_tune_vnested.jsonl') if l.startswith('{')]
-for x,y in zip(a,b):
-    print('lq',x['lq'])
-    for k in x['all']:
-        if k in y['all']: print('  ',k, x['all'][k], y['all'][k], round(y['all'][k]/x['all'][k],4))
+R={}
+for v in ("n0s0","n0s1","n1s0","n1s1","intree"):
+    R[v]=[json.loads(l) for l in open(f'gpurun_out/r2w2_tune_{v}.jsonl') if l.startswith('{')][0]['all']
+for k in R["n0s0"]:
+    b=R["n0s0"][k]
+    print(f"{k:10s} n0s0 {b:8.3f}  " + "  ".join(f"{v} {R[v][k]/b:.4f}" for v in ("n0s1","n1s0","n1s1","intree")))
 PY

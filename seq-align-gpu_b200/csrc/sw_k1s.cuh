@@ -310,14 +310,14 @@ __global__ void __launch_bounds__(K1S_WARPS * 32, (R <= K1S_R3CTA ? 3 : 2)) k1s(
 
       // where this lane's maxima go: slot of the stream's first pair and the distance to the next pair's, in registers -- the
       // flush (once per pair) then touches no kernel parameter (its constant-bank loads sat in the column loop's body).
-      // A/B per plan on the C2 database (profiles/r2y_ab_slot_ptr.txt): 1.1-1.7 % faster for the multi-stripe kernels except
-      // R = 24 and 28 (1.2-1.4 % slower), within +-0.7 % for the single-stripe ones except g x R = 32 x 32 (1.8 % slower).
+      // A/B per plan on the C2 database (profiles/r2y_ab_slot_ptr.txt, r2w2_ab_nested_x_slot.txt): 1-3 % faster for the multi-stripe
+      // kernels except R = 26 and 28 (1-2.5 % slower), within +-0.7 % for the single-stripe ones except g x R = 32 x 32 (1.8 % slower).
       // Also tried there: the four IDP byte selectors in registers instead of re-materialised uniform registers (4 UMOV per
       // column step): 2-4 % SLOWER in the multi-stripe kernels, not kept.
 #ifndef K1S_SLOT_PTR
 #define K1S_SLOT_PTR (-1)
 #endif
-      constexpr bool SLOTP = K1S_SLOT_PTR >= 0 ? K1S_SLOT_PTR != 0 : (MULTI ? (R != 24 && R != 28) : !(R == 32 && g == 32));
+      constexpr bool SLOTP = K1S_SLOT_PTR >= 0 ? K1S_SLOT_PTR != 0 : (MULTI ? (R != 26 && R != 28) : !(R == 32 && g == 32));
       unsigned* slot0 = nullptr; int slot_stride = 0;
       if (SLOTP && valid) {
         const size_t p0 = (size_t)P.stream_pair0[st];
@@ -425,13 +425,12 @@ __global__ void __launch_bounds__(K1S_WARPS * 32, (R <= K1S_R3CTA ? 3 : 2)) k1s(
           if (PF) cw_next = lds32_ordered(rd_lane + ((unsigned)((s + 1) & (RN - 1)) << 2));   // next step's ring word (re-loaded after a publish, above)
       };
       // Multi-stripe kernels: blocks of 32 steps without the per-step block test, for the rows-per-lane values where that is
-      // faster (every multi-stripe plan timed both ways on the C2 database, profiles/r2w_ab_nested_per_R.txt: R = 16, 24, 28,
-      // 29, 30, 32: 0.7-2.7 % faster; 20, 31: the same; 25, 26, 27: 1.4-2.3 % slower).  -DK1S_NESTED=0 / 1 forces one form.
+      // faster: every multi-stripe plan timed on the C2 database under the four combinations of this and the slot pointer below
+      // (profiles/r2w_ab_nested_per_R.txt, r2w2_ab_nested_x_slot.txt): nested for every R but 26, 27, 31.  -DK1S_NESTED=0 / 1 forces one form.
 #ifndef K1S_NESTED
 #define K1S_NESTED (-1)
 #endif
-      constexpr bool NEST = MULTI && (K1S_NESTED >= 0 ? K1S_NESTED != 0
-                                                      : (R == 16 || R == 24 || R == 28 || R == 29 || R == 30 || R == 32));
+      constexpr bool NEST = MULTI && (K1S_NESTED >= 0 ? K1S_NESTED != 0 : (R != 26 && R != 27 && R != 31));
       if (NEST) {
         for (int s0 = 0; s0 < nsteps; s0 += 32) {
           boundary(s0);

@@ -361,8 +361,8 @@ K1SPlan plan_k1s(int64_t lq, int64_t n_streams, int warp_slots) {
     // profiles/r2c_tune_plan.jsonl, r2w_ab_nested_per_R.txt).  A database too small to fill the GPU runs every stream as X items on one CTA per SM, a
     // latency regime with its own ranking (profiles/r1f_c4_plans.txt): it keeps the table measured there.
     struct MultiCost { int R; double us_per_row; };
-    static const MultiCost kBulk[] = {{16, 40.6}, {20, 35.54}, {24, 34.6}, {25, 35.2}, {26, 33.5}, {27, 34.24},
-                                      {28, 33.68}, {29, 33.67}, {30, 34.05}, {31, 33.43}, {32, 33.37}};   // profiles/r2w_ab_nested_per_R.txt
+    static const MultiCost kBulk[] = {{16, 39.9}, {20, 35.5}, {24, 34.11}, {25, 34.06}, {26, 33.46}, {27, 33.85},
+                                      {28, 33.68}, {29, 33.33}, {30, 33.9}, {31, 33.06}, {32, 32.86}};   // profiles/r2w2_ab_nested_x_slot.txt
     static const MultiCost kFew[] = {{16, 44.2}, {20, 39.7}, {24, 37.63}, {25, 37.96}, {26, 36.94}, {27, 36.85},
                                      {28, 36.3}, {29, 36.55}, {30, 36.8}, {31, 37.8}, {32, 36.72}};
     const bool few = n_streams < 2 * (int64_t)warp_slots;
