@@ -17,10 +17,13 @@
 //   * target slots (rows, per-stripe results) are reused round-robin: a warp starts an item of
 //     target t only after target t - K3X_SLOTS has completed (done counter per slot);
 //   * the last warp to finish a target reduces the per-stripe results and writes the target's output.
-// Inside a warp the scheme is k3_intra's: lane l owns 4 rows, the target streams through the lanes by
+// Inside a warp the scheme is k3_intra's: lane l owns 8 rows, the target streams through the lanes by
 // __shfl_up_sync.  The cell update is the latency-optimised form: with Hx = max(0, t, G) (independent of V)
 //   V' = max(V + ge, Hx + oe)     -- the only row-to-row dependency, one VIADDMNMX
 //   H  = max(Hx, V)                 G' = max(G + ge, H + oe)
+// evaluated on gap states shifted by -oe so that every operation has one add (4 VIADDMNMX + 1 IDP per cell, see the kernel).
+// Placement of the items on the machine (CTA levels per SM), the block-ahead fetches and the warp-uniform waits are described
+// where they are implemented; DESIGN.md section 5 has the measurements that led to each of them.
 // Used for (a) the coordinate passes of top-k (TRACK: first maximum in the reference's scan order)
 // and (b) 32-bit rescoring of long targets.
 #pragma once
