@@ -227,6 +227,13 @@ int swgpu_score_targets_noalloc(int device, const int8_t *d_query, int32_t query
                                 int32_t max_target_len, const int8_t *d_table, int gap_open, int gap_extend,
                                 int32_t *d_scores, void *stream);
 
+/* Debug mode, no counterpart in the reference: with SWGPU_GUARD=1 in the environment every device allocation of the engine carries a
+ * 512-byte tail of a known pattern.  swgpu_guard_check() reads the tails of all live allocations back and returns the number of
+ * damaged ones (each is described on stderr); -1 when the mode is off.  swgpu_db_destroy() runs it too and aborts on damage.
+ * swgpu_guard_selftest() overruns a scratch allocation by one byte on purpose and returns 1 when the check reports exactly that. */
+int swgpu_guard_check(void);
+int swgpu_guard_selftest(void);
+
 #ifdef __cplusplus
 }
 #endif

@@ -15,6 +15,74 @@
 #include <cstring>
 #include <vector>
 #include <algorithm>
+#include <map>
+#include <mutex>
+
+// ---- guard zones (swgpu_internal.h) ----
+namespace swi {
+namespace {
+constexpr size_t kGuardBytes = 512;
+struct GuardRec { size_t bytes; int device; };
+std::mutex& guard_mu() { static std::mutex m; return m; }
+std::map<void*, GuardRec>& guard_map() { static std::map<void*, GuardRec> m; return m; }
+bool guard_on() { static const bool on = [] { const char* e = getenv("SWGPU_GUARD"); return e && atoi(e) > 0; }(); return on; }
+}  // namespace
+
+cudaError_t guard_malloc(void** p, size_t bytes) {
+  if (!guard_on()) return (cudaMalloc)(p, bytes);
+  cudaError_t e = (cudaMalloc)(p, bytes + kGuardBytes);
+  if (e != cudaSuccess) return e;
+  e = cudaMemset((char*)*p + bytes, 0xA5, kGuardBytes);
+  if (e != cudaSuccess) return e;
+  int dev = 0; cudaGetDevice(&dev);
+  std::lock_guard<std::mutex> lk(guard_mu());
+  guard_map()[*p] = GuardRec{bytes, dev};
+  return cudaSuccess;
+}
+
+cudaError_t guard_free(void* p) {
+  if (guard_on() && p) { std::lock_guard<std::mutex> lk(guard_mu()); guard_map().erase(p); }
+  return (cudaFree)(p);
+}
+
+int guard_check() {
+  if (!guard_on()) return -1;
+  std::lock_guard<std::mutex> lk(guard_mu());
+  int cur = 0; cudaGetDevice(&cur);
+  int bad = 0;
+  unsigned char tail[kGuardBytes];
+  for (const auto& kv : guard_map()) {
+    cudaSetDevice(kv.second.device);
+    cudaDeviceSynchronize();
+    if (cudaMemcpy(tail, (const char*)kv.first + kv.second.bytes, kGuardBytes, cudaMemcpyDeviceToHost) != cudaSuccess) { ++bad; continue; }
+    size_t first = kGuardBytes;
+    for (size_t i = 0; i < kGuardBytes; ++i) if (tail[i] != 0xA5) { first = i; break; }
+    if (first < kGuardBytes) {
+      ++bad;
+      fprintf(stderr, "SWGPU_GUARD: allocation %p of %zu bytes on device %d was written past its end (first damaged byte at +%zu)\n",
+              kv.first, kv.second.bytes, kv.second.device, first);
+    }
+  }
+  cudaSetDevice(cur);
+  return bad;
+}
+}  // namespace swi
+
+extern "C" int swgpu_guard_check(void) { return swi::guard_check(); }
+
+// Proof that the check sees what it is for: one byte written past the end of a guarded allocation must be reported.
+// Returns 1 when exactly that allocation was reported, 0 otherwise, -1 when the mode is off.
+extern "C" int swgpu_guard_selftest(void) {
+  if (swi::guard_check() < 0) return -1;
+  const int before = swi::guard_check();
+  void* p = nullptr;
+  if (swi::guard_malloc(&p, 1000) != cudaSuccess) return 0;
+  cudaMemset((char*)p + 1000, 0, 1);                       // the overrun
+  const int during = swi::guard_check();
+  swi::guard_free(p);
+  const int after = swi::guard_check();
+  return (during == before + 1 && after == before) ? 1 : 0;
+}
 
 namespace {
 
@@ -235,6 +303,7 @@ void swgpu_db_destroy(swgpu_db_t* db) {
   if (!db) return;
   cudaSetDevice(db->device);
   cudaDeviceSynchronize();
+  if (swi::guard_check() > 0) { fprintf(stderr, "SWGPU_GUARD: damaged guard zones at swgpu_db_destroy\n"); abort(); }   // debug mode only
   cudaFree(db->d_plain); cudaFree(db->d_plain_off); cudaFree(db->d_order);
   cudaFree(db->d_scols); cudaFree(db->d_stream_off); cudaFree(db->d_stream_ncols); cudaFree(db->d_stream_pair0);
   for (auto& S : db->slots) swi::slot_release(S);

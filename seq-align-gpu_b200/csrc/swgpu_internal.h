@@ -18,6 +18,18 @@ inline int fail(int code, const char* fmt, ...) {
 
 }  // namespace swi
 
+// Guard zones (debug mode, SWGPU_GUARD=1 in the environment): every device allocation of the engine gets a 512-byte tail filled
+// with 0xA5, and swgpu_guard_check() (include/swgpu.h) reads all live tails back and counts the damaged ones -- a write past the
+// end of any engine buffer shows up there.  This pool refuses compute-sanitizer (profiles/r2_sanitize_gpu.txt); this is what
+// stands in for its memcheck on the write side.  Off (the default), the two wrappers are cudaMalloc / cudaFree.
+namespace swi {
+cudaError_t guard_malloc(void** p, size_t bytes);
+cudaError_t guard_free(void* p);
+int guard_check();                     // damaged tails among this process's live engine allocations; -1 when the mode is off
+}
+#define cudaMalloc(p, n) swi::guard_malloc((void**)(p), (n))
+#define cudaFree(p) swi::guard_free((void*)(p))
+
 #define CU(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) \
   return swi::fail(e_ == cudaErrorNoDevice || e_ == cudaErrorInsufficientDriver ? SWGPU_ENODEV : SWGPU_ECUDA, \
               "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); } while (0)

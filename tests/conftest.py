@@ -31,3 +31,13 @@ def matrices():
 
 def golden(name):
     return np.load(os.path.join(GOLDEN, name), allow_pickle=False)
+
+
+@pytest.fixture(autouse=True)
+def _guard_zones(request):
+    """Debug mode SWGPU_GUARD=1 (include/swgpu.h): after every GPU test, no live engine allocation may have been written past
+    its end.  Off by default; scripts/gpu_guard.sh runs the GPU suite with it (this pool refuses compute-sanitizer)."""
+    yield
+    if os.environ.get("SWGPU_GUARD") and request.node.get_closest_marker("gpu"):
+        import swgpu
+        assert swgpu.lib().swgpu_guard_check() == 0, "a device buffer of the engine was written past its end (see stderr)"
